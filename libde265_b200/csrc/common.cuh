@@ -1,0 +1,68 @@
+// common.cuh — shared device helpers for the b265 reconstruction kernels (sm_100a).
+// Arithmetic macros follow libde265/util.h:109-116 (Clip3 / Clip_BitDepth / Sign).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/b265.h"
+
+#define B265_WARPS_PER_CTA 8
+#define B265_FULL_MASK 0xffffffffu
+
+__device__ __forceinline__ int clip3(int lo, int hi, int v) { return min(max(v, lo), hi); }
+__device__ __forceinline__ int clip16(int v) { return min(max(v, -32768), 32767); }
+__device__ __forceinline__ int clip8(int v) { return min(max(v, 0), 255); }
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+
+// loads that must observe stores made by other SMs of the same launch (bypass the non-coherent L1)
+__device__ __forceinline__ uint8_t ld_cg_u8(const uint8_t* p) {
+  unsigned v;
+  asm volatile("ld.global.cg.u8 %0, [%1];" : "=r"(v) : "l"(p));
+  return (uint8_t)v;
+}
+__device__ __forceinline__ uint32_t ld_cg_u32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t ld_acquire_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint8_t ld_acquire_u8(const uint8_t* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return (uint8_t)v;
+}
+__device__ __forceinline__ void st_release_u8(uint8_t* p, uint8_t v) {
+  asm volatile("st.release.gpu.global.u8 [%0], %1;" ::"l"(p), "r"((unsigned)v) : "memory");
+}
+
+// Device-side view of one picture being reconstructed (built by backend.cu from b265_frame_job).
+struct FrameDev {
+  uint8_t* plane[3];       // recon target (pre-deblock); == out[] when SAO is off
+  uint8_t* out[3];         // final (post-SAO) surface planes
+  int pitch[3];
+  int width, height;       // luma
+  int cw, ch;              // chroma plane size (0 for 4:0:0)
+  int log2_ctb, log2_min_cb, log2_min_tb;
+  int ctbs_w, ctbs_h;
+  uint32_t flags;          // B265_FRAME_*
+  int cb_qp_offset, cr_qp_offset;
+  const b265_tu* tus;
+  const b265_coeff* coeffs;
+  const b265_pu* pus;
+  const b265_slice* slices;
+  const b265_ctb* ctbs;       // may be NULL
+  const b265_sao* sao;        // may be NULL
+  const uint8_t* unit_info;   // may be NULL
+  const int8_t* qp_y;         // may be NULL
+  const b265_scaling* scaling;
+  uint8_t* done[3];           // intra wavefront completion flags, one byte per 4x4 samples of the plane
+  int done_pitch[3];
+  uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal
+  uint32_t* motion;           // per 4x4 luma unit: 4 words {ref ids, mv0, mv1, flags} rasterised from PUs
+  const uint8_t* ref_plane[16][3];
+  int ref_poc[16];
+  int n_refs;
+};

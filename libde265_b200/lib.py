@@ -1,0 +1,233 @@
+"""ctypes binding of the C ABI in include/b265.h (libb265.so).
+
+Host-side mirror used by the tests, bench.py and the Python decoder wrapper.  The library is the
+product; this module only loads it and declares the record layouts.  If the CUDA library is missing
+it raises — there is no CPU path behind these calls.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libb265.so")
+
+B265_OK = 0
+MEM_HOST, MEM_DEVICE = 0, 1
+TR_DCT, TR_DST, TR_SKIP, TR_BYPASS = 0, 1, 2, 3
+
+TU_DST, TU_SKIP, TU_BYPASS, TU_RDPCM_H, TU_RDPCM_V, TU_ROTATE, TU_NO_EDGE_FILT, TU_INTRA_CU = \
+    0x01, 0x02, 0x04, 0x08, 0x10, 0x20, 0x40, 0x80
+INTRA_NONE = 0xFF
+PU_L0, PU_L1 = 1, 2
+UNIT_EDGE_V, UNIT_EDGE_H, UNIT_TU_EDGE_V, UNIT_TU_EDGE_H, UNIT_INTRA, UNIT_CBF, UNIT_NOFILT, UNIT_DONE = \
+    0x01, 0x02, 0x04, 0x08, 0x10, 0x20, 0x40, 0x80
+FRAME_STRONG_INTRA_SMOOTHING, FRAME_CONSTRAINED_INTRA, FRAME_LF_ACROSS_TILES, FRAME_DEBLOCK, \
+    FRAME_SAO, FRAME_SCALING_LIST, FRAME_PCM_LF_DISABLE = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
+
+
+class Coeff(C.Structure):
+    _fields_ = [("level", C.c_int16), ("pos", C.c_uint16)]
+
+
+class TU(C.Structure):
+    _fields_ = [("x", C.c_uint16), ("y", C.c_uint16), ("cidx_log2", C.c_uint8), ("flags", C.c_uint8),
+                ("qp", C.c_uint8), ("intra_mode", C.c_uint8), ("coeff_off", C.c_uint32),
+                ("ncoeff", C.c_uint16), ("reserved", C.c_uint16)]
+
+
+class PU(C.Structure):
+    _fields_ = [("x", C.c_uint16), ("y", C.c_uint16), ("w", C.c_uint8), ("h", C.c_uint8),
+                ("flags", C.c_uint8), ("slice", C.c_uint8), ("mv", (C.c_int16 * 2) * 2),
+                ("ref_idx", C.c_int8 * 2), ("ref_slot", C.c_uint8 * 2), ("reserved", C.c_uint32)]
+
+
+class PCM(C.Structure):
+    _fields_ = [("x", C.c_uint16), ("y", C.c_uint16), ("log2_size", C.c_uint8),
+                ("reserved", C.c_uint8 * 3), ("sample_off", C.c_uint32)]
+
+
+class SAO(C.Structure):
+    _fields_ = [("type", C.c_uint8 * 3), ("band_eo", C.c_uint8 * 3), ("offset", (C.c_int8 * 4) * 3)]
+
+
+class CTB(C.Structure):
+    _fields_ = [("addr_ts", C.c_int32), ("slice", C.c_uint16), ("tile", C.c_uint16)]
+
+
+class Slice(C.Structure):
+    _fields_ = [("slice_addr_rs", C.c_int32), ("slice_type", C.c_int8), ("beta_offset", C.c_int8),
+                ("tc_offset", C.c_int8), ("deblocking_disabled", C.c_uint8),
+                ("lf_across_slices", C.c_uint8), ("sao_luma", C.c_uint8), ("sao_chroma", C.c_uint8),
+                ("weighted", C.c_uint8), ("luma_log2_denom", C.c_uint8),
+                ("chroma_log2_denom", C.c_uint8), ("pad", C.c_uint8 * 2),
+                ("weight", ((C.c_int16 * 3) * 16) * 2), ("offset", ((C.c_int16 * 3) * 16) * 2)]
+
+
+class Scaling(C.Structure):
+    _fields_ = [("s4", (C.c_uint8 * 16) * 6), ("s8", (C.c_uint8 * 64) * 6),
+                ("s16", (C.c_uint8 * 256) * 6), ("s32", (C.c_uint8 * 1024) * 6)]
+
+
+class FrameJob(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("chroma_format_idc", C.c_uint8),
+                ("bit_depth", C.c_uint8), ("log2_ctb", C.c_uint8), ("log2_min_cb", C.c_uint8),
+                ("log2_min_tb", C.c_uint8), ("cb_qp_offset", C.c_int8), ("cr_qp_offset", C.c_int8),
+                ("log2_sao_offset_scale_unused", C.c_uint8), ("flags", C.c_uint32),
+                ("dst_surface", C.c_int32), ("ref_surfaces", C.c_int32 * 32), ("ref_poc", C.c_int32 * 32),
+                ("n_refs", C.c_int32),
+                ("tus", C.POINTER(TU)), ("n_tus", C.c_int32),
+                ("coeffs", C.POINTER(Coeff)), ("n_coeffs", C.c_int32),
+                ("pus", C.POINTER(PU)), ("n_pus", C.c_int32),
+                ("pcms", C.POINTER(PCM)), ("n_pcms", C.c_int32),
+                ("pcm_samples", C.POINTER(C.c_uint8)), ("n_pcm_samples", C.c_int32),
+                ("slices", C.POINTER(Slice)), ("n_slices", C.c_int32),
+                ("ctbs", C.POINTER(CTB)), ("sao", C.POINTER(SAO)),
+                ("unit_info", C.POINTER(C.c_uint8)), ("qp_y", C.POINTER(C.c_int8)),
+                ("scaling", C.POINTER(Scaling))]
+
+
+_lib = None
+
+
+class B265Error(RuntimeError):
+    pass
+
+
+def load():
+    """Load libb265.so (raises if it has not been built: python -m libde265_b200.build)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise B265Error("libb265.so not built (run `python -m libde265_b200.build`); "
+                        "there is no CPU fallback for the b265 pixel path")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, u8p, i16p = C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_int16)
+    lib.b265_version.restype = C.c_char_p
+    lib.b265_status_string.restype = C.c_char_p
+    lib.b265_status_string.argtypes = [i32]
+    lib.b265_last_error.restype = C.c_char_p
+    lib.b265_last_error.argtypes = [vp]
+    lib.b265_create.argtypes = [i32, C.POINTER(vp)]
+    lib.b265_destroy.argtypes = [vp]
+    lib.b265_destroy.restype = None
+    lib.b265_sync.argtypes = [vp]
+    lib.b265_launch_count.argtypes = [vp]
+    lib.b265_launch_count.restype = C.c_uint64
+    lib.b265_host_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    lib.b265_host_free.argtypes = [vp, vp]
+    lib.b265_host_free.restype = None
+    lib.b265_dev_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
+    lib.b265_dev_free.argtypes = [vp, vp]
+    lib.b265_dev_free.restype = None
+    lib.b265_memcpy_h2d.argtypes = [vp, vp, vp, C.c_size_t]
+    lib.b265_memcpy_d2h.argtypes = [vp, vp, vp, C.c_size_t]
+    lib.b265_timer_start.argtypes = [vp]
+    lib.b265_timer_stop.argtypes = [vp, C.POINTER(C.c_float)]
+    lib.b265_flush_l2.argtypes = [vp]
+    lib.b265_surface_alloc.argtypes = [vp, i32, i32, i32, C.POINTER(i32)]
+    lib.b265_surface_release.argtypes = [vp, i32]
+    lib.b265_surface_fill.argtypes = [vp, i32, i32, i32]
+    lib.b265_surface_upload.argtypes = [vp, i32, i32, vp, C.c_ssize_t]
+    lib.b265_surface_download.argtypes = [vp, i32, i32, vp, C.c_ssize_t, i32]
+    lib.b265_surface_plane.argtypes = [vp, i32, i32, C.POINTER(vp), C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]
+    lib.b265_residual_batch.argtypes = [vp, i32, i32, i32, i32, i32, vp, vp, vp]
+    for name, args in _OPTIONAL.items():
+        if hasattr(lib, name):
+            getattr(lib, name).argtypes = args
+    _lib = lib
+    return lib
+
+
+_vp, _i32 = C.c_void_p, C.c_int
+_OPTIONAL = {
+    "b265_residual_sparse": [_vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32],
+    "b265_mc_batch": [_vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _vp, _i32, _i32, _i32, _i32],
+    "b265_interp_batch": [_vp, _i32, _i32, _i32, _i32, _i32, _vp, C.c_ssize_t, C.c_ssize_t, _vp, _vp],
+    "b265_intra_batch": [_vp, _i32, _i32, _i32, _i32, _vp, _vp, _i32, _i32, _vp],
+    "b265_deblock_planes": [_vp, _i32, _vp, _vp, _i32, _i32],
+    "b265_sao_planes": [_vp, _i32, _vp, _vp, _vp, _i32, _i32],
+    "b265_submit_frames": [_vp, _vp, _i32],
+    "b265_upload_frames": [_vp, _vp, _i32, C.POINTER(_vp)],
+    "b265_run_batch": [_vp, _vp],
+    "b265_free_batch": [_vp, _vp],
+    "b265_set_stage_timing": [_vp, _i32],
+    "b265_get_stage_times": [_vp, C.POINTER(C.c_float * 6)],
+}
+
+
+def check(ctx, status, what=""):
+    if status != B265_OK:
+        lib = load()
+        msg = lib.b265_status_string(status).decode()
+        detail = lib.b265_last_error(ctx).decode() if ctx else ""
+        raise B265Error("%s failed: %s (%s)" % (what or "b265 call", msg, detail))
+
+
+class Context:
+    """One decoder back end == one CUDA device + stream (b265_ctx)."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = C.c_void_p()
+        st = self.lib.b265_create(device, C.byref(h))
+        if st != B265_OK:
+            raise B265Error("b265_create(device=%d): %s — the b265 pixel path requires a CUDA device, "
+                            "there is no CPU fallback" % (device, self.lib.b265_status_string(st).decode()))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.b265_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def sync(self):
+        check(self.h, self.lib.b265_sync(self.h), "sync")
+
+    @property
+    def launches(self):
+        return int(self.lib.b265_launch_count(self.h))
+
+    # -- device memory helpers ------------------------------------------------------------------
+    def dev_alloc(self, nbytes):
+        p = C.c_void_p()
+        check(self.h, self.lib.b265_dev_alloc(self.h, nbytes, C.byref(p)), "dev_alloc")
+        return p
+
+    def dev_free(self, p):
+        self.lib.b265_dev_free(self.h, p)
+
+    def h2d(self, dptr, arr):
+        check(self.h, self.lib.b265_memcpy_h2d(self.h, dptr, arr.ctypes.data, arr.nbytes), "h2d")
+
+    def d2h(self, arr, dptr):
+        check(self.h, self.lib.b265_memcpy_d2h(self.h, arr.ctypes.data, dptr, arr.nbytes), "d2h")
+
+    def timer_start(self):
+        check(self.h, self.lib.b265_timer_start(self.h), "timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float()
+        check(self.h, self.lib.b265_timer_stop(self.h, C.byref(ms)), "timer_stop")
+        return ms.value
+
+    def flush_l2(self):
+        check(self.h, self.lib.b265_flush_l2(self.h), "flush_l2")
+
+    # -- kernel-level calls ---------------------------------------------------------------------
+    def residual_batch(self, kind, log2, coeffs, dst, qp=None, rdpcm=0):
+        """In-place on `dst` (numpy uint8 [n, nT, nT]); coeffs int16 [n, nT, nT] (host buffers)."""
+        n = coeffs.shape[0]
+        check(self.h, self.lib.b265_residual_batch(
+            self.h, MEM_HOST, kind, log2, rdpcm, n, coeffs.ctypes.data,
+            qp.ctypes.data if qp is not None else None, dst.ctypes.data), "residual_batch")
+        return dst
+
+    def residual_batch_dev(self, kind, log2, n, d_coeffs, d_dst, d_qp=None, rdpcm=0):
+        check(self.h, self.lib.b265_residual_batch(self.h, MEM_DEVICE, kind, log2, rdpcm, n, d_coeffs,
+                                                   d_qp, d_dst), "residual_batch(dev)")
