@@ -182,7 +182,9 @@ typedef struct {
   uint8_t weighted;                   /* 1 => explicit weighted prediction applies to this slice
                                          (P: pps weighted_pred_flag, B: weighted_bipred_flag) */
   uint8_t luma_log2_denom, chroma_log2_denom;
-  uint8_t pad[2];
+  uint8_t pps_weighted_pred;          /* pps weighted_pred_flag: the identical-MV bi->uni collapse is
+                                         keyed on THIS flag for P and B slices alike (motion.cc:326) */
+  uint8_t pad;
   int16_t weight[2][16][3];           /* LumaWeight / ChromaWeight[.][.][0..1] (slice.h:195-203) */
   int16_t offset[2][16][3];           /* luma_offset / ChromaOffset, NOT yet scaled by bit depth */
 } b265_slice;

@@ -8,3 +8,4 @@ void launch_residual_dense(cudaStream_t st, int log2, int kind, int rdpcm, int n
                            const int16_t* coeffs, const uint8_t* qp, uint8_t* dst, int sm_count);
 void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order,
                             int n, int sm_count);
+void launch_mc(cudaStream_t st, const FrameDev* frames, const uint32_t* items, int n, int sm_count);

@@ -58,7 +58,7 @@ class Slice(C.Structure):
                 ("tc_offset", C.c_int8), ("deblocking_disabled", C.c_uint8),
                 ("lf_across_slices", C.c_uint8), ("sao_luma", C.c_uint8), ("sao_chroma", C.c_uint8),
                 ("weighted", C.c_uint8), ("luma_log2_denom", C.c_uint8),
-                ("chroma_log2_denom", C.c_uint8), ("pad", C.c_uint8 * 2),
+                ("chroma_log2_denom", C.c_uint8), ("pps_weighted_pred", C.c_uint8), ("pad", C.c_uint8),
                 ("weight", ((C.c_int16 * 3) * 16) * 2), ("offset", ((C.c_int16 * 3) * 16) * 2)]
 
 
@@ -231,3 +231,15 @@ class Context:
     def residual_batch_dev(self, kind, log2, n, d_coeffs, d_dst, d_qp=None, rdpcm=0):
         check(self.h, self.lib.b265_residual_batch(self.h, MEM_DEVICE, kind, log2, rdpcm, n, d_coeffs,
                                                    d_qp, d_dst), "residual_batch(dev)")
+
+    def mc_batch(self, pus, slices, refs, dst, width, height):
+        """pus: ctypes array of PU; slices: ctypes array of Slice; refs: list of (Y,Cb,Cr) numpy
+        planes (contiguous, pitch = row length); dst: (Y,Cb,Cr) numpy planes, modified in place."""
+        import numpy as np
+        n_refs = len(refs)
+        rp = (C.c_void_p * (3 * n_refs))(*[p.ctypes.data for r in refs for p in r])
+        dp = (C.c_void_p * 3)(*[p.ctypes.data for p in dst])
+        check(self.h, self.lib.b265_mc_batch(self.h, MEM_HOST, C.byref(pus), len(pus), C.byref(slices), len(slices),
+                                             rp, n_refs, dp, width, height, dst[0].shape[1], dst[1].shape[1]),
+              "mc_batch")
+        return dst
