@@ -66,3 +66,10 @@ struct FrameDev {
   int ref_poc[16];
   int n_refs;
 };
+
+// one ticket of the intra wavefront: `count` (<= 32/N) TBs of size 2^log2 and equal wave, order[first..]
+struct TuGroup {
+  uint32_t first;
+  uint16_t count;
+  uint16_t log2;
+};

@@ -243,3 +243,59 @@ class Context:
                                              rp, n_refs, dp, width, height, dst[0].shape[1], dst[1].shape[1]),
               "mc_batch")
         return dst
+
+    # -- surfaces + frame-level path ------------------------------------------------------------
+    def surface_alloc(self, width, height, chroma=1):
+        sid = C.c_int()
+        check(self.h, self.lib.b265_surface_alloc(self.h, width, height, chroma, C.byref(sid)), "surface_alloc")
+        return sid.value
+
+    def surface_release(self, sid):
+        check(self.h, self.lib.b265_surface_release(self.h, sid), "surface_release")
+
+    def surface_fill(self, sid, luma, chroma):
+        check(self.h, self.lib.b265_surface_fill(self.h, sid, luma, chroma), "surface_fill")
+
+    def surface_upload(self, sid, planes):
+        for c, p in enumerate(planes):
+            check(self.h, self.lib.b265_surface_upload(self.h, sid, c, p.ctypes.data, p.strides[0]), "surface_upload")
+        self.sync()
+
+    def surface_download(self, sid, width, height, chroma=1):
+        import numpy as np
+        shapes = [(height, width)] + ([((height + 1) // 2, (width + 1) // 2)] * 2 if chroma else [])
+        out = [np.empty(s, dtype=np.uint8) for s in shapes]
+        for c, p in enumerate(out):
+            check(self.h, self.lib.b265_surface_download(self.h, sid, c, p.ctypes.data, p.strides[0], 0), "download")
+        self.sync()
+        return out
+
+    def submit_frames(self, jobs):
+        arr = (FrameJob * len(jobs))(*jobs)
+        check(self.h, self.lib.b265_submit_frames(self.h, C.byref(arr), len(jobs)), "submit_frames")
+
+    def upload_frames(self, jobs):
+        arr = (FrameJob * len(jobs))(*jobs)
+        b = C.c_void_p()
+        check(self.h, self.lib.b265_upload_frames(self.h, C.byref(arr), len(jobs), C.byref(b)), "upload_frames")
+        return b
+
+    def run_batch(self, batch):
+        check(self.h, self.lib.b265_run_batch(self.h, batch), "run_batch")
+
+    def free_batch(self, batch):
+        self.lib.b265_free_batch(self.h, batch)
+
+    def stage_times(self):
+        t = (C.c_float * 6)()
+        check(self.h, self.lib.b265_get_stage_times(self.h, C.byref(t)), "stage_times")
+        return list(t)
+
+
+def as_ptr(arr, typ):
+    """numpy array (or ctypes array) -> ctypes POINTER(typ); caller keeps `arr` alive."""
+    if arr is None:
+        return C.POINTER(typ)()
+    if hasattr(arr, "ctypes"):
+        return C.cast(arr.ctypes.data, C.POINTER(typ))
+    return C.cast(arr, C.POINTER(typ))

@@ -141,3 +141,125 @@ def make_planes(rng, width, height, kind="noise"):
     yy, xx = np.mgrid[0:height, 0:width]
     y = (128 + 90 * np.sin(xx / 11.0) * np.cos(yy / 7.0)).astype(np.uint8)
     return [y, np.ascontiguousarray(y[::2, ::2][:ch, :cw] // 2 + 40), np.ascontiguousarray(255 - y[::2, ::2][:ch, :cw])]
+
+
+# ---- synthetic all-intra frame jobs (frame-level path: intra wavefront + residual + filters) ----
+TU_DT = np.dtype([('x', '<u2'), ('y', '<u2'), ('cidx_log2', 'u1'), ('flags', 'u1'), ('qp', 'u1'),
+                  ('intra_mode', 'u1'), ('coeff_off', '<u4'), ('ncoeff', '<u2'), ('reserved', '<u2')])
+COEFF_DT = np.dtype([('level', '<i2'), ('pos', '<u2')])
+
+
+class SynthJob:
+    """Holds the numpy buffers of one frame job alive and exposes the ctypes FrameJob."""
+
+    def __init__(self, rng, width, height, log2_ctb=5, deblock=True, sao=False, dense=0.6, flags=0):
+        from libde265_b200 import lib as L
+        self.w, self.h, self.log2_ctb = width, height, log2_ctb
+        self.rng = rng
+        self.tus, self.coeffs = [], []
+        self.ncoef = 0
+        uw, uh = width // 4, height // 4
+        self.unit = np.zeros((uh, uw), dtype=np.uint8)
+        self.qp = np.zeros((height // 8, width // 8), dtype=np.int8)
+        self.dense = dense
+        n = 1 << log2_ctb
+        for cy in range(0, height, n):
+            for cx in range(0, width, n):
+                self._cu(cx, cy, log2_ctb)
+        self.tu_arr = np.array(self.tus, dtype=TU_DT)
+        self.co_arr = np.array(self.coeffs, dtype=COEFF_DT) if self.coeffs else np.zeros(1, dtype=COEFF_DT)
+        nctb = ((width + n - 1) // n) * ((height + n - 1) // n)
+        self.slices = (L.Slice * 1)()
+        self.slices[0].slice_type = 2
+        self.slices[0].lf_across_slices = 1
+        self.slices[0].beta_offset = int(rng.integers(-3, 4)) * 2
+        self.slices[0].tc_offset = int(rng.integers(-3, 4)) * 2
+        self.slices[0].sao_luma = self.slices[0].sao_chroma = 1
+        self.sao = None
+        if sao:
+            self.sao = (L.SAO * nctb)()
+            for i in range(nctb):
+                t = int(rng.choice([0, 1, 2], p=[0.2, 0.4, 0.4]))
+                tc = int(rng.choice([0, 1, 2], p=[0.2, 0.4, 0.4]))
+                for c in range(3):
+                    self.sao[i].type[c] = t if c == 0 else tc
+                    self.sao[i].band_eo[c] = int(rng.integers(0, 32)) if self.sao[i].type[c] == 1 else int(rng.integers(0, 4))
+                    for k in range(4):
+                        v = int(rng.integers(0, 8))
+                        if self.sao[i].type[c] == 2:
+                            v = v if k < 2 else -v
+                        else:
+                            v = int(rng.integers(-7, 8))
+                        self.sao[i].offset[c][k] = v
+                if self.sao[i].type[1] == 2:   # Cb and Cr share the edge class
+                    self.sao[i].band_eo[2] = self.sao[i].band_eo[1]
+        J = L.FrameJob()
+        J.width, J.height, J.chroma_format_idc, J.bit_depth = width, height, 1, 8
+        J.log2_ctb, J.log2_min_cb, J.log2_min_tb = log2_ctb, 3, 2
+        J.cb_qp_offset, J.cr_qp_offset = int(rng.integers(-4, 5)), int(rng.integers(-4, 5))
+        J.flags = flags | L.FRAME_STRONG_INTRA_SMOOTHING | L.FRAME_LF_ACROSS_TILES | (L.FRAME_DEBLOCK if deblock else 0) | (L.FRAME_SAO if sao else 0)
+        J.tus, J.n_tus = L.as_ptr(self.tu_arr, L.TU), len(self.tu_arr)
+        J.coeffs, J.n_coeffs = L.as_ptr(self.co_arr, L.Coeff), self.ncoef
+        J.slices, J.n_slices = C.cast(self.slices, C.POINTER(L.Slice)), 1
+        J.unit_info = L.as_ptr(self.unit, C.c_uint8)
+        J.qp_y = L.as_ptr(self.qp, C.c_int8)
+        if sao:
+            J.sao = C.cast(self.sao, C.POINTER(L.SAO))
+        self.job = J
+
+    def _cu(self, x, y, lg):
+        if x >= self.w or y >= self.h:
+            return
+        n = 1 << lg
+        must = x + n > self.w or y + n > self.h
+        if lg > 3 and (must or self.rng.random() < 0.55):
+            h = n // 2
+            for dy in (0, h):
+                for dx in (0, h):
+                    self._cu(x + dx, y + dy, lg - 1)
+            return
+        qp = int(self.rng.integers(18, 42))
+        self.qp[y // 8:(y + n) // 8, x // 8:(x + n) // 8] = qp
+        nxn = lg == 3 and self.rng.random() < 0.35
+        self._tt(x, y, lg, 0, nxn, qp, x, y, 0)
+
+    def _tt(self, x, y, lg, depth, force, qp, xb, yb, blk):
+        n = 1 << lg
+        if lg > 5 or (lg > 2 and (force or self.rng.random() < 0.4)):
+            h = n // 2
+            for i, (dx, dy) in enumerate(((0, 0), (h, 0), (0, h), (h, h))):
+                self._tt(x + dx, y + dy, lg - 1, depth + 1, False, qp, x, y, i)
+            return
+        self._tb(0, x, y, lg, qp)
+        if lg > 2:
+            self._tb(1, x // 2, y // 2, lg - 1, qp)
+            self._tb(2, x // 2, y // 2, lg - 1, qp)
+        elif blk == 3:
+            self._tb(1, xb // 2, yb // 2, 2, qp)
+            self._tb(2, xb // 2, yb // 2, 2, qp)
+
+    def _tb(self, c, x, y, lg, qp):
+        from libde265_b200 import lib as L
+        n = 1 << lg
+        rng = self.rng
+        mode = int(rng.integers(0, 35))
+        nco = 0
+        if rng.random() < self.dense:
+            nco = int(min(n * n, 1 + rng.geometric(0.25))) if rng.random() < 0.9 else int(rng.integers(1, n * n + 1))
+            pos = rng.choice(n * n, size=nco, replace=False) if nco > n * n // 4 else \
+                np.unique((rng.integers(0, min(n, 8), size=nco) + n * rng.integers(0, min(n, 8), size=nco)))
+            nco = len(pos)
+            lev = rng.integers(-40, 41, size=nco)
+            lev[lev == 0] = 1
+            for p_, l_ in zip(pos, lev):
+                self.coeffs.append((int(l_), int(p_)))
+        fl = L.TU_INTRA_CU | (L.TU_DST if (c == 0 and lg == 2) else 0)
+        self.tus.append((x, y, c | (lg << 2), fl, qp if c == 0 else max(0, qp - 3), mode, self.ncoef, nco, 0))
+        self.ncoef += nco
+        if c == 0:
+            u = self.unit[y // 4:(y + n) // 4, x // 4:(x + n) // 4]
+            u |= L.UNIT_INTRA | (L.UNIT_CBF if nco else 0)
+            if x > 0:
+                u[:, 0] |= L.UNIT_EDGE_V | L.UNIT_TU_EDGE_V
+            if y > 0:
+                u[0, :] |= L.UNIT_EDGE_H | L.UNIT_TU_EDGE_H
