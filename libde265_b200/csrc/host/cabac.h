@@ -1,0 +1,139 @@
+// cabac.h — CABAC arithmetic decoding engine (H.265 9.3.4.3) and context-variable initialisation
+// (9.3.2.2, tables 9-5 .. 9-37) for the host syntax parser.  Replaces the reference's cabac.cc
+// (decode_CABAC_bit :159-260, decode_CABAC_bypass :346-374, decode_CABAC_term_bit :277-315) and
+// contextmodel.cc (initialize_CABAC_models :279-347).  The register layout (offset scaled by 7 bits,
+// one byte fetched every 8 shifts) makes the byte position after a terminating bin identical to the
+// reference's, which PCM sample reading and sub-stream switching rely on (slice.cc:4186-4213,4824).
+#pragma once
+#include <stdint.h>
+#include <string.h>
+
+namespace b265h {
+
+// context variable: bit 0 = valMps, bits 1..6 = pStateIdx
+typedef uint8_t Ctx;
+
+enum CtxOffset {
+  CTX_SAO_MERGE = 0,                          // 1
+  CTX_SAO_TYPE = CTX_SAO_MERGE + 1,           // 1
+  CTX_SPLIT_CU = CTX_SAO_TYPE + 1,            // 3
+  CTX_CU_TQ_BYPASS = CTX_SPLIT_CU + 3,        // 1
+  CTX_CU_SKIP = CTX_CU_TQ_BYPASS + 1,         // 3
+  CTX_PRED_MODE = CTX_CU_SKIP + 3,            // 1
+  CTX_PART_MODE = CTX_PRED_MODE + 1,          // 4
+  CTX_PREV_INTRA_LUMA = CTX_PART_MODE + 4,    // 1
+  CTX_INTRA_CHROMA = CTX_PREV_INTRA_LUMA + 1, // 1
+  CTX_RQT_ROOT_CBF = CTX_INTRA_CHROMA + 1,    // 1
+  CTX_MERGE_FLAG = CTX_RQT_ROOT_CBF + 1,      // 1
+  CTX_MERGE_IDX = CTX_MERGE_FLAG + 1,         // 1
+  CTX_INTER_PRED_IDC = CTX_MERGE_IDX + 1,     // 5
+  CTX_REF_IDX = CTX_INTER_PRED_IDC + 5,       // 2
+  CTX_MVP_FLAG = CTX_REF_IDX + 2,             // 1
+  CTX_SPLIT_TRANSFORM = CTX_MVP_FLAG + 1,     // 3
+  CTX_CBF_LUMA = CTX_SPLIT_TRANSFORM + 3,     // 2
+  CTX_CBF_CHROMA = CTX_CBF_LUMA + 2,          // 5 (4 + one for 4:2:2 depth 4)
+  CTX_ABS_MVD_GT0 = CTX_CBF_CHROMA + 5,       // 1
+  CTX_ABS_MVD_GT1 = CTX_ABS_MVD_GT0 + 1,      // 1
+  CTX_CU_QP_DELTA = CTX_ABS_MVD_GT1 + 1,      // 2
+  CTX_TRANSFORM_SKIP = CTX_CU_QP_DELTA + 2,   // 2 (luma, chroma)
+  CTX_LAST_X = CTX_TRANSFORM_SKIP + 2,        // 18
+  CTX_LAST_Y = CTX_LAST_X + 18,               // 18
+  CTX_CODED_SUB_BLOCK = CTX_LAST_Y + 18,      // 4
+  CTX_SIG_COEFF = CTX_CODED_SUB_BLOCK + 4,    // 42 + 2 (transform_skip_context)
+  CTX_GT1 = CTX_SIG_COEFF + 44,               // 24
+  CTX_GT2 = CTX_GT1 + 24,                     // 6
+  CTX_EXPLICIT_RDPCM = CTX_GT2 + 6,           // 2
+  CTX_EXPLICIT_RDPCM_DIR = CTX_EXPLICIT_RDPCM + 2,     // 2
+  CTX_CHROMA_QP_OFFSET_FLAG = CTX_EXPLICIT_RDPCM_DIR + 2,  // 1
+  CTX_CHROMA_QP_OFFSET_IDX = CTX_CHROMA_QP_OFFSET_FLAG + 1, // 1
+  CTX_LOG2_RES_SCALE = CTX_CHROMA_QP_OFFSET_IDX + 1,   // 8
+  CTX_RES_SCALE_SIGN = CTX_LOG2_RES_SCALE + 8,         // 2
+  CTX_COUNT = CTX_RES_SCALE_SIGN + 2
+};
+
+void cabac_init_contexts(Ctx* ctx, int init_type, int slice_qp);
+
+extern const uint8_t g_cabac_lps[64][4];
+extern const uint8_t g_cabac_next_mps[64];
+extern const uint8_t g_cabac_next_lps[64];
+extern const uint8_t g_cabac_renorm[32];
+
+struct Cabac {
+  const uint8_t* cur = nullptr;
+  const uint8_t* end = nullptr;
+  uint32_t range = 510;
+  uint32_t value = 0;
+  int bits_needed = 8;
+
+  void set_data(const uint8_t* p, const uint8_t* e) { cur = p; end = e; }
+  // 9.3.2.5 initialisation at the current byte position
+  void start() {
+    range = 510;
+    bits_needed = 8;
+    value = 0;
+    if (cur < end) { value = (uint32_t)(*cur++) << 8; bits_needed -= 8; }
+    if (cur < end) { value |= *cur++; bits_needed -= 8; }
+  }
+  inline int bin(Ctx& c) {
+    const uint32_t state = c >> 1;
+    uint32_t mps = c & 1;
+    const uint32_t lps = g_cabac_lps[state][(range >> 6) - 4];
+    range -= lps;
+    const uint32_t scaled = range << 7;
+    if (value < scaled) {
+      c = (Ctx)((g_cabac_next_mps[state] << 1) | mps);
+      if (scaled < (256u << 7)) {
+        range = scaled >> 6;
+        value <<= 1;
+        if (++bits_needed == 0) {
+          bits_needed = -8;
+          if (cur < end) value |= *cur++;
+        }
+      }
+      return (int)mps;
+    }
+    const int nb = g_cabac_renorm[lps >> 3];
+    value = (value - scaled) << nb;
+    range = lps << nb;
+    const int bit = (int)(mps ^ 1);
+    if (state == 0) mps ^= 1;
+    c = (Ctx)((g_cabac_next_lps[state] << 1) | mps);
+    bits_needed += nb;
+    if (bits_needed >= 0) {
+      if (cur < end) value |= (uint32_t)(*cur++) << bits_needed;
+      bits_needed -= 8;
+    }
+    return bit;
+  }
+  inline int bypass() {
+    value <<= 1;
+    if (++bits_needed >= 0) {
+      bits_needed = -8;
+      if (cur < end) value |= *cur++;
+    }
+    const uint32_t scaled = range << 7;
+    if (value >= scaled) { value -= scaled; return 1; }
+    return 0;
+  }
+  inline uint32_t bypass_bits(int n) {
+    uint32_t v = 0;
+    while (n-- > 0) v = (v << 1) | (uint32_t)bypass();
+    return v;
+  }
+  inline int terminate() {
+    range -= 2;
+    const uint32_t scaled = range << 7;
+    if (value >= scaled) return 1;
+    if (scaled < (256u << 7)) {
+      range = scaled >> 6;
+      value <<= 1;
+      if (++bits_needed == 0) {
+        bits_needed = -8;
+        if (cur < end) value |= *cur++;
+      }
+    }
+    return 0;
+  }
+};
+
+}  // namespace b265h

@@ -1,0 +1,96 @@
+// picture.h — one coded picture on the host side: the parse-time metadata the CABAC/syntax decoder
+// needs for context selection and prediction-mode derivation, and the WORK LISTS (include/b265.h
+// part A.2) that replace the reference's in-place reconstruction calls S1..S5.
+// Counterpart of the metadata arrays of the reference's de265_image (image.h:411-417); the pixel
+// planes themselves live in HBM (b265 surfaces) and never on the host until output.
+#pragma once
+#include <stdint.h>
+#include <memory>
+#include <vector>
+#include "../../../include/b265.h"
+#include "params.h"
+
+namespace b265h {
+
+enum PredMode : uint8_t { MODE_NONE = 0, MODE_INTRA = 1, MODE_INTER = 2, MODE_SKIP = 3 };
+
+struct SliceUnit {                 // one slice segment NAL of the picture
+  SliceHeader hdr;
+  std::shared_ptr<const Pps> pps;
+  std::vector<uint8_t> rbsp;       // de-escaped NAL payload (after the 2-byte NAL header)
+};
+
+struct Picture {
+  std::shared_ptr<const Sps> sps;
+  std::shared_ptr<const Pps> pps;  // PPS of the first slice
+  int width = 0, height = 0;
+  int poc = 0, nal_type = 0, temporal_id = 0;
+  int pic_output = 1;
+  int64_t pts = 0;
+  void* user_data = nullptr;
+  uint64_t decode_index = 0;       // position in decoding order
+
+  std::vector<SliceUnit> slice_units;
+
+  // ---- parse-time maps ----
+  int cb_w = 0, cb_h = 0;          // in min-CB units
+  int u_w = 0, u_h = 0;            // in 4x4 units
+  std::vector<uint8_t> ct_depth;   // per min-CB
+  std::vector<uint8_t> pred_mode;  // per min-CB (PredMode; MODE_NONE = not decoded)
+  std::vector<uint8_t> cu_flags;   // per min-CB: bit0 pcm, bit1 transquant bypass
+  std::vector<int8_t>  qp_y;       // per min-CB (-> b265_frame_job.qp_y)
+  std::vector<uint8_t> ipm;        // intra luma pred mode per 4x4 unit
+  std::vector<uint8_t> unit_info;  // per 4x4 unit, B265_UNIT_* (-> b265_frame_job.unit_info)
+  std::vector<int32_t> ctb_slice_addr;  // per CTB (raster): SliceAddrRS of the owning slice, -1 = not decoded
+  std::vector<b265_ctb> ctbs;      // per CTB (raster)
+
+  // ---- work lists ----
+  std::vector<b265_tu> tus;
+  std::vector<b265_coeff> coeffs;
+  std::vector<b265_pu> pus;
+  std::vector<b265_pcm> pcms;
+  std::vector<uint8_t> pcm_samples;
+  std::vector<b265_slice> slices;  // one per independent slice
+  std::vector<b265_sao> sao;       // per CTB (raster)
+  bool any_sao = false, any_deblock = false;
+  std::shared_ptr<b265_scaling> scaling;
+
+  // ---- reconstruction / output state ----
+  int surface = -1;                // HBM surface id
+  int error = 0;                   // de265_error of the parse (0 = ok)
+  uint8_t* host_plane[3] = {nullptr, nullptr, nullptr};  // output planes after D2H
+  int host_stride[3] = {0, 0, 0};
+  void* plane_user[3] = {nullptr, nullptr, nullptr};
+  bool planes_external = false;    // allocated through de265_image_allocation
+  double parse_seconds = 0;
+
+  void init_maps() {
+    const Sps& s = *sps;
+    width = s.width; height = s.height;
+    cb_w = s.min_cb_w; cb_h = s.min_cb_h;
+    u_w = width >> 2; u_h = height >> 2;
+    ct_depth.assign((size_t)cb_w * cb_h, 0);
+    pred_mode.assign((size_t)cb_w * cb_h, MODE_NONE);
+    cu_flags.assign((size_t)cb_w * cb_h, 0);
+    qp_y.assign((size_t)cb_w * cb_h, 0);
+    ipm.assign((size_t)u_w * u_h, 1);
+    unit_info.assign((size_t)u_w * u_h, 0);
+    ctb_slice_addr.assign((size_t)s.ctbs_w * s.ctbs_h, -1);
+    ctbs.assign((size_t)s.ctbs_w * s.ctbs_h, b265_ctb{0, 0, 0});
+    sao.assign((size_t)s.ctbs_w * s.ctbs_h, b265_sao{});
+    tus.clear(); coeffs.clear(); pus.clear(); pcms.clear(); pcm_samples.clear(); slices.clear();
+    tus.reserve((size_t)u_w * u_h / 4);
+    coeffs.reserve((size_t)width * height / 8);
+  }
+  void release_parse_state() {
+    std::vector<uint8_t>().swap(ct_depth);
+    std::vector<uint8_t>().swap(ipm);
+    slice_units.clear();
+  }
+};
+
+// Parses all slice segments of `pic` (CABAC + syntax) and fills its work lists.
+// Returns 0 or a de265_error value. Thread-safe across different pictures.
+int decode_picture_slices(Picture& pic);
+
+}  // namespace b265h

@@ -1,0 +1,64 @@
+"""Host parser (CABAC + syntax -> work lists) checked WITHOUT a GPU: the work lists of every picture of
+the golden enc265 streams are reconstructed by the C oracle (orc_reconstruct_frame / orc_deblock /
+orc_sao) and the per-plane MD5 must equal the reference decoder's (`dec265 -o`, committed in
+tests/golden/streams/*.md5.json by tools/make_streams.py).  This pins parser + oracle together
+against the unmodified reference at stream level."""
+import ctypes as C
+import hashlib, json, os
+import numpy as np
+import pytest
+from tests.helpers import GOLDEN, load_oracle
+from libde265_b200 import lib as L
+from libde265_b200.decoder import Decoder
+
+STREAMS = os.path.join(GOLDEN, "streams")
+
+
+def oracle_planes(job):
+    o = load_oracle()
+    w, h = job.width, job.height
+    planes = [np.zeros((h, w), np.uint8), np.zeros((h // 2, w // 2), np.uint8), np.zeros((h // 2, w // 2), np.uint8)]
+    pp = (C.c_void_p * 3)(*[p.ctypes.data for p in planes])
+    pitch = (C.c_int * 3)(w, w // 2, w // 2)
+    o.orc_reconstruct_frame(C.byref(job), pp, pitch, None)
+    if job.flags & L.FRAME_DEBLOCK:
+        o.orc_deblock(C.byref(job), pp, pitch)
+    if job.flags & L.FRAME_SAO:
+        outs = [np.zeros_like(p) for p in planes]
+        op = (C.c_void_p * 3)(*[p.ctypes.data for p in outs])
+        o.orc_sao(C.byref(job), pp, op, pitch)
+        planes = outs
+    return planes
+
+
+def parse_and_reconstruct(data, threads=0, max_frames=None):
+    dec = Decoder(parse_only=True, threads=threads)
+    md5s = []
+
+    def on_pic(img):
+        if max_frames is not None and len(md5s) >= max_frames:
+            return
+        job = dec.job_of(img)
+        md5s.append([hashlib.md5(p.tobytes()).hexdigest() for p in oracle_planes(job)])
+
+    dec.decode_stream(data, on_picture=on_pic)
+    dec.close()
+    return md5s
+
+
+@pytest.mark.parametrize("name,max_frames", [("tiny_416x240_q30", None), ("tiny_416x240_q20_bf", None),
+                                             ("odd_200x136_q26", None), ("cb64_320x192_q34", None),
+                                             ("c1_1080p_q32", 1)])
+def test_parser_matches_reference_md5(name, max_frames):
+    data = open(os.path.join(STREAMS, name + ".bin"), "rb").read()
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    got = parse_and_reconstruct(data, max_frames=max_frames)
+    n = len(gold["md5"]) if max_frames is None else max_frames
+    assert len(got) == n
+    for i in range(n):
+        assert got[i] == gold["md5"][i], "frame %d of %s" % (i, name)
+
+
+def test_parser_threads_same_result():
+    data = open(os.path.join(STREAMS, "tiny_416x240_q30.bin"), "rb").read()
+    assert parse_and_reconstruct(data, threads=0) == parse_and_reconstruct(data, threads=3)
