@@ -208,8 +208,8 @@ LIBDE265_API void b265_de265_set_device(int device);
 /* pictures submitted to the GPU per launch batch (default 8); larger batches raise kernel efficiency */
 LIBDE265_API void b265_de265_set_batch(de265_decoder_context*, int max_pictures);
 /* statistics: [0] pictures decoded [1] host parse seconds (summed over threads) [2] GPU seconds
- * [3] bytes H2D [4] bytes D2H [5] kernel launches */
-LIBDE265_API void b265_de265_get_stats(de265_decoder_context*, double out[6]);
+ * [3] bytes H2D [4] bytes D2H [5] kernel launches [6] GPU batches [7] seconds inside b265_submit_frames */
+LIBDE265_API void b265_de265_get_stats(de265_decoder_context*, double out[8]);
 
 /* Test/bench aid: decoders created while this is on only PARSE (CABAC + syntax -> work lists) and never
  * touch the GPU; returned images carry no pixels, their work lists are read with

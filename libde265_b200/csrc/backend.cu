@@ -86,6 +86,8 @@ void b265_destroy(b265_ctx* ctx) {
     if (s.used && s.base) cudaFree(s.base);
   if (ctx->flush_buf) cudaFree(ctx->flush_buf);
   if (ctx->d_stage.p) cudaFree(ctx->d_stage.p);
+  if (ctx->d_submit.p) cudaFree(ctx->d_submit.p);
+  if (ctx->h_submit.p) cudaFreeHost(ctx->h_submit.p);
   if (ctx->h_stage.p) cudaFreeHost(ctx->h_stage.p);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);

@@ -38,6 +38,7 @@ struct b265_ctx {
   size_t flush_bytes = 0;
   // staging for b265_submit_frames (reused between calls)
   DevBuf d_stage, h_stage;
+  DevBuf d_submit, h_submit;   // grow-only staging of b265_submit_frames
   b265_batch* submit_batch = nullptr;
 };
 

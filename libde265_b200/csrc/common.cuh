@@ -34,6 +34,12 @@ __device__ __forceinline__ uint8_t ld_acquire_u8(const uint8_t* p) {
   asm volatile("ld.acquire.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return (uint8_t)v;
 }
+__device__ __forceinline__ uint8_t ld_relaxed_u8(const uint8_t* p) {
+  unsigned v;
+  asm volatile("ld.relaxed.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return (uint8_t)v;
+}
+__device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void st_release_u8(uint8_t* p, uint8_t v) {
   asm volatile("st.release.gpu.global.u8 [%0], %1;" ::"l"(p), "r"((unsigned)v) : "memory");
 }
@@ -58,8 +64,8 @@ struct FrameDev {
   const uint8_t* unit_info;   // may be NULL
   const int8_t* qp_y;         // may be NULL
   const b265_scaling* scaling;
-  uint8_t* done[3];           // intra wavefront completion flags, one byte per 4x4 samples of the plane
-  int done_pitch[3];
+  uint8_t* done[3];           // intra CTB-wavefront completion flags, one byte per CTB of the plane (raster)
+  int done_pitch[3];          // = ctbs_w
   uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal
   uint32_t* motion;           // per 4x4 luma unit: 4 words {ref ids, mv0, mv1, flags} rasterised from PUs
   const uint8_t* ref_plane[16][3];
@@ -67,9 +73,12 @@ struct FrameDev {
   int n_refs;
 };
 
-// one ticket of the intra wavefront: `count` (<= 32/N) TBs of size 2^log2 and equal wave, order[first..]
-struct TuGroup {
-  uint32_t first;
-  uint16_t count;
-  uint16_t log2;
+// one ticket of the intra CTB wavefront: plane `plane` of CTB `ctb` (raster) of frame `frame`; the CTB's
+// TUs are tus[tu_first .. tu_first+tu_count) in decoding order (all planes interleaved)
+struct IntraTicket {
+  uint16_t frame;
+  uint16_t plane;
+  uint32_t ctb;
+  uint32_t tu_first;
+  uint32_t tu_count;
 };

@@ -1,9 +1,9 @@
 // frames.cu — frame-level C ABI: b265_upload_frames / b265_run_batch / b265_submit_frames.
 //
 // Host work per batch (cheap, linear in the number of TUs): split TUs into the inter-residual lists
-// (by size) and the intra wavefront list, derive each intra TB's wave from a per-4x4 wave map, counting
-// sort by (wave,size), cut into groups; pack every list of every frame into ONE pinned staging buffer
-// and ship it with ONE cudaMemcpyAsync.  Device work: see b265_run_batch.
+// (by size) and the intra CTB tickets (one per picture/CTB/plane holding intra TBs, counting-sorted by
+// the CTB anti-diagonal wave = ctbX + 2*ctbY); pack every list of every frame into ONE pinned staging
+// buffer and ship it with ONE cudaMemcpyAsync.  Device work: see b265_run_batch.
 #include <string.h>
 #include <algorithm>
 #include <vector>
@@ -20,12 +20,14 @@ struct b265_batch {
   FrameDev* d_frames = nullptr;
   uint32_t* d_mc_items = nullptr;     int n_mc = 0;
   uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};
-  uint32_t* d_intra_order = nullptr;  int n_intra = 0;
-  TuGroup* d_groups = nullptr;        int n_groups = 0;
+  IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
   unsigned* d_ticket = nullptr;
-  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // done maps (+ bs) cleared per run
+  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // bs maps cleared per run
+  uint8_t* d_done_init = nullptr;     uint8_t* d_done = nullptr;  size_t done_bytes = 0;  // CTB flags: init -> live per run
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
   int max_wave = 0;
+  int wave_width = 0;                 // largest number of tickets in one wave
+  bool pooled = false;                // dev/host belong to the context's grow-only staging (b265_submit_frames)
 };
 
 static inline size_t al(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -37,32 +39,11 @@ struct Packer {
 };
 }  // namespace
 
-// wave of an intra TB = 1 + max wave among the units that hold its reference samples
-static inline int tb_wave(std::vector<uint16_t>& map, int mw, int mh, int x, int y, int n) {
-  const int ux = x >> 2, uy = y >> 2, nu = n >> 2;
-  int w = 0;
-  if (ux > 0) {
-    const int y1 = std::min(mh, uy + 2 * nu);
-    for (int v = std::max(0, uy - 1); v < y1; v++) w = std::max<int>(w, map[v * mw + ux - 1]);
-  }
-  if (uy > 0) {
-    const int x1 = std::min(mw, ux + 2 * nu);
-    for (int u = ux; u < x1; u++) w = std::max<int>(w, map[(uy - 1) * mw + u]);
-  }
-  w += 1;
-  if (w > 65535) w = 65535;
-  // only the rim is ever looked at by later TBs
-  const int xr = std::min(mw, ux + nu) - 1, yb = std::min(mh, uy + nu) - 1;
-  for (int u = ux; u <= xr; u++) map[yb * mw + u] = (uint16_t)w;
-  for (int v = uy; v <= yb; v++) map[v * mw + xr] = (uint16_t)w;
-  return w;
-}
-
 extern "C" void b265_free_batch(b265_ctx* ctx, b265_batch* b) {
   (void)ctx;
   if (!b) return;
-  if (b->dev) cudaFree(b->dev);
-  if (b->host) cudaFreeHost(b->host);
+  if (b->dev && !b->pooled) cudaFree(b->dev);
+  if (b->host && !b->pooled) cudaFreeHost(b->host);
   delete b;
 }
 
@@ -70,60 +51,65 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   if (n_jobs > 255) return B265_ERR_INVALID_ARG;
   b->n_frames = n_jobs;
   b->frames.assign(n_jobs, FrameDev());
-  struct Key { uint32_t key; uint32_t item; };
+  struct Key { uint32_t wave; IntraTicket t; };
   std::vector<Key> intra;
   std::vector<uint32_t> res[4], mc;
-  std::vector<uint16_t> wmap_l, wmap_c;
+  std::vector<std::vector<uint8_t>> done_init(n_jobs);   // per frame: 3 planes x nctb, 1 = nothing to wait for
+  std::vector<uint32_t> ctb_first, ctb_count;
+  std::vector<uint8_t> ctb_has;
   int max_wave = 0;
-  // ---- pass 1: classify + waves ----
+  // ---- pass 1: classify; TUs arrive in decoding order, so the TUs of one CTB are contiguous ----
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
     if (J.bit_depth != 8 || J.chroma_format_idc > 1 || J.n_tus >= (1 << 24) || J.n_pus >= (1 << 24))
       return B265_ERR_UNSUPPORTED;
-    const int lw = (J.width + 3) >> 2, lh = (J.height + 3) >> 2;
-    const int cw = (((J.width + 1) >> 1) + 3) >> 2, ch = (((J.height + 1) >> 1) + 3) >> 2;
-    wmap_l.assign((size_t)lw * lh, 0);
-    wmap_c.assign((size_t)cw * ch, 0);
+    const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
+    const int nctb = cw_ * ch_;
+    ctb_first.assign(nctb, 0);
+    ctb_count.assign(nctb, 0);
+    ctb_has.assign(nctb, 0);
+    int cur = -1;
     for (int i = 0; i < J.n_tus; i++) {
       const b265_tu& t = J.tus[i];
       const int c = t.cidx_log2 & 3, lg = (t.cidx_log2 >> 2) & 7;
       if (lg < 2 || lg > 5 || c > 2) return B265_ERR_INVALID_ARG;
-      const uint32_t item = ((uint32_t)j << 24) | (uint32_t)i;
-      if (t.intra_mode != B265_INTRA_NONE) {
-        int w = (c == 0) ? tb_wave(wmap_l, lw, lh, t.x, t.y, 1 << lg)
-                : (c == 1) ? tb_wave(wmap_c, cw, ch, t.x, t.y, 1 << lg)
-                           : 0;
-        if (c == 2) {  // Cr mirrors the Cb TB decoded just before it at the same position
-          const int ux = std::min(cw, (t.x >> 2) + (1 << (lg - 2))) - 1, uy = std::min(ch, (t.y >> 2) + (1 << (lg - 2))) - 1;
-          w = wmap_c[uy * cw + ux];
-          if (w == 0) w = tb_wave(wmap_c, cw, ch, t.x, t.y, 1 << lg);
-        }
-        max_wave = std::max(max_wave, w);
-        intra.push_back({((uint32_t)w << 2) | (uint32_t)(lg - 2), item});
-      } else if (t.ncoeff > 0) {
-        res[lg - 2].push_back(item);
+      const int sh = (c && J.chroma_format_idc) ? 1 : 0;
+      const int bx = (t.x << sh) >> J.log2_ctb, by = (t.y << sh) >> J.log2_ctb;
+      if (bx >= cw_ || by >= ch_) return B265_ERR_INVALID_ARG;
+      const int ctb = by * cw_ + bx;
+      if (ctb != cur) {
+        if (ctb_count[ctb]) return B265_ERR_INVALID_ARG;  // TUs of a CTB must be contiguous (decoding order)
+        ctb_first[ctb] = (uint32_t)i;
+        cur = ctb;
       }
+      ctb_count[ctb]++;
+      if (t.intra_mode != B265_INTRA_NONE) ctb_has[ctb] |= (uint8_t)(1 << c);
+      else if (t.ncoeff > 0) res[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
+    }
+    done_init[j].assign((size_t)3 * nctb, 1);
+    for (int ctb = 0; ctb < nctb; ctb++) {
+      if (!ctb_has[ctb]) continue;
+      const uint32_t wave = (uint32_t)(ctb % cw_ + 2 * (ctb / cw_));
+      max_wave = std::max<int>(max_wave, (int)wave);
+      for (int c = 0; c < 3; c++)
+        if (ctb_has[ctb] & (1 << c)) {
+          done_init[j][(size_t)c * nctb + ctb] = 0;
+          intra.push_back({wave, {(uint16_t)j, (uint16_t)c, (uint32_t)ctb, ctb_first[ctb], ctb_count[ctb]}});
+        }
     }
     for (int i = 0; i < J.n_pus; i++) mc.push_back(((uint32_t)j << 24) | (uint32_t)i);
   }
   b->max_wave = max_wave;
-  // ---- counting sort of the intra TBs by (wave,size); stable => decoding order inside a key ----
-  std::vector<uint32_t> order(intra.size());
-  std::vector<TuGroup> groups;
+  // ---- counting sort of the tickets by wave (stable) ----
+  std::vector<IntraTicket> tickets(intra.size());
   {
-    std::vector<uint32_t> cnt((size_t)(max_wave + 1) * 4 + 1, 0);
-    for (auto& k : intra) cnt[k.key + 1]++;
+    std::vector<uint32_t> cnt((size_t)max_wave + 2, 0);
+    for (auto& k : intra) cnt[k.wave + 1]++;
+    for (size_t i = 1; i < cnt.size(); i++) b->wave_width = std::max<int>(b->wave_width, (int)cnt[i]);
     for (size_t i = 1; i < cnt.size(); i++) cnt[i] += cnt[i - 1];
-    std::vector<uint32_t> pos(cnt.begin(), cnt.end() - 1);
-    for (auto& k : intra) order[pos[k.key]++] = k.item;
-    for (size_t key = 0; key + 1 < cnt.size(); key++) {
-      const uint32_t lg = 2 + (key & 3), cap = 32u >> lg;
-      for (uint32_t s = cnt[key]; s < cnt[key + 1]; s += cap)
-        groups.push_back({s, (uint16_t)std::min(cap, cnt[key + 1] - s), (uint16_t)lg});
-    }
+    for (auto& k : intra) tickets[cnt[k.wave]++] = k.t;
   }
-  b->n_intra = (int)order.size();
-  b->n_groups = (int)groups.size();
+  b->n_tickets = (int)tickets.size();
   b->n_mc = (int)mc.size();
   for (int s = 0; s < 4; s++) b->n_res[s] = (int)res[s].size();
 
@@ -133,8 +119,10 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const size_t o_mc = P.take(4 * mc.size());
   size_t o_res[4];
   for (int s = 0; s < 4; s++) o_res[s] = P.take(4 * res[s].size());
-  const size_t o_order = P.take(4 * order.size());
-  const size_t o_groups = P.take(sizeof(TuGroup) * groups.size());
+  const size_t o_tickets = P.take(sizeof(IntraTicket) * tickets.size());
+  size_t done_total = 0;
+  for (int j = 0; j < n_jobs; j++) done_total += done_init[j].size();
+  const size_t o_done_init = P.take(done_total);
   struct FOff { size_t tus, coeffs, pus, slices, ctbs, sao, unit, qp, scaling, pcms, pcm_samples; };
   std::vector<FOff> fo(n_jobs);
   for (int j = 0; j < n_jobs; j++) {
@@ -155,20 +143,25 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   b->upload_bytes = P.off;
   // device-only scratch after the uploaded part
   const size_t o_ticket = P.take(256);
+  const size_t o_done = P.take(done_total);
   const size_t o_zero = P.off;
   struct SOff { size_t done[3], bs, tmp[3], motion; int dp[3]; };
   std::vector<SOff> so(n_jobs);
-  for (int j = 0; j < n_jobs; j++) {
-    const b265_frame_job& J = jobs[j];
-    const int cw = (J.width + 1) >> 1, ch = (J.height + 1) >> 1;
-    so[j].dp[0] = (J.width + 3) >> 2;
-    so[j].dp[1] = so[j].dp[2] = (cw + 3) >> 2;
-    so[j].done[0] = P.take((size_t)so[j].dp[0] * ((J.height + 3) >> 2));
-    so[j].done[1] = P.take((size_t)so[j].dp[1] * ((ch + 3) >> 2));
-    so[j].done[2] = P.take((size_t)so[j].dp[2] * ((ch + 3) >> 2));
-    so[j].bs = P.take((size_t)((J.width + 3) >> 2) * ((J.height + 3) >> 2));
+  {
+    size_t acc = 0;
+    for (int j = 0; j < n_jobs; j++) {
+      const b265_frame_job& J = jobs[j];
+      const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
+      for (int c = 0; c < 3; c++) {
+        so[j].dp[c] = cw_;
+        so[j].done[c] = o_done + acc;
+        acc += (size_t)cw_ * ch_;
+      }
+      so[j].bs = P.take((size_t)((J.width + 3) >> 2) * ((J.height + 3) >> 2));
+    }
   }
   b->zero_bytes = P.off - o_zero;
+  b->done_bytes = done_total;
   for (int j = 0; j < n_jobs; j++) {  // SAO needs the deblocked picture kept aside
     const b265_frame_job& J = jobs[j];
     so[j].tmp[0] = so[j].tmp[1] = so[j].tmp[2] = 0;
@@ -183,20 +176,33 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
   }
   b->dev_bytes = P.off;
-  CK(cudaMalloc((void**)&b->dev, b->dev_bytes));
-  CK(cudaMallocHost((void**)&b->host, b->upload_bytes));
+  if (b->pooled) {  // reuse the context's staging (the previous submission has been drained by the caller)
+    int r = devbuf_reserve(ctx, &ctx->d_submit, b->dev_bytes, false);
+    if (r) return r;
+    r = devbuf_reserve(ctx, &ctx->h_submit, b->upload_bytes, true);
+    if (r) return r;
+    b->dev = (uint8_t*)ctx->d_submit.p;
+    b->host = (uint8_t*)ctx->h_submit.p;
+  } else {
+    CK(cudaMalloc((void**)&b->dev, b->dev_bytes));
+    CK(cudaMallocHost((void**)&b->host, b->upload_bytes));
+  }
   uint8_t* H = b->host;
   uint8_t* D = b->dev;
   auto cp = [&](size_t off, const void* src, size_t bytes) { if (bytes && src) memcpy(H + off, src, bytes); };
   cp(o_mc, mc.data(), 4 * mc.size());
   for (int s = 0; s < 4; s++) cp(o_res[s], res[s].data(), 4 * res[s].size());
-  cp(o_order, order.data(), 4 * order.size());
-  cp(o_groups, groups.data(), sizeof(TuGroup) * groups.size());
+  cp(o_tickets, tickets.data(), sizeof(IntraTicket) * tickets.size());
+  {
+    size_t acc = 0;
+    for (int j = 0; j < n_jobs; j++) { cp(o_done_init + acc, done_init[j].data(), done_init[j].size()); acc += done_init[j].size(); }
+  }
   b->d_frames = (FrameDev*)(D + o_frames);
   b->d_mc_items = (uint32_t*)(D + o_mc);
   for (int s = 0; s < 4; s++) b->d_res_order[s] = (uint32_t*)(D + o_res[s]);
-  b->d_intra_order = (uint32_t*)(D + o_order);
-  b->d_groups = (TuGroup*)(D + o_groups);
+  b->d_tickets = (IntraTicket*)(D + o_tickets);
+  b->d_done_init = D + o_done_init;
+  b->d_done = D + o_done;
   b->d_ticket = (unsigned*)(D + o_ticket);
   b->d_zero_begin = D + o_zero;
   static const b265_slice default_slice = {0, 2, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, {}, {}};
@@ -269,6 +275,7 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   const bool tm = ctx->stage_timing;
   if (tm) cudaEventRecord(ctx->stage_ev[0], st);
   if (b->zero_bytes) CK(cudaMemsetAsync(b->d_zero_begin, 0, b->zero_bytes, st));
+  if (b->done_bytes) CK(cudaMemcpyAsync(b->d_done, b->d_done_init, b->done_bytes, cudaMemcpyDeviceToDevice, st));
   if (b->n_mc) {
     launch_mc(st, b->d_frames, b->d_mc_items, b->n_mc, ctx->sm_count);
     ctx->launches++;
@@ -282,10 +289,10 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
       CK_LAUNCH("k_residual_sparse");
     }
   if (tm) cudaEventRecord(ctx->stage_ev[2], st);
-  if (b->n_groups) {
+  if (b->n_tickets) {
     static int max_ctas = 0;
     if (!max_ctas) max_ctas = intra_max_resident_ctas(ctx->sm_count);
-    launch_intra(st, b->d_frames, b->d_intra_order, b->d_groups, b->n_groups, b->d_ticket, max_ctas);
+    launch_intra(st, b->d_frames, b->d_tickets, b->n_tickets, b->d_ticket, max_ctas, b->wave_width);
     ctx->launches++;
     CK_LAUNCH("k_intra_wavefront");
   }
@@ -330,6 +337,7 @@ int b265_submit_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs) {
     ctx->submit_batch = nullptr;
   }
   b265_batch* b = new b265_batch();
+  b->pooled = true;
   int r = build_batch(ctx, jobs, n_jobs, b);
   if (r) { b265_free_batch(ctx, b); return r; }
   ctx->submit_batch = b;

@@ -28,7 +28,8 @@ using namespace b265h;
 
 struct de265_image {
   Picture pic;
-  enum State { ASSEMBLING, QUEUED, PARSED, DONE } state = ASSEMBLING;
+  enum State { ASSEMBLING, QUEUED, PARSED, TAKEN, DONE } state = ASSEMBLING;
+  double parsed_at = 0;
   int conf_x[3] = {0, 0, 0}, conf_y[3] = {0, 0, 0}, conf_w[3] = {0, 0, 0}, conf_h[3] = {0, 0, 0};
   size_t host_bytes = 0;
   uint8_t* host_base = nullptr;
@@ -52,7 +53,8 @@ struct NalIn {
 };
 
 struct Decoder {
-  b265_ctx* gpu = nullptr;
+  std::vector<b265_ctx*> gpus;   // one CUDA context (own stream + staging) per reconstruction thread
+  b265_ctx* gpu = nullptr;       // gpus[0]
   int gpu_status = 0;
   // ---- input ----
   std::vector<uint8_t> inbuf;
@@ -74,11 +76,13 @@ struct Decoder {
   std::deque<de265_image*> parse_queue;
   std::deque<std::unique_ptr<de265_image>> inflight;  // decoding order; front = oldest not yet reconstructed
   std::vector<std::thread> workers;
-  std::thread recon_thread;
+  std::vector<std::thread> recon_threads;
+  bool draining = false;         // the API thread waits for the pipeline to empty: do not hold back partial batches
+  double batch_wait_s = 0.004;
   bool stop = false;
   bool parse_only = false;
   int n_threads = 0;
-  int max_batch = 8;
+  int max_batch = 16;
   // ---- output ----
   std::deque<std::unique_ptr<de265_image>> reorder;  // reconstructed, waiting for output order
   std::deque<std::unique_ptr<de265_image>> output;
@@ -93,7 +97,8 @@ struct Decoder {
   void* alloc_user = nullptr;
   // ---- stats ----
   double stat_parse_s = 0, stat_gpu_s = 0, stat_h2d = 0, stat_d2h = 0;
-  uint64_t stat_pictures = 0;
+  uint64_t stat_pictures = 0, stat_batches = 0;
+  double stat_submit_s = 0;  // part of stat_gpu_s spent inside b265_submit_frames (host list building + enqueue)
 
   Decoder() {
     int dev = g_device;
@@ -102,8 +107,19 @@ struct Decoder {
       dev = e ? atoi(e) : 0;
     }
     parse_only = g_parse_only;
-    if (!parse_only) gpu_status = b265_create(dev, &gpu);
-    recon_thread = std::thread([this] { recon_loop(); });
+    int n_ctx = 2;
+    if (const char* e = getenv("B265_RECON_CONTEXTS")) n_ctx = std::max(1, std::min(4, atoi(e)));
+    if (parse_only) n_ctx = 1;
+    for (int i = 0; i < n_ctx; i++) {
+      b265_ctx* c = nullptr;
+      if (!parse_only) {
+        int st = b265_create(dev, &c);
+        if (st != B265_OK) { gpu_status = st; c = nullptr; }
+      }
+      gpus.push_back(c);
+    }
+    gpu = gpus[0];
+    for (int i = 0; i < n_ctx; i++) recon_threads.emplace_back([this, i] { recon_loop(i); });
   }
   ~Decoder() {
     {
@@ -113,14 +129,14 @@ struct Decoder {
     cv_parse.notify_all();
     cv_recon.notify_all();
     for (auto& t : workers) t.join();
-    if (recon_thread.joinable()) recon_thread.join();
+    for (auto& t : recon_threads) t.join();
     auto drop = [this](std::unique_ptr<de265_image>& i) { if (i) release_image(*i); };
     for (auto& i : inflight) drop(i);
     for (auto& i : reorder) drop(i);
     for (auto& i : output) drop(i);
     drop(last_returned);
     for (auto& p : host_pool) { if (gpu) b265_host_free(gpu, p.second); }
-    if (gpu) b265_destroy(gpu);
+    for (b265_ctx* c : gpus) if (c) b265_destroy(c);
   }
 
   void warn(int w) {
@@ -181,6 +197,7 @@ struct Decoder {
       {
         std::lock_guard<std::mutex> l(mu);
         img->state = de265_image::PARSED;
+        img->parsed_at = now_s();
         stat_parse_s += img->pic.parse_seconds;
       }
       cv_recon.notify_all();
@@ -204,6 +221,7 @@ struct Decoder {
       parse_one(img);
       std::lock_guard<std::mutex> l(mu);
       img->state = de265_image::PARSED;
+      img->parsed_at = now_s();
       stat_parse_s += img->pic.parse_seconds;
       cv_recon.notify_all();
     } else {
@@ -284,28 +302,51 @@ struct Decoder {
     return true;
   }
 
-  // ---- reconstruction thread: batches of parsed pictures -> GPU -> host planes -> reorder/output ----
-  void recon_loop() {
+  // ---- reconstruction threads (one per CUDA context/stream): batches of consecutive parsed pictures ->
+  //      GPU -> host planes; pictures retire to the reorder buffer strictly in decoding order ----
+  // A batch is taken when it is full, when the API thread is draining (end of stream / reset / back
+  // pressure), or when the oldest parsed picture has waited longer than `batch_wait_s`: the intra
+  // wavefront kernel is latency-bound, so reconstructing a few pictures costs as much as a full batch.
+  void recon_loop(int ci) {
+    b265_ctx* gpu = gpus[ci];
     std::vector<de265_image*> batch;
     std::vector<b265_frame_job> jobs;
     for (;;) {
       batch.clear();
       {
         std::unique_lock<std::mutex> l(mu);
-        cv_recon.wait(l, [this] {
-          return stop || (!inflight.empty() && inflight.front()->state == de265_image::PARSED);
-        });
-        if (stop) return;
-        for (auto& up : inflight) {
-          if (up->state != de265_image::PARSED || (int)batch.size() >= max_batch) break;
-          if (!batch.empty() && (up->pic.width != batch[0]->pic.width || up->pic.height != batch[0]->pic.height)) break;
-          batch.push_back(up.get());
+        for (;;) {
+          if (stop) return;
+          // first picture not yet taken by a recon thread
+          size_t first = 0;
+          while (first < inflight.size() && inflight[first]->state >= de265_image::TAKEN) first++;
+          size_t n = 0;
+          while (first + n < inflight.size() && (int)n < max_batch && inflight[first + n]->state == de265_image::PARSED &&
+                 inflight[first + n]->pic.width == inflight[first]->pic.width &&
+                 inflight[first + n]->pic.height == inflight[first]->pic.height)
+            n++;
+          const bool blocked = first + n < inflight.size() && inflight[first + n]->state == de265_image::PARSED;  // geometry change
+          bool take = n > 0 && ((int)n >= max_batch || draining || blocked || parse_only);
+          if (!take && n > 0) {
+            const double waited = now_s() - inflight[first]->parsed_at;
+            if (waited >= batch_wait_s) take = true;
+            else { cv_recon.wait_for(l, std::chrono::duration<double>(batch_wait_s - waited)); continue; }
+          }
+          if (take) {
+            for (size_t i = 0; i < n; i++) {
+              inflight[first + i]->state = de265_image::TAKEN;
+              batch.push_back(inflight[first + i].get());
+            }
+            break;
+          }
+          cv_recon.wait(l);
         }
       }
       const double t0 = now_s();
       jobs.resize(batch.size());
       std::vector<de265_image*> good;
       int njobs = 0;
+      double d2h = 0, h2d = 0, t_submit = 0;
       for (de265_image* img : batch) {
         Picture& p = img->pic;
         if (parse_only) continue;
@@ -321,19 +362,21 @@ struct Decoder {
         good.push_back(img);
       }
       if (njobs) {
+        const double ts0 = now_s();
         int r = b265_submit_frames(gpu, jobs.data(), njobs);
+        t_submit = now_s() - ts0;
         for (de265_image* img : good) {
           Picture& p = img->pic;
           if (r == B265_OK && prepare_output_planes(*img)) {
             const int np = p.sps->chroma_array_type ? 3 : 1;
             for (int c = 0; c < np && r == B265_OK; c++)
               r = b265_surface_download(gpu, p.surface, c, p.host_plane[c], p.host_stride[c], 0);
-            stat_d2h += (double)p.width * p.height * (np == 3 ? 1.5 : 1.0);
+            d2h += (double)p.width * p.height * (np == 3 ? 1.5 : 1.0);
           } else if (r == B265_OK) {
             p.error = DE265_ERROR_OUT_OF_MEMORY;
           }
-          stat_h2d += (double)(p.tus.size() * sizeof(b265_tu) + p.coeffs.size() * sizeof(b265_coeff) + p.unit_info.size() +
-                               p.qp_y.size() + p.sao.size() * sizeof(b265_sao) + p.ctbs.size() * sizeof(b265_ctb));
+          h2d += (double)(p.tus.size() * sizeof(b265_tu) + p.coeffs.size() * sizeof(b265_coeff) + p.unit_info.size() +
+                          p.qp_y.size() + p.sao.size() * sizeof(b265_sao) + p.ctbs.size() * sizeof(b265_ctb));
         }
         if (r == B265_OK) r = b265_sync(gpu);
         for (de265_image* img : good) {
@@ -345,21 +388,29 @@ struct Decoder {
       {
         std::lock_guard<std::mutex> l(mu);
         stat_gpu_s += now_s() - t0;
-        for (size_t i = 0; i < batch.size(); i++) {
+        stat_d2h += d2h;
+        stat_h2d += h2d;
+        stat_batches++;
+        stat_submit_s += t_submit;
+        for (de265_image* img : batch) {
+          img->state = de265_image::DONE;
+          if (!parse_only) {  // work lists are no longer needed
+            std::vector<b265_tu>().swap(img->pic.tus);
+            std::vector<b265_coeff>().swap(img->pic.coeffs);
+            std::vector<uint8_t>().swap(img->pic.unit_info);
+          }
+        }
+        // retire in decoding order
+        while (!inflight.empty() && inflight.front()->state == de265_image::DONE) {
           std::unique_ptr<de265_image> up = std::move(inflight.front());
           inflight.pop_front();
-          up->state = de265_image::DONE;
-          if (!parse_only) {  // work lists are no longer needed
-            std::vector<b265_tu>().swap(up->pic.tus);
-            std::vector<b265_coeff>().swap(up->pic.coeffs);
-            std::vector<uint8_t>().swap(up->pic.unit_info);
-          }
           stat_pictures++;
           if (up->pic.error && up->pic.error < 1000 && !fatal_error) fatal_error = up->pic.error;
           push_reorder(std::move(up));
         }
       }
       cv_done.notify_all();
+      cv_recon.notify_all();
     }
   }
 
@@ -585,7 +636,10 @@ struct Decoder {
       dispatch_current();
       {
         std::unique_lock<std::mutex> l(mu);
+        draining = true;
+        cv_recon.notify_all();
         cv_done.wait(l, [this] { return inflight.empty(); });
+        draining = false;
         flush_reorder();
         if (more) *more = !output.empty();
         if (fatal_error) {
@@ -608,7 +662,7 @@ struct Decoder {
         if (more) *more = 1;
         return DE265_ERROR_IMAGE_BUFFER_FULL;
       }
-      const size_t limit = (size_t)(2 * max_batch + 2 * n_threads + 2);
+      const size_t limit = (size_t)((gpus.size() + 1) * max_batch + 2 * n_threads + 2);
       cv_done.wait(l, [&] { return inflight.size() < limit; });
     }
     NalIn nal = std::move(nals.front());
@@ -749,7 +803,10 @@ LIBDE265_API void de265_reset(de265_decoder_context* c) {
   Decoder* d = DEC(c);
   d->dispatch_current();
   std::unique_lock<std::mutex> l(d->mu);
+  d->draining = true;
+  d->cv_recon.notify_all();
   d->cv_done.wait(l, [d] { return d->inflight.empty(); });
+  d->draining = false;
   for (auto& i : d->reorder) d->release_locked(*i);
   for (auto& i : d->output) d->release_locked(*i);
   d->reorder.clear();
@@ -878,7 +935,7 @@ LIBDE265_API void b265_de265_set_batch(de265_decoder_context* c, int n) {
   std::lock_guard<std::mutex> l(d->mu);
   d->max_batch = n < 1 ? 1 : (n > 64 ? 64 : n);
 }
-LIBDE265_API void b265_de265_get_stats(de265_decoder_context* c, double out[6]) {
+LIBDE265_API void b265_de265_get_stats(de265_decoder_context* c, double out[8]) {
   Decoder* d = DEC(c);
   std::lock_guard<std::mutex> l(d->mu);
   out[0] = (double)d->stat_pictures;
@@ -886,7 +943,10 @@ LIBDE265_API void b265_de265_get_stats(de265_decoder_context* c, double out[6]) 
   out[2] = d->stat_gpu_s;
   out[3] = d->stat_h2d;
   out[4] = d->stat_d2h;
-  out[5] = d->gpu ? (double)b265_launch_count(d->gpu) : 0;
+  out[6] = (double)d->stat_batches;
+  out[7] = d->stat_submit_s;
+  out[5] = 0;
+  for (b265_ctx* g : d->gpus) if (g) out[5] += (double)b265_launch_count(g);
 }
 
 }  // extern "C"

@@ -6,9 +6,9 @@
 // and DC (:1036-1069).  Border convention as in the reference: p[0] = top-left corner,
 // p[1..2N] = top row then top-right, p[-1..-2N] = left column then bottom-left.
 //
-// Neighbouring samples are produced by other warps of the SAME launch (TU-dependency wavefront):
-// every 4x4 unit on the right/bottom rim of a finished TB gets a release-store in FrameDev::done,
-// and a consumer spins with acquire-loads before reading the pixels through L2 (ld.cg).
+// Neighbouring samples are produced either by the same warp (earlier TBs of the same CTB) or by
+// other warps of the SAME launch (CTB wavefront, k_intra.cu): the warp waits for the neighbouring
+// CTBs' completion flags once per CTB and then reads all border pixels through L2 (ld.cg).
 #pragma once
 #include "common.cuh"
 
@@ -52,20 +52,6 @@ __device__ __forceinline__ bool unit_available(const FrameDev& f, const IntraGeo
   return true;
 }
 
-// block until the unit containing component sample (cx,cy) of plane c has been reconstructed
-__device__ __forceinline__ void wait_unit(const FrameDev& f, int c, int sh, int cx, int cy) {
-  if (f.unit_info) {
-    const uint8_t ui = f.unit_info[((cy << sh) >> 2) * (f.width >> 2) + ((cx << sh) >> 2)];
-    if (!(ui & B265_UNIT_INTRA) || (ui & B265_UNIT_DONE)) return;  // produced by an earlier launch
-  }
-  const uint8_t* flag = f.done[c] + (cy >> 2) * f.done_pitch[c] + (cx >> 2);
-  unsigned ns = 8;
-  while (ld_acquire_u8(flag) == 0) {
-    __nanosleep(ns);
-    if (ns < 256) ns <<= 1;
-  }
-}
-
 // Gather p[-2N..2N] of the TB at component position (xB,yB) of plane c into buf[i + 2N].
 // Returns nothing; all lanes of the warp call it (ballots). `active` false for idle groups.
 template <int LOG2>
@@ -95,7 +81,6 @@ __device__ __forceinline__ void gather_border(const FrameDev& f, int c, int xB, 
 
   uint32_t px = 0;
   if (av) {
-    wait_unit(f, c, sh, ux, uy);
     if (is_left) {
 #pragma unroll
       for (int i = 0; i < 4; i++)  // border index -2N+4*sub+i  <->  row uy-(3-i)... ascending index = going up
@@ -109,7 +94,6 @@ __device__ __forceinline__ void gather_border(const FrameDev& f, int c, int xB, 
   }
   uint32_t pc = 0;
   if (avc) {
-    wait_unit(f, c, sh, xB - 1, yB - 1);
     pc = ld_cg_u8(plane + (size_t)(yB - 1) * pitch + xB - 1);
   }
   // scan-order availability mask of this group: bits 0..2NU-1 left, bit 2NU corner, then top

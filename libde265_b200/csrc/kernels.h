@@ -10,8 +10,8 @@ void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, c
                             int n, int sm_count);
 void launch_mc(cudaStream_t st, const FrameDev* frames, const uint32_t* items, int n, int sm_count);
 int intra_max_resident_ctas(int sm_count);
-void launch_intra(cudaStream_t st, const FrameDev* frames, const uint32_t* order, const TuGroup* groups, int n_groups,
-                  unsigned* ticket, int max_ctas);
+void launch_intra(cudaStream_t st, const FrameDev* frames, const IntraTicket* tickets, int n_tickets,
+                  unsigned* ticket, int max_ctas, int wave_width);
 struct b265_ctx;
 // bS derivation + deblock V/H + SAO for every frame of a batch (k_postfilter.cu); ev (optional) is
 // recorded between deblocking and SAO for stage timing.

@@ -58,7 +58,7 @@ def _bind():
     lib.b265_de265_set_parse_only.restype = None
     lib.b265_de265_set_batch.argtypes = [vp, i32]
     lib.b265_de265_set_batch.restype = None
-    lib.b265_de265_get_stats.argtypes = [vp, C.POINTER(C.c_double * 6)]
+    lib.b265_de265_get_stats.argtypes = [vp, C.POINTER(C.c_double * 8)]
     lib.b265_de265_get_stats.restype = None
     lib.b265_de265_image_job.argtypes = [vp, vp, C.POINTER(L.FrameJob)]
     lib.b265_de265_image_poc.argtypes = [vp]
@@ -138,15 +138,15 @@ class Decoder:
             return True
 
         more = C.c_int(1)
-        while pos < len(mv) or True:
+        finished = False
+        while not finished:
             if pos < len(mv):
                 n = min(chunk, len(mv) - pos)
                 buf = (C.c_uint8 * n).from_buffer_copy(mv[pos:pos + n])
                 lib.de265_push_data(h, buf, n, pos, None)
                 pos += n
-                if pos >= len(mv):
-                    lib.de265_flush_data(h)
-            finished = False
+            if pos >= len(mv):
+                lib.de265_flush_data(h)
             while True:
                 err = lib.de265_decode(h, C.byref(more))
                 got = drain_one()
@@ -161,8 +161,6 @@ class Decoder:
                 if not more.value and not got:
                     finished = pos >= len(mv)
                     break
-            if finished:
-                break
         while drain_one():
             pass
         return out
@@ -176,7 +174,7 @@ class Decoder:
         return J
 
     def stats(self):
-        s = (C.c_double * 6)()
+        s = (C.c_double * 8)()
         self.lib.b265_de265_get_stats(self.h, C.byref(s))
         return {"pictures": int(s[0]), "parse_s": s[1], "gpu_s": s[2], "h2d_bytes": s[3], "d2h_bytes": s[4],
-                "launches": int(s[5])}
+                "launches": int(s[5]), "batches": int(s[6]), "submit_s": s[7]}
