@@ -1,17 +1,293 @@
-"""Workloads behind bench.py.
+"""Workloads behind bench.py (DESIGN.md §Measurement).
 
-idct_sweep  (BASELINE.json configs[1]): synthetic TU coefficient sweep — DST 4x4 and DCT 4/8/16/32,
-            random QP, dequant + inverse transform + add, dense-input form (4*nT^2 B per block).
+stream_4k     (default; BASELINE.json configs[3]) 3840x2160 enc265 intra stream with deblocking switched on
+              (PPS re-written), full GPU reconstruction.  value = frames/s of the reconstruction kernels with the
+              work lists resident in HBM; e2e = frames/s through the libde265 C API (host bitstream in, host
+              pictures out: CABAC parsing on the host cores, H2D of work lists, kernels, D2H of pictures).
+stream_1080p  (configs[0]) the 1080p intra stream, same measurement.
+idct_sweep    (configs[1]) synthetic TU coefficient sweep, dense-input form (4*nT^2 B per block).
+
+The reference arm / cpu_baseline is the unmodified reference decoder `oracle/_ref/dec265` (SSE path) run as
+min(cores, 16) concurrent processes on the same stream (enc265 streams have no WPP/tiles, so the
+reference parallelises only across streams).
 """
 import ctypes as C
-import json, os, sys, time
+import json, os, subprocess, sys, tempfile, time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+STREAMS = os.path.join(ROOT, "tests", "golden", "streams")
+REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 
 SWEEP = [("DST4", 1, 2), ("DCT4", 0, 2), ("DCT8", 0, 3), ("DCT16", 0, 4), ("DCT32", 0, 5)]
+STREAM_WL = {
+    # name: (golden stream, deblocking patched on, loops of the stream per step, kernel batch, description)
+    "stream_4k": ("c4_2160p_q32", True, 8, 32, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
+                  "deblocking enabled by PPS re-write (SAO cannot be enabled in an enc265 stream)"),
+    "stream_1080p": ("c1_1080p_q32", False, 16, 64, "1920x1080 8-bit 4:2:0 enc265 intra stream (16 unique frames, qp 32)"),
+}
 
 
+def _barrier_max(world, value):
+    if world == 1:
+        return value
+    import torch, torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def _all_sum(world, value):
+    if world == 1:
+        return value
+    import torch, torch.distributed as dist
+    t = torch.tensor([value], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return float(t.item())
+
+
+def _stream_bytes(name, patched):
+    data = open(os.path.join(STREAMS, name + ".bin"), "rb").read()
+    if patched:
+        from tools.pps_patch import patch_stream
+        data = patch_stream(data)
+    return data
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# =====================================================================================================
+# reference decoder on the host cores
+# =====================================================================================================
+def run_dec265(data, procs, loops, scalar=False):
+    """`procs` concurrent dec265 processes, each decoding `data` repeated `loops` times.
+    Returns (frames_total, seconds) or None when oracle/_ref/dec265 is not available."""
+    exe = os.path.join(REF_DIR, "dec265")
+    if not os.path.exists(exe):
+        return None
+    with tempfile.TemporaryDirectory() as td:
+        f = os.path.join(td, "in.bin")
+        with open(f, "wb") as fh:
+            for _ in range(loops):
+                fh.write(data)
+        cmd = [exe, "-q"] + (["-0"] if scalar else []) + [f]
+        # warm the page cache / loader
+        subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        t0 = time.perf_counter()
+        ps = [subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for _ in range(procs)]
+        frames = 0
+        for p in ps:
+            out = p.communicate()[0]
+            for line in out.splitlines():
+                if line.startswith("nFrames decoded:"):
+                    frames += int(line.split(":")[1].split()[0])
+        dt = time.perf_counter() - t0
+    return frames, dt
+
+
+def cpu_baseline_stream(wl, budget_s=20.0):
+    name, patched, loops, _, desc = STREAM_WL[wl]
+    data = _stream_bytes(name, patched)
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    procs = min(host_cores(), 16)
+    one = run_dec265(data, 1, 1)
+    if one is None:
+        return cpu_port_stream(wl)
+    fps1 = one[0] / one[1]
+    # size the sample: every process decodes the stream `reps` times, about budget_s/2 seconds
+    reps = max(1, int(budget_s / 2 * fps1 / gold["frames"]))
+    frames, dt = run_dec265(data, procs, reps)
+    return {"value": frames / dt, "unit": "frames/s", "cores": procs, "kind": "reference",
+            "sample": "%d concurrent `dec265 -q` (SSE4.1 build of the unmodified reference) x %d frames each of the same "
+                      "stream; 1 process alone: %.1f frames/s" % (procs, reps * gold["frames"], fps1),
+            "single_process_fps": fps1}
+
+
+def cpu_port_stream(wl):
+    """Fallback when the compiled reference did not travel: host parser + C oracle reconstruction, 1 thread."""
+    from benchmarks.jobs import stream_jobs
+    from tests.test_parser_streams import oracle_planes
+    name, patched, _, _, _ = STREAM_WL[wl]
+    jobs = stream_jobs(_stream_bytes(name, patched), threads=1, max_frames=2)
+    t0 = time.perf_counter()
+    for oj in jobs:
+        oracle_planes(oj.job)
+    dt = time.perf_counter() - t0
+    return {"value": len(jobs) / dt, "unit": "frames/s", "cores": 1, "kind": "port",
+            "sample": "%d frames reconstructed by the C oracle from the parser's work lists (parse time excluded)" % len(jobs)}
+
+
+# =====================================================================================================
+# our arm: stream workloads
+# =====================================================================================================
+def _job_algorithmic_bytes(J):
+    """intra (fused with residual add) writes 1.5*W*H and reads 4 B per non-zero coefficient;
+    deblocking run as two passes reads+writes the picture twice (4P)."""
+    P = J.width * J.height * 3 // 2
+    from libde265_b200 import lib as L
+    intra = P + 4 * J.n_coeffs
+    dbk = 4 * P if (J.flags & L.FRAME_DEBLOCK) else 0
+    return intra, dbk
+
+
+def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
+    from libde265_b200 import lib as L
+    from libde265_b200.decoder import Decoder
+    from benchmarks.jobs import stream_jobs
+    name, patched, loops, kbatch, desc = STREAM_WL[wl]
+    data = _stream_bytes(name, patched)
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    W, H, nuniq = gold["width"], gold["height"], gold["frames"]
+    cores = host_cores()
+    threads = max(1, cores // world - 1)
+
+    # ---------------- kernels with work lists resident in HBM ----------------
+    ctx = L.Context(local)
+    uniq = stream_jobs(data, threads=min(threads, 8))
+    jobs, sids = [], []
+    for i in range(kbatch):
+        oj = uniq[i % nuniq]
+        J = L.FrameJob()
+        C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
+        sid = ctx.surface_alloc(W, H)
+        J.dst_surface = sid
+        sids.append(sid)
+        jobs.append(J)
+    batch = ctx.upload_frames(jobs)
+    ctx.sync()
+    bytes_intra = sum(_job_algorithmic_bytes(J)[0] for J in jobs)
+    bytes_dbk = sum(_job_algorithmic_bytes(J)[1] for J in jobs)
+    for _ in range(a.warmup):
+        ctx.run_batch(batch)
+    ctx.sync()
+    # per-stage device time (CUDA events between the stages, on the context's stream)
+    ctx.lib.b265_set_stage_timing(ctx.h, 1)
+    st = []
+    for _ in range(3):
+        ctx.flush_l2()
+        ctx.run_batch(batch)
+        st.append(ctx.stage_times())
+    ctx.lib.b265_set_stage_timing(ctx.h, 0)
+    stage = [float(np.mean([s[i] for s in st])) for i in range(6)]
+    launches0 = ctx.launches
+    clocks = ClockSampler(local)
+    clocks.start()
+    if world > 1:
+        import torch, torch.distributed as dist
+        dist.barrier(); torch.cuda.synchronize()
+    ctx.sync()
+    ctx.timer_start()
+    for _ in range(a.steps):
+        ctx.run_batch(batch)
+    ms_total = ctx.timer_stop()
+    ms_total = _barrier_max(world, ms_total)
+    clk = clocks.stop()
+    launches = ctx.launches - launches0
+    ms_step = ms_total / a.steps
+    value = world * kbatch / ms_step * 1e3
+    ctx.free_batch(batch)
+    for s in sids:
+        ctx.surface_release(s)
+    ctx.close()
+
+    # ---------------- end to end through the libde265 C API (host bitstream -> host pictures) ----------------
+    step_data = data * loops
+    frames_step = nuniq * loops
+    dec = Decoder(device=local, threads=threads, batch=16)
+    count = [0]
+    cb = lambda img: count.__setitem__(0, count[0] + 1)
+    dec.decode_stream(step_data, chunk=1 << 20, on_picture=cb)      # warm-up: allocations, clocks
+    s0 = dec.stats()
+    count[0] = 0
+    if world > 1:
+        import torch, torch.distributed as dist
+        dist.barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        dec.lib.de265_reset(dec.h)
+        dec.decode_stream(step_data, chunk=1 << 20, on_picture=cb)
+    e2e_s = time.perf_counter() - t0
+    s1 = dec.stats()
+    dec.close()
+    assert count[0] == frames_step * a.steps, "decoder returned %d pictures, expected %d" % (count[0], frames_step * a.steps)
+    e2e_s = _barrier_max(world, e2e_s)
+    e2e_fps = world * frames_step * a.steps / e2e_s
+
+    peak, peak_src = measured_peaks()
+    intra_gbs = bytes_intra / stage[2] / 1e6 if stage[2] > 0 else 0.0
+    dbk_gbs = bytes_dbk / stage[3] / 1e6 if stage[3] > 0 and bytes_dbk else None
+    res = {
+        "metric": "decoded frames/s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
+        "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
+        "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": kbatch,
+                   "mpixel_per_s": value * W * H / 1e6,
+                   "value_is": "reconstruction kernels (intra wavefront + residual, deblock V/H) on a batch of %d pictures "
+                               "whose work lists are resident in HBM" % kbatch,
+                   "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
+                         % (kbatch * W * H * 3 // 2 >> 20),
+                   "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
+                             "2 CUDA contexts, batch 16; %d frames per step" % (threads, frames_step),
+                   "host_cores": cores, "stage_ms[pcm+mc,inter_res,intra,deblock,sao,total]": [round(x, 3) for x in stage]},
+        "e2e": {"value": e2e_fps, "unit": "frames/s",
+                "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
+                "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) / a.steps),
+                "mpixel_per_s": e2e_fps * W * H / 1e6,
+                "host_parse_core_seconds_per_step": (s1["parse_s"] - s0["parse_s"]) / a.steps},
+        "gpu_launches": int(launches), "clocks": clk,
+        "roofline": {"bound": "hbm", "kernel": "k_intra_wavefront", "achieved": intra_gbs, "peak": peak, "unit": "GB/s",
+                     "frac": intra_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "note": "dependency-latency bound (CTB anti-diagonal wavefront), not bandwidth bound; "
+                             "algorithmic bytes = 1.5*W*H written + 4 B per coefficient per picture",
+                     "per_kernel_gbs": {"k_intra_wavefront": round(intra_gbs, 1),
+                                        "deblock(bs+V+H luma/chroma, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None}},
+    }
+    if rank == 0 and world == 1:
+        res["cpu_baseline"] = cpu_baseline_stream(wl)
+    return res
+
+
+def run_reference_stream(a, wl):
+    name, patched, loops, _, desc = STREAM_WL[wl]
+    data = _stream_bytes(name, patched)
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    procs = min(host_cores(), 16)
+    one = run_dec265(data, 1, 1)
+    if one is None:
+        cb = cpu_port_stream(wl)
+        v = cb["value"]
+        ms = None
+    else:
+        fps1 = one[0] / one[1]
+        reps = max(1, int(6.0 * fps1 / gold["frames"]))       # ~6 s of CPU work per step
+        for _ in range(a.warmup):
+            run_dec265(data, procs, 1)
+        frames, secs = 0, 0.0
+        for _ in range(a.steps):
+            f, dt = run_dec265(data, procs, reps)
+            frames += f
+            secs += dt
+        v = frames / secs
+        ms = secs / a.steps * 1e3
+        cb = {"value": v, "unit": "frames/s", "cores": procs, "kind": "reference",
+              "sample": "%d concurrent `dec265 -q` processes (unmodified reference, SSE4.1 build) x %d frames each per step; "
+                        "1 process alone: %.1f frames/s" % (procs, reps * gold["frames"], fps1)}
+    return {"impl": "reference", "metric": "decoded frames/s", "value": v, "unit": "frames/s", "n_gpus": a.gpus,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
+            "config": {"workload": "%s: %s" % (wl, desc), "host_cores": host_cores()},
+            "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# =====================================================================================================
+# idct_sweep (configs[1])
+# =====================================================================================================
 def _sweep_inputs(log2, px_total, seed):
     """px_total pixels worth of blocks; a 2^21-pixel random set tiled (distinct addresses, so no cache reuse)."""
     from tests.helpers import make_coeff_blocks
@@ -27,25 +303,9 @@ def _sweep_inputs(log2, px_total, seed):
     return coeffs, qp, dst
 
 
-def _barrier_max(world, value):
-    if world == 1:
-        return value
-    import torch, torch.distributed as dist
-    t = torch.tensor([value], dtype=torch.float64, device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
-
-
-def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
+def run_sweep(a, rank, world, local, ClockSampler, measured_peaks):
     from libde265_b200 import lib as L
-    if world > 1:
-        import torch, torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl")
     ctx = L.Context(local)
-    wl = a.workload or "idct_sweep"
-    if wl != "idct_sweep":
-        raise SystemExit("unknown workload " + wl)
     px = 1 << 26  # pixels per transform kind per step (256 MiB algorithmic traffic per kind)
     kinds = []
     for name, kind, log2 in SWEEP:
@@ -53,9 +313,7 @@ def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
         n = coeffs.shape[0]
         d_c, d_q, d_d = ctx.dev_alloc(coeffs.nbytes), ctx.dev_alloc(qp.nbytes), ctx.dev_alloc(dst.nbytes)
         ctx.h2d(d_c, coeffs); ctx.h2d(d_q, qp); ctx.h2d(d_d, dst)
-        kinds.append(dict(name=name, kind=kind, log2=log2, n=n, d_c=d_c, d_q=d_q, d_d=d_d,
-                          host=(coeffs, qp, dst)))
-    bytes_per_step = sum(4 * (k["n"] << (2 * k["log2"])) for k in kinds)
+        kinds.append(dict(name=name, kind=kind, log2=log2, n=n, d_c=d_c, d_q=d_q, d_d=d_d, host=(coeffs, qp, dst)))
     px_per_step = sum(k["n"] << (2 * k["log2"]) for k in kinds)
 
     def step():
@@ -65,7 +323,6 @@ def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
     for _ in range(a.warmup):
         step()
     ctx.sync()
-    # per-kernel timing (flush L2 between launches; inputs are also > L2)
     per_kind = {}
     for k in kinds:
         ts = []
@@ -86,24 +343,18 @@ def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
     ctx.timer_start()
     for _ in range(a.steps):
         step()
-    ms_total = ctx.timer_stop()
-    ms_total = _barrier_max(world, ms_total)
+    ms_total = _barrier_max(world, ctx.timer_stop())
     clk = clocks.stop()
     launches = ctx.launches - launches0
     ms_step = ms_total / a.steps
-
-    # end to end through the C ABI with host buffers (H2D + kernel + D2H inside the call)
     e2e_px = 0
     t0 = time.perf_counter()
-    e2e_steps = 1
     for k in kinds:
         c, q, d = k["host"]
         m = min(k["n"], (1 << 24) >> (2 * k["log2"]))
         ctx.residual_batch(k["kind"], k["log2"], c[:m], d[:m].copy(), q[:m])
         e2e_px += m << (2 * k["log2"])
-    e2e_s = time.perf_counter() - t0
-    e2e_s = _barrier_max(world, e2e_s)
-
+    e2e_s = _barrier_max(world, time.perf_counter() - t0)
     peak, peak_src = measured_peaks()
     dom = max(per_kind.items(), key=lambda kv: kv[1]["ms"])
     res = {
@@ -124,11 +375,24 @@ def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
     return res
 
 
-def cpu_baseline_sweep(kinds, budget_s=15.0):
-    """C oracle ('port') timed single-threaded on a bounded sample of the same blocks."""
+def cpu_baseline_sweep(kinds):
+    """the reference's own scalar transform functions when oracle/_ref travelled, else the C oracle; 1 thread"""
     from tests import helpers
-    orc = helpers.load_oracle()
+    ref = helpers.load_ref()
     px, t = 0, 0.0
+    if ref is not None:
+        from tests.test_oracle_transform import ref_residual_batch
+        for k in kinds:
+            c, q, d = k["host"]
+            m = min(k["n"], (1 << 17) >> (2 * k["log2"]))
+            t0 = time.perf_counter()
+            ref_residual_batch(ref, k["kind"], k["log2"], c[:m], d[:m], q[:m])
+            t += time.perf_counter() - t0
+            px += m << (2 * k["log2"])
+        return {"value": px / t / 1e6, "unit": "Mpixel/s", "cores": 1, "kind": "reference",
+                "sample": "2^17 px per transform kind: dequant_coefficients + transform_*_add_8_fallback of the compiled "
+                          "reference called block by block through ctypes (call overhead included), 1 thread"}
+    orc = helpers.load_oracle()
     for k in kinds:
         c, q, d = k["host"]
         m = min(k["n"], (1 << 21) >> (2 * k["log2"]))
@@ -141,21 +405,46 @@ def cpu_baseline_sweep(kinds, budget_s=15.0):
             "sample": "2^21 px per transform kind of the same sweep, C oracle, 1 thread"}
 
 
-def run_reference(a):
-    """Reference arm: the reference's own scalar transform functions on the host cores."""
-    from tests import helpers
-    ref = helpers.load_ref()
+def run_reference_sweep(a):
     kinds = []
     for name, kind, log2 in SWEEP:
         coeffs, qp, dst = _sweep_inputs(log2, 1 << 21, seed=2 + log2 + 10 * kind)
         kinds.append(dict(name=name, kind=kind, log2=log2, n=coeffs.shape[0], host=(coeffs, qp, dst)))
-    if ref is None:
-        cb = cpu_baseline_sweep(kinds)
-    else:
-        from tests.test_oracle_transform import ref_residual_batch
-        cb = cpu_baseline_sweep(kinds)
+    cb = cpu_baseline_sweep(kinds)
     v = cb["value"]
     return {"impl": "reference", "metric": "dequant+inverse-transform+add throughput (config 2 sweep)", "value": v,
             "unit": "Mpixel/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "higher_is_better": True,
             "config": {"workload": "idct_sweep"}, "cpu_baseline": cb,
             "e2e": {"value": v, "unit": "Mpixel/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# =====================================================================================================
+# dispatch
+# =====================================================================================================
+DEFAULT_WORKLOAD = "stream_4k"
+
+
+def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
+    if world > 1:
+        import torch, torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl")
+    wl = a.workload or DEFAULT_WORKLOAD
+    if wl in STREAM_WL:
+        res = run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks)
+    elif wl == "idct_sweep":
+        res = run_sweep(a, rank, world, local, ClockSampler, measured_peaks)
+    else:
+        raise SystemExit("unknown workload " + wl)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return res
+
+
+def run_reference(a):
+    wl = a.workload or DEFAULT_WORKLOAD
+    if wl in STREAM_WL:
+        return run_reference_stream(a, wl)
+    return run_reference_sweep(a)

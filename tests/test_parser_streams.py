@@ -46,12 +46,26 @@ def parse_and_reconstruct(data, threads=0, max_frames=None):
     return md5s
 
 
+def load_stream(name):
+    """golden stream + reference MD5s; '<base>_lf' = the base stream with deblocking switched on by
+    re-writing its PPS (tools/pps_patch.py), MD5s from the reference decoder on the patched stream"""
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    if "base" in gold:
+        from tools.pps_patch import patch_stream
+        data = patch_stream(open(os.path.join(STREAMS, gold["base"] + ".bin"), "rb").read(),
+                            beta_div2=gold["beta_offset_div2"], tc_div2=gold["tc_offset_div2"])
+    else:
+        data = open(os.path.join(STREAMS, name + ".bin"), "rb").read()
+    return data, gold
+
+
 @pytest.mark.parametrize("name,max_frames", [("tiny_416x240_q30", None), ("tiny_416x240_q20_bf", None),
                                              ("odd_200x136_q26", None), ("cb64_320x192_q34", None),
-                                             ("c1_1080p_q32", 1)])
+                                             ("c1_1080p_q32", 1), ("tiny_416x240_q30_lf", None),
+                                             ("tiny_416x240_q20_bf_lf", None), ("odd_200x136_q26_lf", None),
+                                             ("cb64_320x192_q34_lf", None), ("c1_1080p_q32_lf", 1)])
 def test_parser_matches_reference_md5(name, max_frames):
-    data = open(os.path.join(STREAMS, name + ".bin"), "rb").read()
-    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    data, gold = load_stream(name)
     got = parse_and_reconstruct(data, max_frames=max_frames)
     n = len(gold["md5"]) if max_frames is None else max_frames
     assert len(got) == n
