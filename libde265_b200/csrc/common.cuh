@@ -64,6 +64,9 @@ struct FrameDev {
   const uint8_t* unit_info;   // may be NULL
   const int8_t* qp_y;         // may be NULL
   const b265_scaling* scaling;
+  const b265_pcm* pcms;       // PCM coding blocks (S4) and their samples (Y, Cb, Cr per block)
+  const uint8_t* pcm_samples;
+  int n_pcms;
   uint8_t* done[3];           // intra CTB-wavefront completion flags, one byte per CTB of the plane (raster)
   int done_pitch[3];          // = ctbs_w
   uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal

@@ -27,6 +27,7 @@ struct b265_batch {
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
   int max_wave = 0;
   int wave_width = 0;                 // largest number of tickets in one wave
+  int max_pcms = 0;                   // largest PCM block count of a picture
   bool pooled = false;                // dev/host belong to the context's grow-only staging (b265_submit_frames)
 };
 
@@ -250,6 +251,10 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.unit_info = J.unit_info ? D + fo[j].unit : nullptr;
     f.qp_y = J.qp_y ? (const int8_t*)(D + fo[j].qp) : nullptr;
     f.scaling = J.scaling ? (const b265_scaling*)(D + fo[j].scaling) : nullptr;
+    f.pcms = J.n_pcms ? (const b265_pcm*)(D + fo[j].pcms) : nullptr;
+    f.pcm_samples = J.n_pcm_samples ? D + fo[j].pcm_samples : nullptr;
+    f.n_pcms = J.n_pcms;
+    b->max_pcms = std::max(b->max_pcms, J.n_pcms);
     f.bs = D + so[j].bs;
     f.motion = so[j].motion ? (uint32_t*)(D + so[j].motion) : nullptr;
     f.n_refs = std::min(J.n_refs, 16);
@@ -276,6 +281,11 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   if (tm) cudaEventRecord(ctx->stage_ev[0], st);
   if (b->zero_bytes) CK(cudaMemsetAsync(b->d_zero_begin, 0, b->zero_bytes, st));
   if (b->done_bytes) CK(cudaMemcpyAsync(b->d_done, b->d_done_init, b->done_bytes, cudaMemcpyDeviceToDevice, st));
+  if (b->max_pcms) {
+    launch_pcm(st, b->d_frames, b->n_frames, b->max_pcms);
+    ctx->launches++;
+    CK_LAUNCH("k_pcm");
+  }
   if (b->n_mc) {
     launch_mc(st, b->d_frames, b->d_mc_items, b->n_mc, ctx->sm_count);
     ctx->launches++;

@@ -924,9 +924,9 @@ LIBDE265_API int de265_get_parameter_bool(de265_decoder_context* c, enum de265_p
 }
 
 LIBDE265_API void b265_de265_set_parse_only(int on) { g_parse_only = on != 0; }
-LIBDE265_API int b265_de265_image_job(de265_decoder_context* c, const struct de265_image* img, b265_frame_job* out) {
+LIBDE265_API int b265_de265_image_job(de265_decoder_context* c, const struct de265_image* img, void* out) {
   if (!c || !img || !out) return B265_ERR_INVALID_ARG;
-  DEC(c)->fill_job(*const_cast<de265_image*>(img), *out);
+  DEC(c)->fill_job(*const_cast<de265_image*>(img), *static_cast<b265_frame_job*>(out));
   return img->pic.error;
 }
 LIBDE265_API int b265_de265_image_poc(const struct de265_image* img) { return img->pic.poc; }

@@ -9,6 +9,13 @@ void launch_residual_dense(cudaStream_t st, int log2, int kind, int rdpcm, int n
 void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order,
                             int n, int sm_count);
 void launch_mc(cudaStream_t st, const FrameDev* frames, const uint32_t* items, int n, int sm_count);
+// PCM sample store (k_blocks.cu): grid (max_pcms, n_frames)
+void launch_pcm(cudaStream_t st, const FrameDev* frames, int n_frames, int max_pcms);
+// isolated-block kernels behind b265_intra_batch / b265_interp_batch (k_blocks.cu)
+void launch_intra_blocks(cudaStream_t st, int log2, int cidx, int n_blocks, const uint8_t* modes, const uint8_t* borders,
+                         int strong, int no_edge_filter, uint8_t* out);
+void launch_interp_blocks(cudaStream_t st, int luma, int n_blocks, int w, int h, const uint8_t* src, long long src_stride,
+                          long long src_block_stride, const uint8_t* frac_xy, int16_t* out);
 int intra_max_resident_ctas(int sm_count);
 void launch_intra(cudaStream_t st, const FrameDev* frames, const IntraTicket* tickets, int n_tickets,
                   unsigned* ticket, int max_ctas, int wave_width);

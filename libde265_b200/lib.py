@@ -244,6 +244,48 @@ class Context:
               "mc_batch")
         return dst
 
+    def residual_sparse(self, tus, coeffs, plane):
+        """tus: ctypes array of TU addressing `plane` (numpy uint8 2-D, modified in place); coeffs: ctypes array of Coeff."""
+        h, w = plane.shape
+        check(self.h, self.lib.b265_residual_sparse(self.h, MEM_HOST, C.byref(tus), len(tus),
+                                                    C.byref(coeffs) if len(coeffs) else None, len(coeffs),
+                                                    plane.ctypes.data, plane.strides[0], w, h), "residual_sparse")
+        return plane
+
+    def intra_batch(self, log2, cidx, modes, borders, strong=0, no_edge_filter=0):
+        """modes uint8 [n]; borders uint8 [n, 4*nT+1] (p[-2nT..2nT]); returns uint8 [n, nT, nT]."""
+        import numpy as np
+        n, nT = len(modes), 1 << log2
+        out = np.empty((n, nT, nT), dtype=np.uint8)
+        check(self.h, self.lib.b265_intra_batch(self.h, MEM_HOST, log2, cidx, n, modes.ctypes.data, borders.ctypes.data,
+                                                strong, no_edge_filter, out.ctypes.data), "intra_batch")
+        return out
+
+    def interp_batch(self, luma, w, h, buf, origin, stride, block_stride, n, frac_xy):
+        """buf: uint8 numpy holding n blocks with halo; block i's integer position is at flat offset
+        origin + i*block_stride (row stride `stride`); frac_xy uint8 [n, 2]. Returns int16 [n, h, w]."""
+        import numpy as np
+        out = np.empty((n, h, w), dtype=np.int16)
+        check(self.h, self.lib.b265_interp_batch(self.h, MEM_HOST, luma, n, w, h, buf.ctypes.data + origin, stride,
+                                                 block_stride, frac_xy.ctypes.data, out.ctypes.data), "interp_batch")
+        return out
+
+    def deblock_planes(self, job, planes):
+        """In-place deblocking of numpy planes (Y[,Cb,Cr]) with the metadata of FrameJob `job`."""
+        pp = (C.c_void_p * 3)(*([p.ctypes.data for p in planes] + [None] * (3 - len(planes))))
+        check(self.h, self.lib.b265_deblock_planes(self.h, MEM_HOST, C.byref(job), pp, planes[0].strides[0],
+                                                   planes[1].strides[0] if len(planes) > 1 else 0), "deblock_planes")
+        return planes
+
+    def sao_planes(self, job, in_planes):
+        import numpy as np
+        out = [np.zeros_like(p) for p in in_planes]
+        ip = (C.c_void_p * 3)(*([p.ctypes.data for p in in_planes] + [None] * (3 - len(in_planes))))
+        op = (C.c_void_p * 3)(*([p.ctypes.data for p in out] + [None] * (3 - len(out))))
+        check(self.h, self.lib.b265_sao_planes(self.h, MEM_HOST, C.byref(job), ip, op, in_planes[0].strides[0],
+                                               in_planes[1].strides[0] if len(in_planes) > 1 else 0), "sao_planes")
+        return out
+
     # -- surfaces + frame-level path ------------------------------------------------------------
     def surface_alloc(self, width, height, chroma=1):
         sid = C.c_int()

@@ -202,6 +202,18 @@ void orc_reconstruct_frame(const b265_frame_job* J, uint8_t* const* planes, cons
                            const uint8_t* const* ref_planes) {
   if (J->n_pus > 0)
     orc_mc_batch(J->pus, J->n_pus, J->slices, ref_planes, J->n_refs, planes, J->width, J->height, pitch[0], pitch[1]);
+  /* S4: PCM blocks (read_pcm_samples, slice.cc:4356-4406; samples are already at the bit depth) */
+  for (int i = 0; i < J->n_pcms; i++) {
+    const b265_pcm* p = &J->pcms[i];
+    const uint8_t* s = J->pcm_samples + p->sample_off;
+    int n = 1 << p->log2_size;
+    for (int y = 0; y < n; y++)
+      for (int x = 0; x < n; x++) planes[0][(size_t)(p->y + y) * pitch[0] + p->x + x] = *s++;
+    if (!J->chroma_format_idc) continue;
+    for (int c = 1; c < 3; c++)
+      for (int y = 0; y < n / 2; y++)
+        for (int x = 0; x < n / 2; x++) planes[c][(size_t)(p->y / 2 + y) * pitch[c] + p->x / 2 + x] = *s++;
+  }
   const b265_scaling* sl = (J->flags & B265_FRAME_SCALING_LIST) ? J->scaling : NULL;
   for (int i = 0; i < J->n_tus; i++) {
     const b265_tu* tu = &J->tus[i];

@@ -152,11 +152,12 @@ COEFF_DT = np.dtype([('level', '<i2'), ('pos', '<u2')])
 class SynthJob:
     """Holds the numpy buffers of one frame job alive and exposes the ctypes FrameJob."""
 
-    def __init__(self, rng, width, height, log2_ctb=5, deblock=True, sao=False, dense=0.6, flags=0):
+    def __init__(self, rng, width, height, log2_ctb=5, deblock=True, sao=False, dense=0.6, flags=0, pcm=0.0):
         from libde265_b200 import lib as L
         self.w, self.h, self.log2_ctb = width, height, log2_ctb
         self.rng = rng
         self.tus, self.coeffs = [], []
+        self.pcm_prob, self.pcms, self.pcm_samples = pcm, [], []
         self.ncoef = 0
         uw, uh = width // 4, height // 4
         self.unit = np.zeros((uh, uw), dtype=np.uint8)
@@ -205,6 +206,13 @@ class SynthJob:
         J.qp_y = L.as_ptr(self.qp, C.c_int8)
         if sao:
             J.sao = C.cast(self.sao, C.POINTER(L.SAO))
+        if self.pcms:
+            self.pcm_arr = (L.PCM * len(self.pcms))()
+            for i, (x, y, lg, off) in enumerate(self.pcms):
+                self.pcm_arr[i].x, self.pcm_arr[i].y, self.pcm_arr[i].log2_size, self.pcm_arr[i].sample_off = x, y, lg, off
+            self.pcm_buf = np.concatenate(self.pcm_samples)
+            J.pcms, J.n_pcms = C.cast(self.pcm_arr, C.POINTER(L.PCM)), len(self.pcms)
+            J.pcm_samples, J.n_pcm_samples = L.as_ptr(self.pcm_buf, C.c_uint8), len(self.pcm_buf)
         self.job = J
 
     def _cu(self, x, y, lg):
@@ -220,6 +228,18 @@ class SynthJob:
             return
         qp = int(self.rng.integers(18, 42))
         self.qp[y // 8:(y + n) // 8, x // 8:(x + n) // 8] = qp
+        if self.pcm_prob and self.rng.random() < self.pcm_prob:   # PCM coding block (S4), no TUs
+            from libde265_b200 import lib as L
+            off = sum(len(a) for a in self.pcm_samples)
+            self.pcms.append((x, y, lg, off))
+            self.pcm_samples.append(self.rng.integers(0, 256, size=n * n + n * n // 2, dtype=np.uint8))
+            u = self.unit[y // 4:(y + n) // 4, x // 4:(x + n) // 4]
+            u |= L.UNIT_INTRA | L.UNIT_DONE | (L.UNIT_NOFILT if self.rng.random() < 0.5 else 0)
+            if x > 0:
+                u[:, 0] |= L.UNIT_EDGE_V
+            if y > 0:
+                u[0, :] |= L.UNIT_EDGE_H
+            return
         nxn = lg == 3 and self.rng.random() < 0.35
         self._tt(x, y, lg, 0, nxn, qp, x, y, 0)
 
