@@ -67,6 +67,9 @@ struct FrameDev {
   const b265_pcm* pcms;       // PCM coding blocks (S4) and their samples (Y, Cb, Cr per block)
   const uint8_t* pcm_samples;
   int n_pcms;
+  int n_tus;
+  uint64_t* tb_mask;          // per TU: availability mask of the intra TB's neighbouring units (k_intra_prep)
+  int16_t* resid[3];          // residuals of the coded intra TBs (same geometry/pitch as plane[], in samples)
   uint8_t* done[3];           // intra CTB-wavefront completion flags, one byte per CTB of the plane (raster)
   int done_pitch[3];          // = ctbs_w
   uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal
@@ -78,9 +81,11 @@ struct FrameDev {
 
 // one ticket of the intra CTB wavefront: plane `plane` of CTB `ctb` (raster) of frame `frame`; the CTB's
 // TUs are tus[tu_first .. tu_first+tu_count) in decoding order (all planes interleaved)
+#define B265_TICKET_MIXED 1  // the CTB plane also holds samples not produced by this ticket (inter / PCM)
 struct IntraTicket {
   uint16_t frame;
-  uint16_t plane;
+  uint8_t plane;
+  uint8_t flags;
   uint32_t ctb;
   uint32_t tu_first;
   uint32_t tu_count;

@@ -19,7 +19,8 @@ struct b265_batch {
   // device pointers into dev
   FrameDev* d_frames = nullptr;
   uint32_t* d_mc_items = nullptr;     int n_mc = 0;
-  uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};
+  uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};     // inter TUs (residual added in place)
+  uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
   IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
   unsigned* d_ticket = nullptr;
   uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // bs maps cleared per run
@@ -28,6 +29,8 @@ struct b265_batch {
   int max_wave = 0;
   int wave_width = 0;                 // largest number of tickets in one wave
   int max_pcms = 0;                   // largest PCM block count of a picture
+  int max_tus = 0;
+  int log2_ctb = 4;                   // largest CTB of the batch (sizes the wavefront's shared-memory tiles)
   bool pooled = false;                // dev/host belong to the context's grow-only staging (b265_submit_frames)
 };
 
@@ -54,10 +57,11 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   b->frames.assign(n_jobs, FrameDev());
   struct Key { uint32_t wave; IntraTicket t; };
   std::vector<Key> intra;
-  std::vector<uint32_t> res[4], mc;
+  std::vector<uint32_t> res[4], ires[4], mc;
   std::vector<std::vector<uint8_t>> done_init(n_jobs);   // per frame: 3 planes x nctb, 1 = nothing to wait for
   std::vector<uint32_t> ctb_first, ctb_count;
   std::vector<uint8_t> ctb_has;
+  std::vector<uint32_t> ctb_area;   // samples covered by intra TBs, per plane and CTB
   int max_wave = 0;
   // ---- pass 1: classify; TUs arrive in decoding order, so the TUs of one CTB are contiguous ----
   for (int j = 0; j < n_jobs; j++) {
@@ -69,6 +73,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     ctb_first.assign(nctb, 0);
     ctb_count.assign(nctb, 0);
     ctb_has.assign(nctb, 0);
+    ctb_area.assign((size_t)3 * nctb, 0);
+    b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
+    if (J.log2_ctb < 4 || J.log2_ctb > 6) return B265_ERR_INVALID_ARG;
     int cur = -1;
     for (int i = 0; i < J.n_tus; i++) {
       const b265_tu& t = J.tus[i];
@@ -84,18 +91,26 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
         cur = ctb;
       }
       ctb_count[ctb]++;
-      if (t.intra_mode != B265_INTRA_NONE) ctb_has[ctb] |= (uint8_t)(1 << c);
-      else if (t.ncoeff > 0) res[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
+      if (t.intra_mode != B265_INTRA_NONE) {
+        ctb_has[ctb] |= (uint8_t)(1 << c);
+        ctb_area[(size_t)c * nctb + ctb] += 1u << (2 * lg);
+        if (t.ncoeff > 0) ires[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
+      } else if (t.ncoeff > 0) res[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
     }
     done_init[j].assign((size_t)3 * nctb, 1);
     for (int ctb = 0; ctb < nctb; ctb++) {
       if (!ctb_has[ctb]) continue;
       const uint32_t wave = (uint32_t)(ctb % cw_ + 2 * (ctb / cw_));
       max_wave = std::max<int>(max_wave, (int)wave);
+      const int S = 1 << J.log2_ctb;
+      const int bw = std::min(S, J.width - (ctb % cw_) * S), bh = std::min(S, J.height - (ctb / cw_) * S);
       for (int c = 0; c < 3; c++)
         if (ctb_has[ctb] & (1 << c)) {
           done_init[j][(size_t)c * nctb + ctb] = 0;
-          intra.push_back({wave, {(uint16_t)j, (uint16_t)c, (uint32_t)ctb, ctb_first[ctb], ctb_count[ctb]}});
+          // a CTB plane not fully covered by intra TBs also holds inter / PCM samples written by earlier launches
+          const uint32_t full = (c && J.chroma_format_idc) ? (uint32_t)(((bw + 1) >> 1) * ((bh + 1) >> 1)) : (uint32_t)(bw * bh);
+          const uint8_t fl = ctb_area[(size_t)c * nctb + ctb] != full ? B265_TICKET_MIXED : 0;
+          intra.push_back({wave, {(uint16_t)j, (uint8_t)c, fl, (uint32_t)ctb, ctb_first[ctb], ctb_count[ctb]}});
         }
     }
     for (int i = 0; i < J.n_pus; i++) mc.push_back(((uint32_t)j << 24) | (uint32_t)i);
@@ -112,7 +127,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   }
   b->n_tickets = (int)tickets.size();
   b->n_mc = (int)mc.size();
-  for (int s = 0; s < 4; s++) b->n_res[s] = (int)res[s].size();
+  for (int s = 0; s < 4; s++) { b->n_res[s] = (int)res[s].size(); b->n_ires[s] = (int)ires[s].size(); }
 
   // ---- layout ----
   Packer P;
@@ -120,6 +135,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const size_t o_mc = P.take(4 * mc.size());
   size_t o_res[4];
   for (int s = 0; s < 4; s++) o_res[s] = P.take(4 * res[s].size());
+  size_t o_ires[4];
+  for (int s = 0; s < 4; s++) o_ires[s] = P.take(4 * ires[s].size());
   const size_t o_tickets = P.take(sizeof(IntraTicket) * tickets.size());
   size_t done_total = 0;
   for (int j = 0; j < n_jobs; j++) done_total += done_init[j].size();
@@ -146,7 +163,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const size_t o_ticket = P.take(256);
   const size_t o_done = P.take(done_total);
   const size_t o_zero = P.off;
-  struct SOff { size_t done[3], bs, tmp[3], motion; int dp[3]; };
+  struct SOff { size_t done[3], bs, tmp[3], motion, resid[3], tb_mask; int dp[3]; };
   std::vector<SOff> so(n_jobs);
   {
     size_t acc = 0;
@@ -166,6 +183,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   for (int j = 0; j < n_jobs; j++) {  // SAO needs the deblocked picture kept aside
     const b265_frame_job& J = jobs[j];
     so[j].tmp[0] = so[j].tmp[1] = so[j].tmp[2] = 0;
+    so[j].resid[0] = so[j].resid[1] = so[j].resid[2] = 0;
     so[j].motion = (J.n_pus > 0 && (J.flags & B265_FRAME_DEBLOCK)) ? P.take((size_t)16 * ((J.width + 3) >> 2) * ((J.height + 3) >> 2)) : 0;
     if (J.flags & B265_FRAME_SAO) {
       const int pitch = (J.width + 255) & ~255, cpitch = (((J.width + 1) >> 1) + 127) & ~127;
@@ -173,6 +191,24 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       if (J.chroma_format_idc) {
         so[j].tmp[1] = P.take((size_t)cpitch * ((J.height + 1) >> 1));
         so[j].tmp[2] = P.take((size_t)cpitch * ((J.height + 1) >> 1));
+      }
+    }
+  }
+  {  // int16 residual planes of the coded intra TBs (same geometry as the destination surface)
+    std::vector<uint8_t> need(n_jobs, 0);
+    for (int s = 0; s < 4; s++)
+      for (uint32_t o : ires[s]) need[o >> 24] = 1;
+    for (int j = 0; j < n_jobs; j++) {
+      so[j].tb_mask = P.take((size_t)8 * jobs[j].n_tus);
+      if (!need[j]) continue;
+      const b265_frame_job& J = jobs[j];
+      if (J.dst_surface < 0 || J.dst_surface >= (int)ctx->surfaces.size() || !ctx->surfaces[J.dst_surface].used)
+        return B265_ERR_INVALID_ARG;
+      const Surface& S = ctx->surfaces[J.dst_surface];
+      so[j].resid[0] = P.take((size_t)2 * S.pitch[0] * J.height);
+      if (J.chroma_format_idc) {
+        so[j].resid[1] = P.take((size_t)2 * S.pitch[1] * ((J.height + 1) >> 1));
+        so[j].resid[2] = P.take((size_t)2 * S.pitch[2] * ((J.height + 1) >> 1));
       }
     }
   }
@@ -193,6 +229,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   auto cp = [&](size_t off, const void* src, size_t bytes) { if (bytes && src) memcpy(H + off, src, bytes); };
   cp(o_mc, mc.data(), 4 * mc.size());
   for (int s = 0; s < 4; s++) cp(o_res[s], res[s].data(), 4 * res[s].size());
+  for (int s = 0; s < 4; s++) cp(o_ires[s], ires[s].data(), 4 * ires[s].size());
   cp(o_tickets, tickets.data(), sizeof(IntraTicket) * tickets.size());
   {
     size_t acc = 0;
@@ -201,6 +238,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   b->d_frames = (FrameDev*)(D + o_frames);
   b->d_mc_items = (uint32_t*)(D + o_mc);
   for (int s = 0; s < 4; s++) b->d_res_order[s] = (uint32_t*)(D + o_res[s]);
+  for (int s = 0; s < 4; s++) b->d_ires_order[s] = (uint32_t*)(D + o_ires[s]);
   b->d_tickets = (IntraTicket*)(D + o_tickets);
   b->d_done_init = D + o_done_init;
   b->d_done = D + o_done;
@@ -233,6 +271,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       f.pitch[c] = S.pitch[c];
       f.plane[c] = (so[j].tmp[c] && (J.flags & B265_FRAME_SAO)) ? D + so[j].tmp[c] : S.plane[c];
       f.done[c] = D + so[j].done[c];
+      f.resid[c] = so[j].resid[c] ? (int16_t*)(D + so[j].resid[c]) : nullptr;
       f.done_pitch[c] = so[j].dp[c];
     }
     f.width = J.width; f.height = J.height;
@@ -254,6 +293,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.pcms = J.n_pcms ? (const b265_pcm*)(D + fo[j].pcms) : nullptr;
     f.pcm_samples = J.n_pcm_samples ? D + fo[j].pcm_samples : nullptr;
     f.n_pcms = J.n_pcms;
+    f.n_tus = J.n_tus;
+    f.tb_mask = (uint64_t*)(D + so[j].tb_mask);
+    b->max_tus = std::max(b->max_tus, J.n_tus);
     b->max_pcms = std::max(b->max_pcms, J.n_pcms);
     f.bs = D + so[j].bs;
     f.motion = so[j].motion ? (uint32_t*)(D + so[j].motion) : nullptr;
@@ -272,7 +314,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
 
 // ------------------------------------------------------------------------------------------
 // Device work for one batch, all on ctx->stream:
-//   clear done/bs maps -> [pcm store] -> MC (all PUs) -> inter residual (4 sizes) -> intra wavefront
+//   clear done/bs maps -> [pcm store] -> MC (all PUs) -> inter residual (4 sizes, in place)
+//   -> intra residual (4 sizes, to the int16 scratch planes) -> intra wavefront
 //   -> boundary strength -> deblock V -> deblock H -> SAO
 // ------------------------------------------------------------------------------------------
 static int run_batch(b265_ctx* ctx, b265_batch* b) {
@@ -299,10 +342,17 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
       CK_LAUNCH("k_residual_sparse");
     }
   if (tm) cudaEventRecord(ctx->stage_ev[2], st);
+  for (int s = 0; s < 4; s++)
+    if (b->n_ires[s]) {
+      launch_residual_sparse(st, 2 + s, b->d_frames, b->d_ires_order[s], b->n_ires[s], ctx->sm_count, true);
+      ctx->launches++;
+      CK_LAUNCH("k_residual_sparse(scratch)");
+    }
   if (b->n_tickets) {
-    static int max_ctas = 0;
-    if (!max_ctas) max_ctas = intra_max_resident_ctas(ctx->sm_count);
-    launch_intra(st, b->d_frames, b->d_tickets, b->n_tickets, b->d_ticket, max_ctas, b->wave_width);
+    launch_intra_prep(st, b->d_frames, b->n_frames, b->max_tus);
+    ctx->launches++;
+    CK_LAUNCH("k_intra_prep");
+    launch_intra(st, b->d_frames, b->d_tickets, b->n_tickets, b->d_ticket, ctx->sm_count, b->wave_width, b->log2_ctb);
     ctx->launches++;
     CK_LAUNCH("k_intra_wavefront");
   }

@@ -1,20 +1,33 @@
-// intra.cuh — intra prediction as group-cooperative device code (a group = N lanes = one N x N TB).
+// intra.cuh — intra prediction as warp-cooperative device code (lanes 0..N-1 of a warp = one N x N TB).
 //
 // Restates libde265/intrapred.cc: intra_border_computer (:344-688: availability by picture edge,
 // CTB slice/tile ownership, z-scan order and constrained_intra_pred; reference-sample substitution
 // :395-431), intra_prediction_sample_filtering (:816-889), angular (:903-1005), planar (:1009-1032)
-// and DC (:1036-1069).  Border convention as in the reference: p[0] = top-left corner,
-// p[1..2N] = top row then top-right, p[-1..-2N] = left column then bottom-left.
+// and DC (:1036-1069).
 //
-// Neighbouring samples are produced either by the same warp (earlier TBs of the same CTB) or by
-// other warps of the SAME launch (CTB wavefront, k_intra.cu): the warp waits for the neighbouring
-// CTBs' completion flags once per CTB and then reads all border pixels through L2 (ld.cg).
+// The code is written for the LATENCY of one warp walking the TBs of a CTB one after the other
+// (k_intra.cu): few instructions per TB, no global memory access on the way.
+//  * availability of the neighbouring 4-sample units is a 64-bit mask per TB, computed beforehand by a
+//    parallel kernel (intra_avail_mask, k_intra_prep);
+//  * neighbouring samples come from the CTB's "edge store" in shared memory: only the bottom row and
+//    the right column of a finished TB can ever be read by later TBs, so the store keeps the rows
+//    y = -1, 3, 7, ... and the columns x = -1, 3, 7, ... of the CTB;
+//  * the border lives in two byte lines T[k] = p[k] (corner, top, top-right) and L[k] = p[-k] (corner,
+//    left, bottom-left) whose samples 1.. are word aligned: gather, [1 2 1] filter and the angular
+//    interpolation work on 4 samples per instruction (funnel shifts, byte-wise averages, dp4a);
+//  * modes 2..17 are predicted with the lane owning a COLUMN (the main reference is the left line), all
+//    other modes with the lane owning a ROW.
 #pragma once
 #include "common.cuh"
 
-#define B265_BORDER_BYTES 512  // per warp: 32/N groups x 2 buffers x (4N+8) bytes
+#define B265_BORDER_BYTES 512  // per warp: 2 buffers x (6N+8) bytes, N <= 32
 
-template <int N> struct IntraBuf { static constexpr int STRIDE = 4 * N + 8; };
+// border buffer: [3 pad][ext N][T 2N+1][3 pad][ext N][L 2N+1]; T[1] and L[1] are 4-byte aligned
+template <int N> struct IntraBuf {
+  static constexpr int TOP = N + 3;
+  static constexpr int LEFT = 4 * N + 7;
+  static constexpr int STRIDE = 6 * N + 8;
+};
 
 __device__ __forceinline__ unsigned morton4(unsigned x, unsigned y) {
   // interleave the low 4 bits of x (even positions) and y (odd positions)
@@ -23,163 +36,164 @@ __device__ __forceinline__ unsigned morton4(unsigned x, unsigned y) {
   return x | (y << 1);
 }
 
+// Picture / CTB constants of a ticket, held in registers (the FrameDev record lives in global memory;
+// re-reading its fields per TB would cost an L2 round trip each).
 struct IntraGeom {
-  int sh;            // 0 luma, 1 chroma (4:2:0)
-  int xL, yL;        // luma position of the block
-  int cur_ctb, cur_slice, cur_tile;
-  unsigned cur_zs;   // z-scan order address of the block at min-TB granularity
+  int sh;                    // 0 luma, 1 chroma (4:2:0)
+  int width, height;         // luma picture size
+  int log2_ctb, log2_min_tb;
+  int cx, cy;                // CTB position in CTB units
+  unsigned nb;               // neighbouring CTBs usable for prediction (same slice, same tile, earlier in decoding
+                             // order; intrapred.cc:486-508): bit0 left, bit1 upper-left, bit2 upper, bit3 upper-right
+  const uint8_t* unit_info;  // non-NULL only with constrained_intra_pred
+  int unit_pitch;
+  uint8_t* plane;            // destination plane of this component
+  const int16_t* resid;
+  int pitch;
+  bool strong;               // strong_intra_smoothing_enabled
 };
 
-// z-scan address of the min-TB containing luma sample (x,y)  (pps MinTbAddrZS)
-__device__ __forceinline__ unsigned zs_addr(const FrameDev& f, int x, int y, int ctb) {
-  const int d = f.log2_ctb - f.log2_min_tb;
-  const int m = (1 << f.log2_ctb) - 1;
-  const unsigned ts = f.ctbs ? (unsigned)f.ctbs[ctb].addr_ts : (unsigned)ctb;
-  return (ts << (2 * d)) + morton4((x & m) >> f.log2_min_tb, (y & m) >> f.log2_min_tb);
+// z-scan order of the min-TB containing luma sample (x,y) inside its CTB (pps MinTbAddrZS minus the CTB term)
+__device__ __forceinline__ unsigned zs_in_ctb(const IntraGeom& g, int x, int y) {
+  const int m = (1 << g.log2_ctb) - 1;
+  return morton4((x & m) >> g.log2_min_tb, (y & m) >> g.log2_min_tb);
 }
 
-// availability of the neighbouring 4-sample unit whose defining luma sample is (nx,ny)
-__device__ __forceinline__ bool unit_available(const FrameDev& f, const IntraGeom& g, int nx, int ny) {
-  if (nx < 0 || ny < 0 || nx >= f.width || ny >= f.height) return false;
-  const int ctb = (ny >> f.log2_ctb) * f.ctbs_w + (nx >> f.log2_ctb);
-  if (ctb != g.cur_ctb && f.ctbs) {
-    if (f.ctbs[ctb].slice != g.cur_slice || f.ctbs[ctb].tile != g.cur_tile) return false;
+// availability of the neighbouring 4-sample unit whose defining luma sample is (nx,ny); cur_zs = zs_in_ctb of
+// the current block.  Pure ALU unless constrained_intra_pred is on.
+__device__ __forceinline__ bool unit_available(const IntraGeom& g, unsigned cur_zs, int nx, int ny) {
+  if (nx < 0 || ny < 0 || nx >= g.width || ny >= g.height) return false;
+  const int dx = (nx >> g.log2_ctb) - g.cx, dy = (ny >> g.log2_ctb) - g.cy;
+  if (dx == 0 && dy == 0) {
+    if (zs_in_ctb(g, nx, ny) > cur_zs) return false;   // not decoded yet
+  } else {
+    // CTBs below or to the right come later in decoding order (or lie in another tile)
+    int bit;
+    if (dy == 0 && dx == -1) bit = 0;
+    else if (dy == -1 && dx >= -1 && dx <= 1) bit = 2 + dx;
+    else return false;
+    if (!((g.nb >> bit) & 1u)) return false;
   }
-  if (zs_addr(f, nx, ny, ctb) > g.cur_zs) return false;
-  if ((f.flags & B265_FRAME_CONSTRAINED_INTRA) && f.unit_info) {
-    if (!(f.unit_info[(ny >> 2) * (f.width >> 2) + (nx >> 2)] & B265_UNIT_INTRA)) return false;
+  if (g.unit_info) {
+    if (!(__ldg(&g.unit_info[(ny >> 2) * g.unit_pitch + (nx >> 2)]) & B265_UNIT_INTRA)) return false;
   }
   return true;
 }
 
-// Gather p[-2N..2N] of the TB at component position (xB,yB) of plane c into buf[i + 2N].
-// Returns nothing; all lanes of the warp call it (ballots). `active` false for idle groups.
+// Availability mask of the TB at component position (xB,yB), size N = 1 << log2, in scan order
+// (intrapred.cc:395-431 walks bottom-left -> corner -> top-right): bits 0..N/2-1 = left units bottom-up,
+// bit N/2 = corner, bits N/2+1..N = top units left to right.
+__device__ __forceinline__ uint64_t intra_avail_mask(const IntraGeom& g, int xB, int yB, int log2) {
+  const int N = 1 << log2, H = N >> 1, sh = g.sh;
+  const unsigned cur_zs = zs_in_ctb(g, xB << sh, yB << sh);
+  uint64_t M = 0;
+  for (int s = 0; s < H; s++)
+    if (unit_available(g, cur_zs, (xB - 1) << sh, (yB + 2 * N - 1 - 4 * s) << sh)) M |= 1ull << s;
+  if (unit_available(g, cur_zs, (xB - 1) << sh, (yB - 1) << sh)) M |= 1ull << H;
+  for (int w = 0; w < H; w++)
+    if (unit_available(g, cur_zs, (xB + 4 * w) << sh, (yB - 1) << sh)) M |= 1ull << (H + 1 + w);
+  return M;
+}
+
+// Edge store of the CTB plane a warp is walking (shared memory).
+//   rows[q][16 + c] = sample (c, 4q-1) relative to the CTB origin, c = -1..2S-1   (q = 0: row above the CTB)
+//   cols[q][r]      = sample (4q-1, r),                            r = 0..S-1     (q = 0: column left of the CTB)
+struct CtbEdges {
+  uint8_t* rows;
+  uint8_t* cols;
+  int S, rstride;   // rstride = 2S + 16
+  int x0, y0;       // component position of the CTB origin
+};
+__host__ __device__ constexpr int ctb_edges_bytes(int S) { return (S / 4 + 1) * (2 * S + 16) + (S / 4 + 1) * S; }
+
+// Border of the TB at (xr,yr) relative to the CTB origin -> buf (IntraBuf layout), with the reference
+// sample substitution of intrapred.cc:395-431: a missing unit copies the nearest available sample before it
+// in scan order, leading missing units copy the first available sample, nothing available -> 128.
+// Called by all lanes of the warp.
 template <int LOG2>
-__device__ __forceinline__ void gather_border(const FrameDev& f, int c, int xB, int yB, int sub, int grp,
-                                              bool active, uint8_t* buf) {
-  constexpr int N = 1 << LOG2, NU = N / 4;  // NU units per N samples
-  const int sh = (c && f.cw) ? 1 : 0;
-  IntraGeom g;
-  g.sh = sh; g.xL = xB << sh; g.yL = yB << sh;
-  g.cur_ctb = (g.yL >> f.log2_ctb) * f.ctbs_w + (g.xL >> f.log2_ctb);
-  g.cur_slice = f.ctbs ? f.ctbs[active ? g.cur_ctb : 0].slice : 0;
-  g.cur_tile = f.ctbs ? f.ctbs[active ? g.cur_ctb : 0].tile : 0;
-  g.cur_zs = active ? zs_addr(f, g.xL, g.yL, g.cur_ctb) : 0;
-  const uint8_t* plane = f.plane[c];
-  const int pitch = f.pitch[c];
-
-  // lane `sub` owns scan unit: sub < 2NU -> left column unit (bottom-up), else top row unit
-  const bool is_left = sub < 2 * NU;
-  int ux, uy;  // component position of the unit's defining sample (reference: bottom row / left col)
-  if (is_left) { ux = xB - 1; uy = yB + 2 * N - 1 - 4 * sub; }
-  else         { ux = xB + 4 * (sub - 2 * NU); uy = yB - 1; }
-  bool av = active && unit_available(f, g, ux << sh, uy << sh);
-  // (the reference tests slice/tile ownership once per neighbouring CTB, intrapred.cc:486-508; a
-  //  left/top/top-right run of N samples never straddles two CTBs, so the per-unit test is the same)
-  bool avc = false;
-  if (active && sub == 0) avc = unit_available(f, g, (xB - 1) << sh, (yB - 1) << sh);
-
-  uint32_t px = 0;
-  if (av) {
-    if (is_left) {
-#pragma unroll
-      for (int i = 0; i < 4; i++)  // border index -2N+4*sub+i  <->  row uy-(3-i)... ascending index = going up
-        px |= (uint32_t)ld_cg_u8(plane + (size_t)(uy - i) * pitch + ux) << (8 * i);
-    } else {
-      const uint8_t* s = plane + (size_t)uy * pitch + ux;
-      px = ((reinterpret_cast<uintptr_t>(s) & 3) == 0) ? ld_cg_u32(s)
-           : ((uint32_t)ld_cg_u8(s) | ((uint32_t)ld_cg_u8(s + 1) << 8) | ((uint32_t)ld_cg_u8(s + 2) << 16) |
-              ((uint32_t)ld_cg_u8(s + 3) << 24));
-    }
-  }
-  uint32_t pc = 0;
-  if (avc) {
-    pc = ld_cg_u8(plane + (size_t)(yB - 1) * pitch + xB - 1);
-  }
-  // scan-order availability mask of this group: bits 0..2NU-1 left, bit 2NU corner, then top
-  const uint32_t ball = __ballot_sync(B265_FULL_MASK, av);
-  const uint32_t ballc = __ballot_sync(B265_FULL_MASK, avc);
-  const uint32_t gm = (N == 32) ? ball : ((ball >> (grp * N)) & ((1u << N) - 1u));
-  const uint64_t corner = (ballc >> (grp * N)) & 1u;
-  const uint64_t leftm = gm & ((1u << (2 * NU)) - 1u);
-  const uint64_t topm = (uint64_t)(gm >> (2 * NU));
-  const uint64_t M = leftm | (corner << (2 * NU)) | (topm << (2 * NU + 1));
-
-  // unit -> border index of its first (lowest-index) sample
-  auto first_index = [&](int s) -> int {  // scan unit s
-    if (s < 2 * NU) return -2 * N + 4 * s;
-    if (s == 2 * NU) return 0;
-    return 1 + 4 * (s - 2 * NU - 1);
+__device__ __forceinline__ void gather_border(const CtbEdges& E, int xr, int yr, uint64_t M, int lane, uint8_t* buf) {
+  constexpr int N = 1 << LOG2, H = N / 2;
+  const uint8_t* colp = E.cols + (xr >> 2) * E.S;             // column xr-1, indexed by relative row
+  const uint8_t* rowp = E.rows + (yr >> 2) * E.rstride + 16;  // row yr-1, indexed by relative column
+  auto sample = [&](int t, bool last) -> uint32_t {  // first / last sample (scan order) of scan unit t
+    if (t < H) return colp[yr + 4 * (H - 1 - t) + (last ? 0 : 3)];
+    if (t == H) return rowp[xr - 1];
+    return rowp[xr + 4 * (t - H - 1) + (last ? 3 : 0)];
   };
-  auto last_index = [&](int s) -> int { return (s == 2 * NU) ? 0 : first_index(s) + 3; };
-
-  // left units store bottom-up: border index -2N+4*sub+i holds row uy-i?  index grows towards the corner
-  if (active) {
-    if (av) {
-      const int base = is_left ? (-2 * N + 4 * sub) : (1 + 4 * (sub - 2 * NU));
-      uint8_t* d = buf + 2 * N + base;
-#pragma unroll
-      for (int i = 0; i < 4; i++) d[i] = (px >> (8 * i)) & 0xff;
-    }
-    if (sub == 0 && avc) buf[2 * N] = (uint8_t)pc;
+  auto subst = [&](int s) -> uint32_t {
+    if (M == 0) return 128;
+    const uint64_t lower = M & ((1ull << s) - 1ull);
+    if (lower) return sample(63 - __clzll((long long)lower), true);
+    return sample(__ffsll((long long)M) - 1, false);
+  };
+  if (lane < N) {
+    const bool left = lane < H;
+    const int w = left ? lane : lane - H;        // word of the line: samples 1+4w .. 4+4w
+    const int s = left ? H - 1 - lane : H + 1 + w;
+    uint32_t v;
+    if ((M >> s) & 1ull)
+      v = left ? *reinterpret_cast<const uint32_t*>(colp + yr + 4 * w) : *reinterpret_cast<const uint32_t*>(rowp + xr + 4 * w);
+    else
+      v = subst(s) * 0x01010101u;
+    *reinterpret_cast<uint32_t*>(buf + (left ? IntraBuf<N>::LEFT : IntraBuf<N>::TOP) + 1 + 4 * w) = v;
   }
-  __syncwarp();
-  {
-    // reference_sample_substitution (intrapred.cc:395-431): missing samples copy the nearest
-    // available sample below/left in scan order, leading ones copy the first available sample
-    const bool incomplete = active && M != ((1ull << (4 * NU + 1)) - 1ull);
-    auto subst = [&](int s) -> int {
-      if (M == 0) return 128;
-      const uint64_t lower = M & ((1ull << s) - 1ull);
-      if (lower) return buf[2 * N + last_index(63 - __clzll((long long)lower))];
-      return buf[2 * N + first_index(__ffsll((long long)M) - 1)];
-    };
-    const int s_me = is_left ? sub : sub + 1;
-    int vme = 0, vc = 0;
-    const bool need_me = incomplete && !av, need_c = incomplete && (sub == 0) && !corner;
-    if (need_me) vme = subst(s_me);
-    if (need_c) vc = subst(2 * NU);
-    __syncwarp();
-    if (need_me) {
-      uint8_t* d = buf + 2 * N + first_index(s_me);
-#pragma unroll
-      for (int i = 0; i < 4; i++) d[i] = (uint8_t)vme;
-    }
-    if (need_c) buf[2 * N] = (uint8_t)vc;
+  if (lane == (N < 32 ? N : 0)) {
+    const uint32_t c = ((M >> H) & 1ull) ? (uint32_t)rowp[xr - 1] : subst(H);
+    buf[IntraBuf<N>::TOP] = (uint8_t)c;
+    buf[IntraBuf<N>::LEFT] = (uint8_t)c;
   }
   __syncwarp();
 }
 
+// byte-wise (a + b) >> 1 and (a + b + 1) >> 1 on four packed samples
+__device__ __forceinline__ uint32_t hadd4(uint32_t a, uint32_t b) { return (a & b) + (((a ^ b) & 0xfefefefeu) >> 1); }
+__device__ __forceinline__ uint32_t avg4(uint32_t a, uint32_t b) { return (a | b) - (((a ^ b) & 0xfefefefeu) >> 1); }
+
 // ---- intra_prediction_sample_filtering (intrapred.cc:816-889) ----
-// p = src + 2N (border centre).  Writes the filtered border to dst (same layout) when the mode/size
-// rule asks for it and returns the buffer to predict from.  Called by all lanes of the warp.
+// Writes the filtered border to dst (same layout) when the mode/size rule asks for it and returns the
+// buffer to predict from.  (a + 2b + c + 2) >> 2 == avg4(b, hadd4(a, c)) exactly.  All lanes call it.
 template <int LOG2>
-__device__ __forceinline__ const uint8_t* filter_border(const uint8_t* src, uint8_t* dst, int sub, int mode,
-                                                        int cidx, bool strong_enabled, bool active) {
-  constexpr int N = 1 << LOG2;
-  bool filt = false;
-  if (active && cidx == 0 && mode != 1 && N != 4) {
-    const int d = min(abs(mode - 26), abs(mode - 10));
-    filt = (N == 8) ? d > 7 : (N == 16) ? d > 1 : d > 0;
-  }
-  const uint8_t* p = src + 2 * N;
-  if (filt) {
-    bool bi = false;
-    if (N == 32 && strong_enabled)
-      bi = abs(p[0] + p[64] - 2 * p[32]) < 8 && abs(p[0] + p[-64] - 2 * p[-32]) < 8;  // 1 << (bitDepth-5)
-    uint8_t* q = dst + 2 * N;
-    for (int j = sub; j < 4 * N + 1; j += N) {
-      const int i = j - 2 * N;
-      int v;
-      if (i == -2 * N || i == 2 * N) v = p[i];
-      else if (bi) v = (i == 0) ? p[0] : (i < 0 ? p[0] + ((-i * (p[-64] - p[0]) + 32) >> 6)
-                                                : p[0] + ((i * (p[64] - p[0]) + 32) >> 6));
-      else v = (p[i + 1] + 2 * p[i] + p[i - 1] + 2) >> 2;
-      q[i] = (uint8_t)v;
+__device__ __forceinline__ uint8_t* filter_border(uint8_t* src, uint8_t* dst, int lane, int mode, int cidx, bool strong_enabled) {
+  constexpr int N = 1 << LOG2, H = N / 2;
+  if (cidx != 0 || mode == 1 || N == 4) return src;  // warp-uniform
+  const int d = min(abs(mode - 26), abs(mode - 10));
+  const bool filt = (N == 8) ? d > 7 : (N == 16) ? d > 1 : d > 0;
+  if (!filt) return src;
+  const uint8_t* T = src + IntraBuf<N>::TOP;
+  const uint8_t* L = src + IntraBuf<N>::LEFT;
+  bool bi = false;
+  if (N == 32 && strong_enabled)
+    bi = abs(T[0] + T[2 * N] - 2 * T[N]) < 8 && abs(L[0] + L[2 * N] - 2 * L[N]) < 8;  // 1 << (bitDepth-5)
+  if (lane < N) {
+    const bool left = lane < H;
+    const int w = left ? lane : lane - H;
+    const uint8_t* X = left ? L : T;
+    uint32_t out;
+    if (N == 32 && bi) {
+      const int p0 = X[0], pe = X[2 * N];
+      out = 0;
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int k = 1 + 4 * w + i;
+        out |= (uint32_t)(p0 + ((k * (pe - p0) + 32) >> 6)) << (8 * i);  // k = 64 gives pe
+      }
+    } else {
+      const uint32_t* xw = reinterpret_cast<const uint32_t*>(X + 1 + 4 * w);
+      const uint32_t prev = xw[-1], cur = xw[0], next = (w == H - 1) ? 0u : xw[1];
+      const uint32_t a = __funnelshift_l(prev, cur, 8);   // samples k-1
+      const uint32_t c = __funnelshift_r(cur, next, 8);   // samples k+1
+      out = avg4(cur, hadd4(a, c));
+      if (w == H - 1) out = (out & 0x00ffffffu) | (cur & 0xff000000u);  // p[+-2N] stays
     }
+    *reinterpret_cast<uint32_t*>(dst + (left ? IntraBuf<N>::LEFT : IntraBuf<N>::TOP) + 1 + 4 * w) = out;
+  }
+  if (lane == (N < 32 ? N : 0)) {
+    const int c = bi ? T[0] : (L[1] + 2 * T[0] + T[1] + 2) >> 2;
+    dst[IntraBuf<N>::TOP] = (uint8_t)c;
+    dst[IntraBuf<N>::LEFT] = (uint8_t)c;
   }
   __syncwarp();
-  return filt ? dst : src;
+  return dst;
 }
 
 __constant__ int8_t c_intra_angle[35] = {0,  0,  32, 26, 21, 17, 13, 9,  5,  2,  0,  -2, -5, -9, -13, -17, -21, -26,
@@ -187,57 +201,99 @@ __constant__ int8_t c_intra_angle[35] = {0,  0,  32, 26, 21, 17, 13, 9,  5,  2, 
 __constant__ int16_t c_intra_inv_angle[15] = {-4096, -1638, -910, -630, -482, -390, -315, -256,
                                               -315,  -390,  -482, -630, -910, -1638, -4096};
 
-// Prediction of row `sub` (N samples) from the border buffer b (b[i+2N] = p[i]).
-// Contains group-wide shuffles (DC sum): all lanes of the warp call it.
+// Prediction of line `lane` of the TB from the border buffer pb: a ROW for planar, DC and modes 18..34,
+// a COLUMN for modes 2..17 (returns true).  h[i] holds samples 2i (low half) and 2i+1 (high half) of
+// the line as 16-bit values.  Contains warp-wide shuffles / barriers: all lanes of the warp call it.
 template <int LOG2>
-__device__ __forceinline__ void predict_row(const uint8_t* b, int sub, int mode, int cidx, bool edge_filters,
-                                            int (&pred)[1 << LOG2]) {
+__device__ __forceinline__ bool predict_line(uint8_t* pb, int lane, int mode, int cidx, bool edge_filters,
+                                             uint32_t (&h)[(1 << LOG2) / 2]) {
   constexpr int N = 1 << LOG2;
-  const uint8_t* p = b + 2 * N;
-  const int y = sub;
-  // DC value is needed by the whole group; compute it unconditionally (cheap) to keep shuffles uniform
-  int dc = p[1 + sub] + p[-1 - sub];
-#pragma unroll
-  for (int o = N / 2; o > 0; o >>= 1) dc += __shfl_xor_sync(B265_FULL_MASK, dc, o);
-  dc = (dc + N) >> (LOG2 + 1);
-  if (mode == 0) {  // planar (intrapred.cc:1009-1032)
-#pragma unroll
-    for (int x = 0; x < N; x++)
-      pred[x] = ((N - 1 - x) * p[-1 - y] + (x + 1) * p[N + 1] + (N - 1 - y) * p[1 + x] + (y + 1) * p[-N - 1] + N) >>
-                (LOG2 + 1);
-  } else if (mode == 1) {  // DC (:1036-1069)
-#pragma unroll
-    for (int x = 0; x < N; x++) pred[x] = dc;
-    if (cidx == 0 && N < 32) {
-      if (y == 0) {
-#pragma unroll
-        for (int x = 1; x < N; x++) pred[x] = (p[x + 1] + 3 * dc + 2) >> 2;
-        pred[0] = (p[-1] + 2 * dc + p[1] + 2) >> 2;
-      } else {
-        pred[0] = (p[-y - 1] + 3 * dc + 2) >> 2;
-      }
-    }
-  } else {  // angular (:903-1005)
+  uint8_t* T = pb + IntraBuf<N>::TOP;
+  uint8_t* L = pb + IntraBuf<N>::LEFT;
+  const bool active = lane < N;
+  const int l = active ? lane : 0;
+  if (mode >= 2) {  // angular (:903-1005); the main line M is T (vertical modes) or L (horizontal modes)
+    const bool horiz = mode < 18;
+    uint8_t* Mp = horiz ? L : T;
+    const uint8_t* Op = horiz ? T : L;
     const int ang = c_intra_angle[mode];
-    const int inv = (mode >= 11 && mode <= 25) ? c_intra_inv_angle[mode - 11] : 0;
-    if (mode >= 18) {
-      const int idx = ((y + 1) * ang) >> 5, fact = ((y + 1) * ang) & 31;
-      auto ref = [&](int k) -> int { return k >= 0 ? p[k] : p[-((k * inv + 128) >> 8)]; };
+    if (ang < 0) {  // extend the main line to negative indices by projecting the other line
+      const int inv = c_intra_inv_angle[mode - 11];
+      const int k = -1 - l;
+      if (k > ((N * ang) >> 5)) Mp[k] = Op[(k * inv + 128) >> 8];  // lowest index read below is ((N*ang)>>5) + 1
+      __syncwarp();
+    }
+    const int t = (l + 1) * ang, idx = t >> 5, f = t & 31;
+    const uint8_t* a = Mp + idx + 1;   // samples a[0..N] are needed
+    const unsigned m = (unsigned)(reinterpret_cast<uintptr_t>(a) & 3u);
+    const uint32_t* aw = reinterpret_cast<const uint32_t*>(a - m);
+    uint32_t w[N / 4 + 1], lo[N / 4 + 1];
 #pragma unroll
-      for (int x = 0; x < N; x++)
-        pred[x] = fact ? ((32 - fact) * ref(x + idx + 1) + fact * ref(x + idx + 2) + 16) >> 5 : ref(x + idx + 1);
-      if (mode == 26 && cidx == 0 && N < 32 && edge_filters) pred[0] = clip8(p[1] + ((p[-1 - y] - p[0]) >> 1));
+    for (int j = 0; j <= N / 4; j++) w[j] = aw[j];
+#pragma unroll
+    for (int j = 0; j < N / 4; j++) lo[j] = __funnelshift_r(w[j], w[j + 1], 8 * m);
+    lo[N / 4] = w[N / 4] >> (8 * m);
+    const uint32_t W0 = (uint32_t)(32 - f) | ((uint32_t)f << 8);
+#pragma unroll
+    for (int j = 0; j < N / 4; j++) {
+      const uint32_t b34 = __funnelshift_r(lo[j], lo[j + 1], 24);
+      const uint32_t v0 = __dp4a(lo[j], W0, 16u), v1 = __dp4a(lo[j], W0 << 8, 16u);
+      const uint32_t v2 = __dp4a(lo[j], W0 << 16, 16u), v3 = __dp4a(b34, W0, 16u);
+      h[2 * j] = (__byte_perm(v0, v1, 0x5410) >> 5) & 0x00ff00ffu;
+      h[2 * j + 1] = (__byte_perm(v2, v3, 0x5410) >> 5) & 0x00ff00ffu;
+    }
+    if ((mode == 26 || mode == 10) && cidx == 0 && N < 32 && edge_filters)
+      h[0] = (h[0] & 0xffff0000u) | (uint32_t)clip8(Mp[1] + ((Op[1 + l] - Mp[0]) >> 1));
+    return horiz;
+  }
+  if (mode == 0) {  // planar (:1009-1032), lane = row y
+    const int y = l;
+    const uint32_t abd = (uint32_t)L[1 + y] | ((uint32_t)T[N + 1] << 8) | ((uint32_t)L[N + 1] << 24);
+    const uint32_t Wy = ((uint32_t)(N - 1 - y) << 16) | ((uint32_t)(y + 1) << 24);
+    const uint32_t* tw = reinterpret_cast<const uint32_t*>(T + 1);
+#pragma unroll
+    for (int j = 0; j < N / 4; j++) {
+      const uint32_t t4 = tw[j];
+      uint32_t v[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) {
+        const int x = 4 * j + i;
+        const uint32_t op = __byte_perm(abd, t4, 0x3010u | ((4u + i) << 8));   // [L[1+y], T[N+1], T[1+x], L[N+1]]
+        v[i] = __dp4a(op, Wy | (uint32_t)(N - 1 - x) | ((uint32_t)(x + 1) << 8), (uint32_t)N) >> (LOG2 + 1);
+      }
+      h[2 * j] = v[0] | (v[1] << 16);
+      h[2 * j + 1] = v[2] | (v[3] << 16);
+    }
+    return false;
+  }
+  // DC (:1036-1069), lane = row y
+  int dc = active ? T[1 + l] + L[1 + l] : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) dc += __shfl_xor_sync(B265_FULL_MASK, dc, o);
+  dc = (dc + N) >> (LOG2 + 1);
+#pragma unroll
+  for (int i = 0; i < N / 2; i++) h[i] = (uint32_t)dc * 0x00010001u;
+  if (cidx == 0 && N < 32) {
+    if (l == 0) {
+#pragma unroll
+      for (int i = 0; i < N / 2; i++)
+        h[i] = (uint32_t)((T[1 + 2 * i] + 3 * dc + 2) >> 2) | ((uint32_t)((T[2 + 2 * i] + 3 * dc + 2) >> 2) << 16);
+      h[0] = (h[0] & 0xffff0000u) | (uint32_t)((L[1] + 2 * dc + T[1] + 2) >> 2);
     } else {
-      auto ref = [&](int k) -> int { return k >= 0 ? p[-k] : p[(k * inv + 128) >> 8]; };
-#pragma unroll
-      for (int x = 0; x < N; x++) {
-        const int idx = ((x + 1) * ang) >> 5, fact = ((x + 1) * ang) & 31;
-        pred[x] = fact ? ((32 - fact) * ref(y + idx + 1) + fact * ref(y + idx + 2) + 16) >> 5 : ref(y + idx + 1);
-      }
-      if (mode == 10 && cidx == 0 && N < 32 && edge_filters && y == 0) {
-#pragma unroll
-        for (int x = 0; x < N; x++) pred[x] = clip8(p[-1] + ((p[1 + x] - p[0]) >> 1));
-      }
+      h[0] = (h[0] & 0xffff0000u) | (uint32_t)((L[1 + l] + 3 * dc + 2) >> 2);
     }
   }
+  return false;
+}
+
+// Clip1(pred + residual) on the 16-bit pairs, then pack the line to bytes.  r = residual line as int16 pairs
+// (values pre-clamped to +-1024 by the residual kernel, so the 16-bit add cannot wrap).
+template <int N>
+__device__ __forceinline__ void finish_line(uint32_t (&h)[N / 2], const uint32_t (&r)[N / 2], bool coded, uint32_t (&px)[N / 4]) {
+  if (coded) {
+#pragma unroll
+    for (int i = 0; i < N / 2; i++) h[i] = __viaddmin_s16x2_relu(h[i], r[i], 0x00ff00ffu);
+  }
+#pragma unroll
+  for (int j = 0; j < N / 4; j++) px[j] = __byte_perm(h[2 * j], h[2 * j + 1], 0x6420);
 }

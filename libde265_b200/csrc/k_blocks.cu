@@ -7,7 +7,6 @@
 //  * k_intra_blocks: intra_prediction_sample_filtering + planar/DC/angular (intrapred.cc:816-1069)
 //    from explicit border arrays, the same device functions the wavefront uses (intra.cuh).
 //  * k_interp_blocks: put_hevc_qpel_8 / put_hevc_epel_8 slots (fallback-motion.cc:298-407, 482-625).
-#include "transform.cuh"
 #include "intra.cuh"
 #include "kernels.h"
 
@@ -46,30 +45,44 @@ template <int LOG2>
 __global__ void __launch_bounds__(128) k_intra_blocks(int cidx, int n_blocks, const uint8_t* __restrict__ modes,
                                                       const uint8_t* __restrict__ borders, int strong, int no_edge_filter,
                                                       uint8_t* __restrict__ out) {
-  constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE, GROUPS = 32 / N;
+  constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE;
   __shared__ __align__(16) uint8_t sm[4][B265_BORDER_BYTES];
-  const int warp = threadIdx.x >> 5, lane = lane_id(), grp = lane / N, sub = lane % N;
-  const int blk = (blockIdx.x * 4 + warp) * GROUPS + grp;
-  const bool active = blk < n_blocks;
-  uint8_t* buf0 = sm[warp] + grp * 2 * STRIDE;
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int blk = blockIdx.x * 4 + warp;   // one block per warp (lanes 0..N-1), as in the wavefront
+  if (blk >= n_blocks) return;
+  uint8_t* buf0 = sm[warp];
   uint8_t* buf1 = buf0 + STRIDE;
-  const int mode = active ? modes[blk] : 1;
-  if (active) {
-    const uint8_t* b = borders + (size_t)blk * (4 * N + 1);
-    for (int j = sub; j < 4 * N + 1; j += N) buf0[j] = b[j];
+  const int mode = modes[blk];
+  {  // p[-2N..2N] -> the two border lines T[k] = p[k], L[k] = p[-k]
+    const uint8_t* p = borders + (size_t)blk * (4 * N + 1) + 2 * N;
+    for (int k = lane; k <= 2 * N; k += 32) {
+      buf0[IntraBuf<N>::TOP + k] = p[k];
+      buf0[IntraBuf<N>::LEFT + k] = p[-k];
+    }
   }
   __syncwarp();
-  const uint8_t* pb = filter_border<LOG2>(buf0, buf1, sub, mode, cidx, strong != 0, active);
-  int pred[N];
-  predict_row<LOG2>(pb, sub, mode, cidx, !no_edge_filter, pred);
-  if (active) store_row_u8<N>(out + (size_t)blk * N * N + sub * N, pred);
+  uint8_t* pb = filter_border<LOG2>(buf0, buf1, lane, mode, cidx, strong != 0);
+  uint32_t h[N / 2];
+  const bool by_column = predict_line<LOG2>(pb, lane, mode, cidx, !no_edge_filter, h);
+  if (lane < N) {
+    uint32_t px[N / 4];
+    const uint32_t none[N / 2] = {};
+    finish_line<N>(h, none, false, px);
+    uint8_t* d = out + (size_t)blk * N * N;
+    if (!by_column) {
+#pragma unroll
+      for (int q = 0; q < N / 4; q++) reinterpret_cast<uint32_t*>(d + lane * N)[q] = px[q];
+    } else {
+#pragma unroll
+      for (int j = 0; j < N; j++) d[j * N + lane] = (uint8_t)(px[j >> 2] >> (8 * (j & 3)));
+    }
+  }
 }
 
 void launch_intra_blocks(cudaStream_t st, int log2, int cidx, int n_blocks, const uint8_t* modes, const uint8_t* borders,
                          int strong, int no_edge_filter, uint8_t* out) {
   if (n_blocks <= 0) return;
-  const int per_cta = 4 * (32 >> log2);
-  const int grid = (n_blocks + per_cta - 1) / per_cta;
+  const int grid = (n_blocks + 3) / 4;
   switch (log2) {
     case 2: k_intra_blocks<2><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;
     case 3: k_intra_blocks<3><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;

@@ -1,65 +1,163 @@
-// k_intra.cu — intra prediction + residual of all intra TBs of a batch of pictures as ONE persistent
-// launch: a CTB-level wavefront.
+// k_intra.cu — intra prediction (+ residual add) of all intra TBs of a batch of pictures as ONE
+// persistent launch: a CTB-level wavefront.
 //
 // Intra TBs form dependency chains in z-scan order inside a CTB (every TB reads the reconstructed
-// samples left of / above it), so a CTB plane is walked SEQUENTIALLY by one warp — the hand-over
-// between consecutive TBs is a warp-level barrier, not a trip through global flags — and
-// parallelism comes from (a) the three colour planes, (b) the CTB anti-diagonal
-// wave = ctbX + 2*ctbY (a CTB needs its left, upper-left, upper and upper-right neighbours,
+// samples left of / above it, including below-left and above-right), so a CTB plane is walked
+// SEQUENTIALLY by one warp and parallelism comes from (a) the three colour planes, (b) the CTB
+// anti-diagonal wave = ctbX + 2*ctbY (a CTB needs its left, upper-left, upper and upper-right neighbours,
 // intrapred.cc:597-687), and (c) the pictures of the batch, which are mutually independent.
+// The kernel is therefore bound by the LATENCY of that one warp; everything that does not depend on
+// neighbouring samples is kept off its path:
+//  * the residuals of the intra TBs (dequant + inverse transform) are computed beforehand by the fully
+//    parallel k_residual_sparse<.., true> launches into an int16 residual plane (frames.cu);
+//  * the availability mask of every TB is computed beforehand by k_intra_prep (one thread per TB);
+//  * the samples a TB needs from earlier TBs of the same CTB come from the CTB's edge store in shared
+//    memory (intra.cuh), so global memory is read once per CTB (bordering row/column of the neighbouring
+//    CTBs, one L2 round trip after the flag wait) and never per TB.
 //
 // Host side (frames.cu) emits one ticket per (picture, CTB, plane) that contains intra TBs, sorted by
 // wave.  Warps draw tickets from an atomic counter; a warp waits for the (at most four) neighbouring
-// CTB flags of its plane with acquire loads, processes the CTB's TBs in decoding order, then publishes
-// its own flag with a release store.  Every dependency has a smaller ticket, tickets are only held by
-// running warps, so spinning cannot deadlock for any grid size.
+// CTB flags of its plane, processes the CTB's TBs in decoding order, then publishes its own flag with a
+// release store.  Every dependency has a smaller ticket, tickets are only held by running warps, so
+// spinning cannot deadlock for any grid size.
 //
-// Per TB (N lanes of the warp own one row each): gather border -> substitute -> filter -> predict row
-// in registers -> scatter+dequant coefficients -> IDCT passes -> add -> ONE store of the finished row.
-// HBM traffic per TB: N*N bytes written + 4 B per non-zero coefficient read; borders come from L2.
+// HBM traffic per TB: N*N bytes written (+ 2*N*N bytes of residual read when the TB is coded).
+#include <stdio.h>
 #include <stdlib.h>
+#include "transform.cuh"
 #include "intra.cuh"
-#include "residual.cuh"
 #include "kernels.h"
+
 
 #define INTRA_WARPS 4   // one warp per SM sub-partition; several CTAs per SM when the batch is large
 
-template <int LOG2>
-__device__ __forceinline__ void intra_tb(const FrameDev* __restrict__ f, const b265_tu tu, int16_t* wtr, uint8_t* wborder) {
-  constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE;
-  const int lane = lane_id(), grp = lane / N, sub = lane % N;
-  const bool active = grp == 0;
-  const int cidx = tu.cidx_log2 & 3;
-  uint8_t* buf0 = wborder;
-  uint8_t* buf1 = buf0 + STRIDE;
-  gather_border<LOG2>(*f, cidx, tu.x, tu.y, sub, grp, active, buf0);
-  const uint8_t* pb = filter_border<LOG2>(buf0, buf1, sub, tu.intra_mode, cidx,
-                                          (f->flags & B265_FRAME_STRONG_INTRA_SMOOTHING) != 0, active);
-  int pred[N];
-  predict_row<LOG2>(pb, sub, active ? tu.intra_mode : 1, cidx, !(tu.flags & B265_TU_NO_EDGE_FILT), pred);
-
-  const int pitch = f->pitch[cidx];
-  uint8_t* d = f->plane[cidx] + (size_t)tu.y * pitch + tu.x;
-  if (tu.ncoeff > 0) {  // warp-uniform
-    int16_t* blk = wtr;
-    __syncwarp();
-    zero_warp_scratch(wtr);
-    __syncwarp();
-    const int bounds = scatter_coeffs<LOG2>(blk, sub, f->coeffs + tu.coeff_off, active ? tu.ncoeff : 0, tu.qp, tu.flags,
-                                            cidx, (f->flags & B265_FRAME_SCALING_LIST) ? f->scaling : nullptr);
-    residual_add_store<LOG2>(blk, sub, tu.flags, bounds, active, pred, d, pitch);
-  } else if (active) {
-    store_row_u8<N>(d + sub * pitch, pred);
+// ---------------------------------------------------------------------------------------------
+// k_intra_prep: availability mask of every intra TB (one thread per TU), FrameDev::tb_mask[tu]
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_intra_prep(const FrameDev* __restrict__ frames) {
+  const FrameDev& f = frames[blockIdx.y];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < f.n_tus; i += gridDim.x * blockDim.x) {
+    const b265_tu tu = f.tus[i];
+    if (tu.intra_mode == B265_INTRA_NONE) continue;
+    const int c = tu.cidx_log2 & 3, lg = (tu.cidx_log2 >> 2) & 7;
+    IntraGeom g;
+    g.sh = (c && f.cw) ? 1 : 0;
+    g.width = f.width; g.height = f.height;
+    g.log2_ctb = f.log2_ctb; g.log2_min_tb = f.log2_min_tb;
+    g.cx = (tu.x << g.sh) >> f.log2_ctb; g.cy = (tu.y << g.sh) >> f.log2_ctb;
+    g.unit_info = (f.flags & B265_FRAME_CONSTRAINED_INTRA) ? f.unit_info : nullptr;
+    g.unit_pitch = f.width >> 2;
+    g.nb = 0;
+    const b265_ctb* ctbs = f.ctbs;
+    const b265_ctb me = ctbs ? ctbs[g.cy * f.ctbs_w + g.cx] : b265_ctb{0, 0, 0};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {  // left, upper-left, upper, upper-right
+      const int nx = g.cx + (k == 3 ? 1 : (k == 2 ? 0 : -1)), ny = g.cy - (k == 0 ? 0 : 1);
+      if (nx < 0 || ny < 0 || nx >= f.ctbs_w) continue;
+      bool ok = true;
+      if (ctbs) {
+        const b265_ctb r = ctbs[ny * f.ctbs_w + nx];
+        ok = r.slice == me.slice && r.tile == me.tile && r.addr_ts < me.addr_ts;
+      }
+      if (ok) g.nb |= 1u << k;
+    }
+    f.tb_mask[i] = intra_avail_mask(g, tu.x, tu.y, lg);
   }
-  // the next TB of this CTB (same warp) may read these samples through L2
-  __threadfence_block();
-  __syncwarp();
 }
 
-struct IntraSmem {
-  __align__(16) int16_t tr[INTRA_WARPS][B265_TR_SMEM_PER_WARP / 2];
-  __align__(16) uint8_t border[INTRA_WARPS][B265_BORDER_BYTES];
-};
+void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus) {
+  if (n_frames <= 0 || max_tus <= 0) return;
+  int gx = (max_tus + 255) / 256;
+  if (gx > 592) gx = 592;
+  k_intra_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames);
+}
+
+// ---------------------------------------------------------------------------------------------
+// the wavefront
+// ---------------------------------------------------------------------------------------------
+// residual line `l` of a coded TB (written by k_residual_sparse<LOG2, true>, transposed for modes 2..17)
+template <int N>
+__device__ __forceinline__ void load_resid_line(const int16_t* __restrict__ p, uint32_t (&w)[N / 2]) {
+  if (N == 4) {
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+    w[0] = v.x; w[1] = v.y;
+  } else {
+#pragma unroll
+    for (int q = 0; q < N / 8; q++) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + q);
+      w[4 * q] = v.x; w[4 * q + 1] = v.y; w[4 * q + 2] = v.z; w[4 * q + 3] = v.w;
+    }
+  }
+}
+
+template <int N>
+__device__ __forceinline__ void store_words(uint8_t* p, const uint32_t (&px)[N / 4]) {
+  if (N == 4) *reinterpret_cast<uint32_t*>(p) = px[0];
+  else if (N == 8) *reinterpret_cast<uint2*>(p) = make_uint2(px[0], px[1]);
+  else {
+#pragma unroll
+    for (int q = 0; q < N / 16; q++)
+      reinterpret_cast<uint4*>(p)[q] = make_uint4(px[4 * q], px[4 * q + 1], px[4 * q + 2], px[4 * q + 3]);
+  }
+}
+// the edge store is only 4-byte aligned in general
+template <int N>
+__device__ __forceinline__ void store_words_smem(uint8_t* p, const uint32_t (&px)[N / 4]) {
+#pragma unroll
+  for (int q = 0; q < N / 4; q++) reinterpret_cast<uint32_t*>(p)[q] = px[q];
+}
+
+template <int LOG2, bool TRACE>
+__device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, int cidx, int x, int y, int mode, int flags,
+                                         bool coded, uint64_t M, uint8_t* wborder, long long (&acc)[4]) {
+  constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE;
+  long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+  if (TRACE) c0 = clock64();
+  const int lane = lane_id();
+  const bool active = lane < N;
+  const int l = active ? lane : 0;
+  // the residual line is independent of the neighbours: issue its load first
+  uint32_t r[N / 2];
+  if (coded && active) load_resid_line<N>(g.resid + (size_t)(y + l) * g.pitch + x, r);
+  const int xr = x - E.x0, yr = y - E.y0;
+  uint8_t* buf0 = wborder;
+  uint8_t* buf1 = buf0 + STRIDE;
+  gather_border<LOG2>(E, xr, yr, M, lane, buf0);
+  if (TRACE) c1 = clock64();
+  uint8_t* pb = filter_border<LOG2>(buf0, buf1, lane, mode, cidx, g.strong);
+  if (TRACE) c2 = clock64();
+  uint32_t h[N / 2];
+  const bool by_column = predict_line<LOG2>(pb, lane, mode, cidx, !(flags & B265_TU_NO_EDGE_FILT), h);
+  if (TRACE) c3 = clock64();
+  if (active) {
+    uint32_t px[N / 4];
+    finish_line<N>(h, r, coded, px);
+    uint8_t* d = g.plane + (size_t)y * g.pitch + x;
+    uint8_t* erow = E.rows + ((yr + N) >> 2) * E.rstride + 16 + xr;   // row below the TB's last row ... i.e. its bottom row
+    uint8_t* ecol = E.cols + ((xr + N) >> 2) * E.S + yr;              // its right column
+    // The corner sample of a later TB lies on an edge row AND an edge column but only needs to be this TB's
+    // bottom row OR right column: the right column is therefore also entered into the edge rows it crosses.
+    if (!by_column) {   // lane = row
+      store_words<N>(d + (size_t)l * g.pitch, px);
+      ecol[l] = (uint8_t)(px[N / 4 - 1] >> 24);
+      if ((l & 3) == 3) E.rows[((yr + l + 1) >> 2) * E.rstride + 16 + xr + N - 1] = (uint8_t)(px[N / 4 - 1] >> 24);
+      if (l == N - 1) store_words_smem<N>(erow, px);
+    } else {            // lane = column
+#pragma unroll
+      for (int j = 0; j < N; j++) d[(size_t)j * g.pitch + l] = (uint8_t)(px[j >> 2] >> (8 * (j & 3)));
+      erow[l] = (uint8_t)(px[N / 4 - 1] >> 24);
+      if (l == N - 1) {
+        store_words_smem<N>(ecol, px);
+#pragma unroll
+        for (int q = 0; q < N / 4; q++) E.rows[((yr + 4 * q + 4) >> 2) * E.rstride + 16 + xr + N - 1] = (uint8_t)(px[q] >> 24);
+      }
+    }
+  }
+  __syncwarp();  // the next TB of this CTB reads the edge store
+  if (TRACE) {
+    acc[0] += c1 - c0; acc[1] += c2 - c1; acc[2] += c3 - c2; acc[3] += clock64() - c3;
+  }
+}
 
 __device__ __forceinline__ void wait_flag(const uint8_t* flag, unsigned sleep_ns) {
   // relaxed polling (no L1 invalidation per iteration); the caller issues one acquire fence afterwards
@@ -68,35 +166,133 @@ __device__ __forceinline__ void wait_flag(const uint8_t* flag, unsigned sleep_ns
   }
 }
 
-__global__ void __launch_bounds__(INTRA_WARPS * 32, 4)
+// Copy the samples bordering the CTB (and, for CTBs that also hold inter/PCM samples, the edge rows/columns
+// of the CTB itself) from L2 into the edge store.  Called by the whole warp after the neighbour flags have
+// been acquired.  Loads are issued back to back (one L2 round trip), then stored.
+__device__ __forceinline__ void fill_edges(const IntraGeom& g, const CtbEdges& E, bool interior) {
+  const int lane = lane_id();
+  const int S = E.S, pitch = g.pitch;
+  const int W = (g.width + g.sh) >> g.sh, H = (g.height + g.sh) >> g.sh;
+  const uint8_t* org = g.plane + (size_t)E.y0 * pitch + E.x0;
+  // row -1: columns 0..2S-1 as words (the plane width is a multiple of 4): S/2 <= 32 words; corner by lane 31
+  uint32_t top = 0, corner = 0, left[2] = {0, 0};
+  const bool has_top = g.cy > 0 && lane < S / 2 && E.x0 + 4 * lane < W;
+  if (has_top) top = ld_cg_u32(org - pitch + 4 * lane);
+  const bool has_corner = g.cy > 0 && g.cx > 0 && lane == 31;
+  if (has_corner) corner = ld_cg_u8(org - pitch - 1);
+#pragma unroll
+  for (int k = 0; k < 2; k++) {  // column -1: S <= 64 rows
+    const int r = lane + 32 * k;
+    if (g.cx > 0 && r < S && E.y0 + r < H) left[k] = ld_cg_u8(org + (size_t)r * pitch - 1);
+  }
+  if (has_top) *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * lane) = top;
+  if (has_corner) E.rows[15] = (uint8_t)corner;
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const int r = lane + 32 * k;
+    if (g.cx > 0 && r < S) {
+      E.cols[r] = (uint8_t)left[k];
+      if ((r & 3) == 3) E.rows[((r + 1) >> 2) * E.rstride + 15] = (uint8_t)left[k];  // sample (-1, r) of the inner edge rows
+    }
+  }
+  if (interior) {
+    // rows 4q-1 (q >= 1), columns 0..S-1
+    const int wpr = S / 4;
+    for (int i = lane; i < (S / 4) * wpr; i += 32) {
+      const int q = 1 + i / wpr, w = i % wpr, r = 4 * q - 1;
+      if (E.y0 + r < H && E.x0 + 4 * w < W)
+        *reinterpret_cast<uint32_t*>(E.rows + q * E.rstride + 16 + 4 * w) = ld_cg_u32(org + (size_t)r * pitch + 4 * w);
+    }
+    // columns 4q-1 (q >= 1), rows 0..S-1
+    for (int i = lane; i < (S / 4) * S; i += 32) {
+      const int q = 1 + i / S, r = i % S, cidx = 4 * q - 1;
+      if (E.y0 + r < H && E.x0 + cidx < W) E.cols[q * S + r] = ld_cg_u8(org + (size_t)r * pitch + cidx);
+    }
+  }
+  __syncwarp();
+}
+
+// TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 8 x uint64 {t_ticket, t_deps, t_tile, t_tbs, t_pub,
+// n_tbs, gather, filter} + 4 more {predict, add+store, globaltimer, sm id}: 12 x uint64 per ticket, SM cycles
+template <bool TRACE>
+__global__ void __launch_bounds__(INTRA_WARPS * 32)
 k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __restrict__ tickets, int n_tickets,
-                  unsigned* __restrict__ ticket, unsigned sleep_ns) {
-  __shared__ IntraSmem sm;
+                  unsigned* __restrict__ ticket, unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
+  extern __shared__ __align__(16) uint8_t dyn_smem[];
+  __shared__ __align__(16) uint8_t s_border[INTRA_WARPS][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
+  uint8_t* my_edges = dyn_smem + (size_t)warp * tile_bytes;
   for (;;) {
     unsigned t = 0;
     if (lane == 0) t = atomicAdd(ticket, 1u);
     t = __shfl_sync(B265_FULL_MASK, t, 0);
     if (t >= (unsigned)n_tickets) break;
+    long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
+    unsigned long long gt0 = 0;
+    int n_tbs = 0;
+    long long acc[4] = {0, 0, 0, 0};
+    if (TRACE) {
+      tr0 = clock64();
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
+    }
     const IntraTicket tk = tickets[t];
-    const FrameDev* f = frames + tk.frame;
+    const FrameDev* __restrict__ f = frames + tk.frame;
     const int c = tk.plane;
-    const int cx = tk.ctb % f->ctbs_w, cy = tk.ctb / f->ctbs_w;
-    // prefetch the first 32 TU records of the CTB while waiting for the neighbours
+    // picture constants -> registers (independent loads, one round trip)
+    IntraGeom g;
+    const int ctbs_w = f->ctbs_w;
+    const uint32_t fflags = f->flags;
+    const b265_ctb* __restrict__ ctbs = f->ctbs;
+    uint8_t* done = f->done[c];
     const uint4* tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
+    const uint2* masks = reinterpret_cast<const uint2*>(f->tb_mask);
+    g.sh = (c && f->cw) ? 1 : 0;
+    g.width = f->width; g.height = f->height;
+    g.log2_ctb = f->log2_ctb; g.log2_min_tb = f->log2_min_tb;
+    g.plane = f->plane[c]; g.resid = f->resid[c]; g.pitch = f->pitch[c];
+    g.unit_info = (fflags & B265_FRAME_CONSTRAINED_INTRA) ? f->unit_info : nullptr;
+    g.unit_pitch = g.width >> 2;
+    g.strong = (fflags & B265_FRAME_STRONG_INTRA_SMOOTHING) != 0;
+    g.cx = tk.ctb % ctbs_w; g.cy = tk.ctb / ctbs_w;
+    const int cx = g.cx, cy = g.cy;
+    // prefetch the first 32 TU records of the CTB while waiting for the neighbours
     uint4 mine = make_uint4(0, 0xff000000u, 0, 0);
-    if ((uint32_t)lane < tk.tu_count) mine = tus4[tk.tu_first + lane];
-    // neighbours: left, upper-left, upper, upper-right
-    if (lane < 4) {
-      const int nx = cx + (lane == 3 ? 1 : (lane == 2 ? 0 : -1)), ny = cy - (lane == 0 ? 0 : 1);
-      if (nx >= 0 && ny >= 0 && nx < f->ctbs_w) wait_flag(f->done[c] + ny * f->ctbs_w + nx, sleep_ns);
+    uint2 mymask = make_uint2(0, 0);
+    if ((uint32_t)lane < tk.tu_count) {
+      mine = __ldg(tus4 + tk.tu_first + lane);
+      mymask = __ldg(masks + tk.tu_first + lane);
+    }
+    CtbEdges E;
+    E.S = (1 << g.log2_ctb) >> g.sh;
+    E.rstride = 2 * E.S + 16;
+    E.rows = my_edges;
+    E.cols = my_edges + (E.S / 4 + 1) * E.rstride;
+    E.x0 = cx * E.S;
+    E.y0 = cy * E.S;
+    // neighbours: lane 0 left, 1 upper-left, 2 upper, 3 upper-right; lane 4 reads this CTB's own record
+    {
+      const int nx = cx + (lane == 3 ? 1 : (lane == 2 || lane == 4 ? 0 : -1)), ny = cy - (lane == 0 || lane == 4 ? 0 : 1);
+      const bool exists = lane < 5 && nx >= 0 && ny >= 0 && nx < ctbs_w;
+      b265_ctb rec = {0, 0, 0};
+      if (exists && ctbs) rec = ctbs[ny * ctbs_w + nx];
+      if (exists && lane < 4) wait_flag(done + ny * ctbs_w + nx, sleep_ns);
+      const int my_ts = __shfl_sync(B265_FULL_MASK, rec.addr_ts, 4);
+      const int my_slice = __shfl_sync(B265_FULL_MASK, (int)rec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)rec.tile, 4);
+      const bool usable = exists && lane < 4 && (!ctbs || (rec.slice == my_slice && rec.tile == my_tile_id && rec.addr_ts < my_ts));
+      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;
     }
     fence_acq_rel_gpu();
     __syncwarp();
+    if (TRACE) tr1 = clock64();
+    fill_edges(g, E, (tk.flags & B265_TICKET_MIXED) != 0);
+    if (TRACE) tr2 = clock64();
     for (uint32_t base = 0; base < tk.tu_count; base += 32) {
       if (base) {
         mine = make_uint4(0, 0xff000000u, 0, 0);
-        if (base + lane < tk.tu_count) mine = tus4[tk.tu_first + base + lane];
+        if (base + lane < tk.tu_count) {
+          mine = __ldg(tus4 + tk.tu_first + base + lane);
+          mymask = __ldg(masks + tk.tu_first + base + lane);
+        }
       }
       const int n_here = min(32u, tk.tu_count - base);
       // lanes whose TU is an intra TB of this plane
@@ -105,56 +301,82 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
       while (todo) {
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
-        b265_tu tu;
-        {
-          const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
-          tu.x = (uint16_t)(r0 & 0xffff);
-          tu.y = (uint16_t)(r0 >> 16);
-          tu.cidx_log2 = (uint8_t)(r1 & 0xff);
-          tu.flags = (uint8_t)((r1 >> 8) & 0xff);
-          tu.qp = (uint8_t)((r1 >> 16) & 0xff);
-          tu.intra_mode = (uint8_t)(r1 >> 24);
-          tu.coeff_off = __shfl_sync(B265_FULL_MASK, mine.z, src);
-          tu.ncoeff = (uint16_t)(__shfl_sync(B265_FULL_MASK, mine.w, src) & 0xffff);
-          tu.reserved = 0;
-        }
-        switch ((tu.cidx_log2 >> 2) & 7) {
-          case 2: intra_tb<2>(f, tu, sm.tr[warp], sm.border[warp]); break;
-          case 3: intra_tb<3>(f, tu, sm.tr[warp], sm.border[warp]); break;
-          case 4: intra_tb<4>(f, tu, sm.tr[warp], sm.border[warp]); break;
-          default: intra_tb<5>(f, tu, sm.tr[warp], sm.border[warp]); break;
+        const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
+        const uint32_t r3 = __shfl_sync(B265_FULL_MASK, mine.w, src);
+        const int x = (int)(r0 & 0xffff), y = (int)(r0 >> 16);
+        const int flags = (int)((r1 >> 8) & 0xff), mode = (int)(r1 >> 24);
+        const bool coded = (r3 & 0xffff) != 0;
+        const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
+                           ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
+        if (TRACE) n_tbs++;
+        switch ((r1 >> 2) & 7) {
+          case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+          case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+          case 4: intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+          default: intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
         }
       }
     }
     // publish: every sample of this CTB plane is final (pre-deblock) now
-    __threadfence();
+    // (bar.warp.sync orders the other lanes' stores before lane 0's release store, which is cumulative)
+    if (TRACE) tr3 = clock64();
     __syncwarp();
-    if (lane == 0) st_release_u8(f->done[c] + tk.ctb, 1);
+    if (lane == 0) st_release_u8(done + tk.ctb, 1);
     __syncwarp();
+    if (TRACE && lane == 0) {
+      unsigned smid;
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+      unsigned long long* o = trace + (size_t)t * 12;
+      o[0] = tr0; o[1] = tr1; o[2] = tr2; o[3] = tr3; o[4] = clock64(); o[5] = n_tbs; o[6] = acc[0]; o[7] = acc[1];
+      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = smid;
+    }
   }
 }
 
-int intra_max_resident_ctas(int sm_count) {
+static int tile_bytes_for(int log2_ctb) { return (ctb_edges_bytes(1 << log2_ctb) + 15) & ~15; }
+
+int intra_max_resident_ctas(int sm_count, int log2_ctb) {
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intra_wavefront, INTRA_WARPS * 32, 0);
+  const size_t dyn = (size_t)INTRA_WARPS * tile_bytes_for(log2_ctb);
+  cudaFuncSetAttribute(k_intra_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  cudaFuncSetAttribute(k_intra_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intra_wavefront<false>, INTRA_WARPS * 32, dyn);
   if (per_sm < 1) per_sm = 1;
   return per_sm * sm_count;
 }
 
 void launch_intra(cudaStream_t st, const FrameDev* frames, const IntraTicket* tickets, int n_tickets, unsigned* ticket,
-                  int max_ctas, int wave_width) {
+                  int sm_count, int wave_width, int log2_ctb) {
   if (n_tickets <= 0) return;
+  static int max_ctas[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (!max_ctas[log2_ctb & 7]) max_ctas[log2_ctb & 7] = intra_max_resident_ctas(sm_count, log2_ctb);
   // warps beyond ~3 waves' worth would only poll; keep them off the SMs the working warps run on
   int want = 3 * wave_width;
-  if (want < 296) want = 296;
+  if (want < 2 * sm_count) want = 2 * sm_count;
   if (want > n_tickets) want = n_tickets;
   int ctas = (want + INTRA_WARPS - 1) / INTRA_WARPS;
-  if (ctas > max_ctas) ctas = max_ctas;
+  if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
   cudaMemsetAsync(ticket, 0, sizeof(unsigned), st);
   static int sleep_ns = -1;
   if (sleep_ns < 0) {
     const char* e = getenv("B265_INTRA_SLEEP_NS");
     sleep_ns = e ? atoi(e) : 100;
   }
-  k_intra_wavefront<<<ctas, INTRA_WARPS * 32, 0, st>>>(frames, tickets, n_tickets, ticket, (unsigned)sleep_ns);
+  const int tb = tile_bytes_for(log2_ctb);
+  static const char* trace_path = getenv("B265_INTRA_TRACE");
+  if (trace_path) {  // developer aid: synchronous, one file per process (last launch wins)
+    unsigned long long* d = nullptr;
+    cudaMalloc((void**)&d, (size_t)n_tickets * 96);
+    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, tickets, n_tickets, ticket,
+                                                                                     (unsigned)sleep_ns, tb, d);
+    cudaStreamSynchronize(st);
+    unsigned long long* h = (unsigned long long*)malloc((size_t)n_tickets * 96);
+    cudaMemcpy(h, d, (size_t)n_tickets * 96, cudaMemcpyDeviceToHost);
+    if (FILE* fp = fopen(trace_path, "wb")) { fwrite(h, 96, (size_t)n_tickets, fp); fclose(fp); }
+    free(h);
+    cudaFree(d);
+    return;
+  }
+  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, tickets, n_tickets, ticket,
+                                                                                    (unsigned)sleep_ns, tb, nullptr);
 }

@@ -74,7 +74,7 @@ k_residual_dense(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__
 // Sparse work-list form. order[] lists TUs (frame<<24 | index) of ONE size; the prediction is read
 // from the destination plane (written by the MC kernel of an earlier launch).
 // ---------------------------------------------------------------------------------------------
-template <int LOG2>
+template <int LOG2, bool SCRATCH>
 __global__ void __launch_bounds__(B265_WARPS_PER_CTA * 32)
 k_residual_sparse(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ order, int n) {
   constexpr int N = TrBlk<LOG2>::N, G = 32 / N;
@@ -99,15 +99,25 @@ k_residual_sparse(const FrameDev* __restrict__ frames, const uint32_t* __restric
     const int cidx = tu.cidx_log2 & 3;
     int bounds = scatter_coeffs<LOG2>(blk, sub, f->coeffs + tu.coeff_off, active ? tu.ncoeff : 0, tu.qp,
                                       tu.flags, cidx, (f->flags & B265_FRAME_SCALING_LIST) ? f->scaling : nullptr);
-    int pred[N];
-    uint8_t* d = nullptr;
-    int pitch = 0;
-    if (active) {
-      pitch = f->pitch[cidx];
-      d = f->plane[cidx] + (size_t)tu.y * pitch + tu.x;
-      load_row_u8<N>(d + sub * pitch, pred);
+    if (SCRATCH) {
+      int16_t* d = nullptr;
+      int pitch = 0;
+      if (active) {
+        pitch = f->pitch[cidx];
+        d = f->resid[cidx] + (size_t)tu.y * pitch + tu.x;
+      }
+      residual_store_scratch<LOG2>(blk, sub, tu.flags, bounds, active, d, pitch, tu.intra_mode >= 2 && tu.intra_mode < 18);
+    } else {
+      int pred[N];
+      uint8_t* d = nullptr;
+      int pitch = 0;
+      if (active) {
+        pitch = f->pitch[cidx];
+        d = f->plane[cidx] + (size_t)tu.y * pitch + tu.x;
+        load_row_u8<N>(d + sub * pitch, pred);
+      }
+      residual_add_store<LOG2>(blk, sub, tu.flags, bounds, active, pred, d, pitch);
     }
-    residual_add_store<LOG2>(blk, sub, tu.flags, bounds, active, pred, d, pitch);
   }
 }
 
@@ -128,7 +138,7 @@ void launch_residual_dense(cudaStream_t st, int log2, int kind, int rdpcm, int n
 }
 
 void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order,
-                            int n, int sm_count) {
+                            int n, int sm_count, bool to_scratch) {
   if (n <= 0) return;
   const int G = 32 >> log2;
   int warps = (n + G - 1) / G;
@@ -136,9 +146,13 @@ void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, c
   int grid = min(ctas, sm_count * 8);
   dim3 b(B265_WARPS_PER_CTA * 32);
   switch (log2) {
-    case 2: k_residual_sparse<2><<<grid, b, 0, st>>>(frames, order, n); break;
-    case 3: k_residual_sparse<3><<<grid, b, 0, st>>>(frames, order, n); break;
-    case 4: k_residual_sparse<4><<<grid, b, 0, st>>>(frames, order, n); break;
-    default: k_residual_sparse<5><<<grid, b, 0, st>>>(frames, order, n); break;
+    case 2: to_scratch ? k_residual_sparse<2, true><<<grid, b, 0, st>>>(frames, order, n)
+                       : k_residual_sparse<2, false><<<grid, b, 0, st>>>(frames, order, n); break;
+    case 3: to_scratch ? k_residual_sparse<3, true><<<grid, b, 0, st>>>(frames, order, n)
+                       : k_residual_sparse<3, false><<<grid, b, 0, st>>>(frames, order, n); break;
+    case 4: to_scratch ? k_residual_sparse<4, true><<<grid, b, 0, st>>>(frames, order, n)
+                       : k_residual_sparse<4, false><<<grid, b, 0, st>>>(frames, order, n); break;
+    default: to_scratch ? k_residual_sparse<5, true><<<grid, b, 0, st>>>(frames, order, n)
+                        : k_residual_sparse<5, false><<<grid, b, 0, st>>>(frames, order, n); break;
   }
 }

@@ -84,3 +84,50 @@ __device__ __forceinline__ void residual_add_store(int16_t* blk, int sub, int fl
     store_row_u8<N>(dst + sub * pitch, pred);
   }
 }
+
+// Scratch form for intra TBs: the residual rows go to an int16 plane (row pitch in samples) and are
+// added to the prediction later by the intra wavefront.  Values are clamped to +-1024, which is exact:
+// Clip1(pred + r) only depends on r clamped to [-255, 255].  `transposed` stores element (row y, col x) of
+// the block at dst[x * pitch + y] (the wavefront predicts modes 2..17 column-wise, intra.cuh).
+__device__ __forceinline__ int clip_res(int v) { return min(max(v, -1024), 1023); }
+
+template <int LOG2>
+__device__ __forceinline__ void residual_store_scratch(int16_t* blk, int sub, int flags, int bounds, bool active,
+                                                       int16_t* dst, int pitch, bool transposed) {
+  constexpr int N = TrBlk<LOG2>::N, S = TrBlk<LOG2>::S;
+  const bool vert = active && (flags & B265_TU_RDPCM_V) && (flags & (B265_TU_SKIP | B265_TU_BYPASS));
+  if (__any_sync(B265_FULL_MASK, vert)) {
+    if (vert) {  // lane `sub` accumulates down column `sub`
+      int acc = 0;
+      for (int y = 0; y < N; y++) {
+        int c = blk[y * S + sub];
+        int v = (flags & B265_TU_BYPASS) ? c : (((c << (5 + LOG2)) + 2048) >> 12);
+        acc += v;
+        dst[transposed ? (size_t)sub * pitch + y : (size_t)y * pitch + sub] = (int16_t)clip_res(acc);
+      }
+    }
+    __syncwarp();
+    active = active && !vert;
+  }
+  int r[N];
+  residual_rows<LOG2>(blk, sub, flags, bounds & 0xff, bounds >> 8, active, r);
+  if (active && transposed) {
+#pragma unroll
+    for (int x = 0; x < N; x++) dst[(size_t)x * pitch + sub] = (int16_t)clip_res(r[x]);
+  } else if (active) {
+    uint32_t* d = reinterpret_cast<uint32_t*>(dst + (size_t)sub * pitch);
+    if (N == 4) {
+      *reinterpret_cast<uint2*>(d) = make_uint2((uint32_t)(clip_res(r[0]) & 0xffff) | ((uint32_t)clip_res(r[1]) << 16),
+                                                (uint32_t)(clip_res(r[2]) & 0xffff) | ((uint32_t)clip_res(r[3]) << 16));
+    } else {
+#pragma unroll
+      for (int q = 0; q < N / 8; q++) {
+        uint32_t w[4];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+          w[k] = (uint32_t)(clip_res(r[8 * q + 2 * k]) & 0xffff) | ((uint32_t)clip_res(r[8 * q + 2 * k + 1]) << 16);
+        reinterpret_cast<uint4*>(d)[q] = make_uint4(w[0], w[1], w[2], w[3]);
+      }
+    }
+  }
+}
