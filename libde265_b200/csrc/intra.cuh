@@ -18,6 +18,7 @@
 //  * modes 2..17 are predicted with the lane owning a COLUMN (the main reference is the left line), all
 //    other modes with the lane owning a ROW.
 #pragma once
+#include <type_traits>
 #include "common.cuh"
 
 #define B265_BORDER_BYTES 512  // per warp: 2 buffers x (6N+8) bytes, N <= 32
@@ -109,36 +110,42 @@ __host__ __device__ constexpr int ctb_edges_bytes(int S) { return (S / 4 + 1) * 
 // Border of the TB at (xr,yr) relative to the CTB origin -> buf (IntraBuf layout), with the reference
 // sample substitution of intrapred.cc:395-431: a missing unit copies the nearest available sample before it
 // in scan order, leading missing units copy the first available sample, nothing available -> 128.
-// Called by all lanes of the warp.
+// Branch-free: every lane resolves its scan unit to a source unit t (itself, the nearest available one
+// before it, or the first available one), loads that unit's word from the edge store and picks the bytes
+// with one PRMT.  Called by all lanes of the warp.
 template <int LOG2>
-__device__ __forceinline__ void gather_border(const CtbEdges& E, int xr, int yr, uint64_t M, int lane, uint8_t* buf) {
+__device__ __forceinline__ void gather_border(const CtbEdges& E, int xr, int yr, uint64_t M64, int lane, uint8_t* buf) {
   constexpr int N = 1 << LOG2, H = N / 2;
-  const uint8_t* colp = E.cols + (xr >> 2) * E.S;             // column xr-1, indexed by relative row
-  const uint8_t* rowp = E.rows + (yr >> 2) * E.rstride + 16;  // row yr-1, indexed by relative column
-  auto sample = [&](int t, bool last) -> uint32_t {  // first / last sample (scan order) of scan unit t
-    if (t < H) return colp[yr + 4 * (H - 1 - t) + (last ? 0 : 3)];
-    if (t == H) return rowp[xr - 1];
-    return rowp[xr + 4 * (t - H - 1) + (last ? 3 : 0)];
+  typedef typename std::conditional<(N == 32), uint64_t, uint32_t>::type mask_t;   // N + 1 scan units
+  const mask_t M = (mask_t)M64;
+  const uint8_t* colp = E.cols + (xr >> 2) * E.S + yr;                   // column xr-1, from the TB's first row down
+  const uint8_t* rowp = E.rows + (yr >> 2) * E.rstride + 16 + xr;        // row yr-1, from the TB's first column on
+  auto fetch = [&](int s) -> uint32_t {
+    const bool av = (M >> s) & 1;
+    const mask_t lower = M & (((mask_t)1 << s) - 1);
+    int t, pick;  // pick: 0 = the unit itself, 1 = its last sample in scan order, 2 = its first sample
+    if (N == 32) {
+      t = av ? s : (lower ? 63 - __clzll((long long)lower) : __ffsll((long long)M) - 1);
+    } else {
+      t = av ? s : (lower ? 31 - __clz((int)lower) : __ffs((int)M) - 1);
+    }
+    pick = av ? 0 : (lower ? 1 : 2);
+    if (M == 0) t = H;
+    // unit t as a word: left units run down the column, the corner is the last byte of the word before the row
+    const uint8_t* a = t < H ? colp + 4 * (H - 1 - t) : rowp + 4 * (t - H - 1);
+    const uint32_t w = *reinterpret_cast<const uint32_t*>(a);
+    // scan order runs UP the left column (last sample = byte 0) and RIGHT along the top row (last = byte 3)
+    const bool byte0 = (t < H) ? (pick == 1) : (pick == 2 && t != H);
+    const uint32_t sel = (pick == 0 && t != H) ? 0x3210u : (byte0 ? 0x0000u : 0x3333u);
+    return M ? __byte_perm(w, 0, sel) : 0x80808080u;
   };
-  auto subst = [&](int s) -> uint32_t {
-    if (M == 0) return 128;
-    const uint64_t lower = M & ((1ull << s) - 1ull);
-    if (lower) return sample(63 - __clzll((long long)lower), true);
-    return sample(__ffsll((long long)M) - 1, false);
-  };
-  if (lane < N) {
-    const bool left = lane < H;
-    const int w = left ? lane : lane - H;        // word of the line: samples 1+4w .. 4+4w
-    const int s = left ? H - 1 - lane : H + 1 + w;
-    uint32_t v;
-    if ((M >> s) & 1ull)
-      v = left ? *reinterpret_cast<const uint32_t*>(colp + yr + 4 * w) : *reinterpret_cast<const uint32_t*>(rowp + xr + 4 * w);
-    else
-      v = subst(s) * 0x01010101u;
-    *reinterpret_cast<uint32_t*>(buf + (left ? IntraBuf<N>::LEFT : IntraBuf<N>::TOP) + 1 + 4 * w) = v;
-  }
-  if (lane == (N < 32 ? N : 0)) {
-    const uint32_t c = ((M >> H) & 1ull) ? (uint32_t)rowp[xr - 1] : subst(H);
+  const bool left = lane < H;
+  const int wi = left ? lane : lane - H;                           // word of the line: samples 1+4w .. 4+4w
+  const int s = lane < N ? (left ? H - 1 - lane : lane + 1) : H;   // scan unit of this lane
+  const uint32_t v = fetch(s);
+  const uint32_t c = fetch(H);
+  if (lane < N) *reinterpret_cast<uint32_t*>(buf + (left ? IntraBuf<N>::LEFT : IntraBuf<N>::TOP) + 1 + 4 * wi) = v;
+  if (lane == 0) {
     buf[IntraBuf<N>::TOP] = (uint8_t)c;
     buf[IntraBuf<N>::LEFT] = (uint8_t)c;
   }

@@ -159,9 +159,16 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
   }
 }
 
-__device__ __forceinline__ void wait_flag(const uint8_t* flag, unsigned sleep_ns) {
-  // relaxed polling (no L1 invalidation per iteration); the caller issues one acquire fence afterwards
-  while (ld_relaxed_u8(flag) == 0) {
+// Wait until the (up to four) flags polled by lanes 0..3 are set.  The loop is executed by the WHOLE warp
+// with a warp-uniform exit condition: a per-lane polling loop leaves the warp split into independently
+// scheduled groups, which then walk the TBs separately and pay the slow path of every warp collective.
+// Acquire loads: the poll that sees the flag set orders the sample loads that follow (no separate fence
+// on the path between two dependent CTBs); the vote extends the ordering to the other lanes.
+__device__ __forceinline__ void wait_flags(const uint8_t* flag, bool polls, unsigned sleep_ns) {
+  for (;;) {
+    unsigned v = 1;
+    if (polls) v = ld_acquire_u8(flag);
+    if (__all_sync(B265_FULL_MASK, v != 0)) break;
     if (sleep_ns) __nanosleep(sleep_ns);
   }
 }
@@ -215,37 +222,39 @@ __device__ __forceinline__ void fill_edges(const IntraGeom& g, const CtbEdges& E
 // TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 8 x uint64 {t_ticket, t_deps, t_tile, t_tbs, t_pub,
 // n_tbs, gather, filter} + 4 more {predict, add+store, globaltimer, sm id}: 12 x uint64 per ticket, SM cycles
 template <bool TRACE>
-__global__ void __launch_bounds__(INTRA_WARPS * 32)
+__global__ void __launch_bounds__(INTRA_WARPS * 32, 4)
 k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __restrict__ tickets, int n_tickets,
                   unsigned* __restrict__ ticket, unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ __align__(16) uint8_t s_border[INTRA_WARPS][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
   uint8_t* my_edges = dyn_smem + (size_t)warp * tile_bytes;
-  for (;;) {
-    unsigned t = 0;
-    if (lane == 0) t = atomicAdd(ticket, 1u);
-    t = __shfl_sync(B265_FULL_MASK, t, 0);
-    if (t >= (unsigned)n_tickets) break;
-    long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
-    unsigned long long gt0 = 0;
-    int n_tbs = 0;
-    long long acc[4] = {0, 0, 0, 0};
-    if (TRACE) {
-      tr0 = clock64();
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
-    }
-    const IntraTicket tk = tickets[t];
-    const FrameDev* __restrict__ f = frames + tk.frame;
-    const int c = tk.plane;
-    // picture constants -> registers (independent loads, one round trip)
-    IntraGeom g;
-    const int ctbs_w = f->ctbs_w;
+  // Software pipeline over tickets: the next ticket number is drawn while the current CTB is walked, its
+  // record is loaded during the TB loop and its picture constants are loaded before the (slow) release
+  // store of the current CTB, so that none of these round trips sits between two dependent CTBs.
+  // Holding a reserved ticket cannot deadlock: the smallest unfinished ticket is always being processed
+  // (a warp reserves ticket B only while processing a smaller ticket A and then processes B next).
+  unsigned t = 0;
+  if (lane == 0) t = atomicAdd(ticket, 1u);
+  t = __shfl_sync(B265_FULL_MASK, t, 0);
+  IntraTicket tk = {0, 0, 0, 0, 0, 0};
+  if (t < (unsigned)n_tickets) tk = tickets[t];
+  // picture constants of the ticket -> registers (independent loads, one round trip)
+  IntraGeom g;
+  int ctbs_w = 1;
+  const b265_ctb* __restrict__ ctbs = nullptr;
+  uint8_t* done = nullptr;
+  const uint4* tus4 = nullptr;
+  const uint2* masks = nullptr;
+  auto load_constants = [&](const IntraTicket& k) {
+    const FrameDev* __restrict__ f = frames + k.frame;
+    const int c = k.plane;
     const uint32_t fflags = f->flags;
-    const b265_ctb* __restrict__ ctbs = f->ctbs;
-    uint8_t* done = f->done[c];
-    const uint4* tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
-    const uint2* masks = reinterpret_cast<const uint2*>(f->tb_mask);
+    ctbs_w = f->ctbs_w;
+    ctbs = f->ctbs;
+    done = f->done[c];
+    tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
+    masks = reinterpret_cast<const uint2*>(f->tb_mask);
     g.sh = (c && f->cw) ? 1 : 0;
     g.width = f->width; g.height = f->height;
     g.log2_ctb = f->log2_ctb; g.log2_min_tb = f->log2_min_tb;
@@ -253,6 +262,21 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     g.unit_info = (fflags & B265_FRAME_CONSTRAINED_INTRA) ? f->unit_info : nullptr;
     g.unit_pitch = g.width >> 2;
     g.strong = (fflags & B265_FRAME_STRONG_INTRA_SMOOTHING) != 0;
+  };
+  if (t < (unsigned)n_tickets) load_constants(tk);
+  while (t < (unsigned)n_tickets) {
+    long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
+    unsigned long long gt0 = 0;
+    int n_tbs = 0;
+    long long acc[4] = {0, 0, 0, 0};
+    long long lacc = 0;
+    if (TRACE) {
+      tr0 = clock64();
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
+    }
+    unsigned t_next = 0;
+    if (lane == 0) t_next = atomicAdd(ticket, 1u);   // consumed after fill_edges
+    const int c = tk.plane;
     g.cx = tk.ctb % ctbs_w; g.cy = tk.ctb / ctbs_w;
     const int cx = g.cx, cy = g.cy;
     // prefetch the first 32 TU records of the CTB while waiting for the neighbours
@@ -275,17 +299,19 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
       const bool exists = lane < 5 && nx >= 0 && ny >= 0 && nx < ctbs_w;
       b265_ctb rec = {0, 0, 0};
       if (exists && ctbs) rec = ctbs[ny * ctbs_w + nx];
-      if (exists && lane < 4) wait_flag(done + ny * ctbs_w + nx, sleep_ns);
+      wait_flags(done + ny * ctbs_w + nx, exists && lane < 4, sleep_ns);
       const int my_ts = __shfl_sync(B265_FULL_MASK, rec.addr_ts, 4);
       const int my_slice = __shfl_sync(B265_FULL_MASK, (int)rec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)rec.tile, 4);
       const bool usable = exists && lane < 4 && (!ctbs || (rec.slice == my_slice && rec.tile == my_tile_id && rec.addr_ts < my_ts));
-      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;
+      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;   // (bar.warp.sync semantics: the acquire of lanes 0-3 covers the warp)
     }
-    fence_acq_rel_gpu();
-    __syncwarp();
     if (TRACE) tr1 = clock64();
     fill_edges(g, E, (tk.flags & B265_TICKET_MIXED) != 0);
     if (TRACE) tr2 = clock64();
+    // the next ticket's record travels while the TBs are processed
+    t_next = __shfl_sync(B265_FULL_MASK, t_next, 0);
+    IntraTicket tk_next = {0, 0, 0, 0, 0, 0};
+    if (t_next < (unsigned)n_tickets) tk_next = tickets[t_next];
     for (uint32_t base = 0; base < tk.tu_count; base += 32) {
       if (base) {
         mine = make_uint4(0, 0xff000000u, 0, 0);
@@ -299,6 +325,8 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
       const bool want = lane < n_here && (mine.y >> 24) != B265_INTRA_NONE && (int)(mine.y & 3) == c;
       unsigned todo = __ballot_sync(B265_FULL_MASK, want);
       while (todo) {
+        long long lc0 = 0;
+        if (TRACE) lc0 = clock64();
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
         const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
@@ -308,7 +336,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
         const bool coded = (r3 & 0xffff) != 0;
         const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
                            ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
-        if (TRACE) n_tbs++;
+        if (TRACE) { n_tbs++; lacc += clock64() - lc0; }
         switch ((r1 >> 2) & 7) {
           case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
           case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
@@ -317,18 +345,24 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
         }
       }
     }
+    if (TRACE) tr3 = clock64();
+    // next ticket's picture constants: issued before the release store so that both round trips overlap
+    uint8_t* my_flag = done + tk.ctb;
+    const unsigned t_cur = t;
+    t = t_next;
+    tk = tk_next;
+    if (t < (unsigned)n_tickets) load_constants(tk);
     // publish: every sample of this CTB plane is final (pre-deblock) now
     // (bar.warp.sync orders the other lanes' stores before lane 0's release store, which is cumulative)
-    if (TRACE) tr3 = clock64();
     __syncwarp();
-    if (lane == 0) st_release_u8(done + tk.ctb, 1);
+    if (lane == 0) st_release_u8(my_flag, 1);
     __syncwarp();
     if (TRACE && lane == 0) {
       unsigned smid;
       asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-      unsigned long long* o = trace + (size_t)t * 12;
+      unsigned long long* o = trace + (size_t)t_cur * 12;
       o[0] = tr0; o[1] = tr1; o[2] = tr2; o[3] = tr3; o[4] = clock64(); o[5] = n_tbs; o[6] = acc[0]; o[7] = acc[1];
-      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = smid;
+      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = ((unsigned long long)lacc << 16) | smid;
     }
   }
 }

@@ -3,6 +3,8 @@ import sys
 import numpy as np
 a = np.fromfile(sys.argv[1], dtype=np.uint64).reshape(-1, 12).astype(np.int64)
 t0, t1, t2, t3, t4, ntb, a_g, a_f, a_p, a_s, gt, sm = a.T
+lacc = sm >> 16
+sm = sm & 0xffff
 print("tickets %d, TBs %d, span %.3f ms (globaltimer)" % (len(a), ntb.sum(), (gt.max() - gt.min()) / 1e6))
 ph = {"wait+fence": t1 - t0, "tile": t2 - t1, "tbs": t3 - t2, "publish": t4 - t3, "total": t4 - t0}
 for k, v in ph.items():
@@ -20,3 +22,4 @@ m = ntb >= 12
 print("tickets with >=12 TBs: gather %.0f filter %.0f predict %.0f add+store %.0f loop %.0f" % (
     a_g[m].sum() / ntb[m].sum(), a_f[m].sum() / ntb[m].sum(), a_p[m].sum() / ntb[m].sum(), a_s[m].sum() / ntb[m].sum(),
     ((t3 - t2)[m].sum() - (a_g + a_f + a_p + a_s)[m].sum()) / ntb[m].sum()))
+print("loop head (ffs+shfl+decode) per TB: %.0f cycles" % (lacc.sum() / ntb.sum()))
