@@ -32,6 +32,21 @@ const uint8_t g_cabac_next_lps[64] = {0,  0,  1,  2,  2,  4,  4,  5,  6,  7,  8,
 const uint8_t g_cabac_renorm[32] = {6, 5, 4, 4, 3, 3, 3, 3, 2, 2, 2, 2, 2, 2, 2, 2,
                                     1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1};
 
+// next context byte for (ctx << 1) | decodedLps, built from the two transition tables above
+uint8_t g_cabac_next[256];
+namespace {
+struct NextTabInit {
+  NextTabInit() {
+    for (int c = 0; c < 128; c++) {
+      const int state = c >> 1, mps = c & 1;
+      g_cabac_next[(c << 1) | 0] = (uint8_t)((g_cabac_next_mps[state] << 1) | mps);
+      g_cabac_next[(c << 1) | 1] = (uint8_t)((g_cabac_next_lps[state] << 1) | (state == 0 ? mps ^ 1 : mps));
+    }
+  }
+};
+const NextTabInit g_next_init;
+}  // namespace
+
 namespace {
 
 struct InitRow {

@@ -57,11 +57,12 @@ extern const uint8_t g_cabac_lps[64][4];
 extern const uint8_t g_cabac_next_mps[64];
 extern const uint8_t g_cabac_next_lps[64];
 extern const uint8_t g_cabac_renorm[32];
+extern uint8_t g_cabac_next[256];   // next context byte, indexed by (ctx << 1) | decodedLps
 
 struct Cabac {
   const uint8_t* cur = nullptr;
   const uint8_t* end = nullptr;
-  uint32_t range = 510;
+  uint32_t range = 510;   // after start(): kept in [256, 510] between decisions
   uint32_t value = 0;
   int bits_needed = 8;
 
@@ -74,36 +75,27 @@ struct Cabac {
     if (cur < end) { value = (uint32_t)(*cur++) << 8; bits_needed -= 8; }
     if (cur < end) { value |= *cur++; bits_needed -= 8; }
   }
+  // 9.3.4.3.2 DecodeDecision without data-dependent branches: the MPS/LPS outcome is a mask, the state
+  // transition one table look-up (g_cabac_next[ctx*2 + lps]), the renormalisation shift a leading-zero count
+  // (0 or 1 after an MPS, 1..6 after an LPS).  The only branch left is the byte refill (every 8th shift).
   inline int bin(Ctx& c) {
-    const uint32_t state = c >> 1;
-    uint32_t mps = c & 1;
-    const uint32_t lps = g_cabac_lps[state][(range >> 6) - 4];
-    range -= lps;
-    const uint32_t scaled = range << 7;
-    if (value < scaled) {
-      c = (Ctx)((g_cabac_next_mps[state] << 1) | mps);
-      if (scaled < (256u << 7)) {
-        range = scaled >> 6;
-        value <<= 1;
-        if (++bits_needed == 0) {
-          bits_needed = -8;
-          if (cur < end) value |= *cur++;
-        }
-      }
-      return (int)mps;
-    }
-    const int nb = g_cabac_renorm[lps >> 3];
-    value = (value - scaled) << nb;
-    range = lps << nb;
-    const int bit = (int)(mps ^ 1);
-    if (state == 0) mps ^= 1;
-    c = (Ctx)((g_cabac_next_lps[state] << 1) | mps);
-    bits_needed += nb;
+    const uint32_t s = c;
+    const uint32_t lps = g_cabac_lps[s >> 1][(range >> 6) & 3];
+    uint32_t r = range - lps;
+    const uint32_t scaled = r << 7;
+    const uint32_t m = (uint32_t)((int32_t)(scaled - value - 1) >> 31);   // ~0 iff value >= scaled (LPS)
+    value -= scaled & m;
+    r += (lps - r) & m;
+    c = g_cabac_next[(s << 1) | (m & 1)];
+    const int sh = __builtin_clz(r) - 23;   // r in [6, 510]
+    range = r << sh;
+    value <<= sh;
+    bits_needed += sh;
     if (bits_needed >= 0) {
       if (cur < end) value |= (uint32_t)(*cur++) << bits_needed;
       bits_needed -= 8;
     }
-    return bit;
+    return (int)((s ^ m) & 1);
   }
   inline int bypass() {
     value <<= 1;
@@ -112,11 +104,31 @@ struct Cabac {
       if (cur < end) value |= *cur++;
     }
     const uint32_t scaled = range << 7;
-    if (value >= scaled) { value -= scaled; return 1; }
-    return 0;
+    const uint32_t m = (uint32_t)((int32_t)(scaled - value - 1) >> 31);
+    value -= scaled & m;
+    return (int)(m & 1);
+  }
+  // n <= 8 bypass bins at once: n bypass decisions are the long division of the scaled offset by the scaled
+  // range (same register contents afterwards as n calls of bypass(); cabac.cc:377-410 of the reference
+  // uses the same identity)
+  inline uint32_t bypass_chunk(int n) {
+    value <<= n;
+    bits_needed += n;
+    if (bits_needed >= 0) {
+      if (cur < end) value |= (uint32_t)(*cur++) << bits_needed;
+      bits_needed -= 8;
+    }
+    const uint32_t scaled = range << 7;
+    uint32_t v = value / scaled;
+    const uint32_t lim = (1u << n) - 1;
+    if (v > lim) v = lim;  // only on corrupt data
+    value -= v * scaled;
+    return v;
   }
   inline uint32_t bypass_bits(int n) {
     uint32_t v = 0;
+    while (n > 8) { v = (v << 8) | bypass_chunk(8); n -= 8; }
+    if (n >= 3) return (v << n) | bypass_chunk(n);
     while (n-- > 0) v = (v << 1) | (uint32_t)bypass();
     return v;
   }

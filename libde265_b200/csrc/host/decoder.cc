@@ -395,8 +395,8 @@ struct Decoder {
         for (de265_image* img : batch) {
           img->state = de265_image::DONE;
           if (!parse_only) {  // work lists are no longer needed
-            std::vector<b265_tu>().swap(img->pic.tus);
-            std::vector<b265_coeff>().swap(img->pic.coeffs);
+            img->pic.tus.release();
+            img->pic.coeffs.release();
             std::vector<uint8_t>().swap(img->pic.unit_info);
           }
         }

@@ -5,12 +5,51 @@
 // planes themselves live in HBM (b265 surfaces) and never on the host until output.
 #pragma once
 #include <stdint.h>
+#include <stdlib.h>
 #include <memory>
 #include <vector>
 #include "../../../include/b265.h"
 #include "params.h"
 
 namespace b265h {
+
+// Growable array of PODs without value-initialisation (the work lists are written once, sequentially, by the
+// syntax decoder's inner loops: no zero fill, no per-element capacity check when the caller reserves first).
+template <class T>
+struct PodBuf {
+  T* p = nullptr;
+  size_t n = 0, cap = 0;
+  PodBuf() {}
+  PodBuf(const PodBuf&) = delete;
+  PodBuf& operator=(const PodBuf&) = delete;
+  PodBuf(PodBuf&& o) noexcept : p(o.p), n(o.n), cap(o.cap) { o.p = nullptr; o.n = o.cap = 0; }
+  PodBuf& operator=(PodBuf&& o) noexcept {
+    if (this != &o) { free(p); p = o.p; n = o.n; cap = o.cap; o.p = nullptr; o.n = o.cap = 0; }
+    return *this;
+  }
+  ~PodBuf() { free(p); }
+  void reserve(size_t c) {
+    if (c <= cap) return;
+    T* q = (T*)realloc(p, c * sizeof(T));
+    if (!q) abort();
+    p = q; cap = c;
+  }
+  // room for `extra` more elements; returns the write position (the caller advances n)
+  T* room(size_t extra) {
+    if (n + extra > cap) reserve(n + extra > 2 * cap ? n + extra : 2 * cap);
+    return p + n;
+  }
+  void push_back(const T& v) { *room(1) = v; n++; }
+  void clear() { n = 0; }
+  void release() { free(p); p = nullptr; n = cap = 0; }
+  size_t size() const { return n; }
+  bool empty() const { return n == 0; }
+  T* data() { return p; }
+  const T* data() const { return p; }
+  T& operator[](size_t i) { return p[i]; }
+  const T& operator[](size_t i) const { return p[i]; }
+  T& back() { return p[n - 1]; }
+};
 
 enum PredMode : uint8_t { MODE_NONE = 0, MODE_INTRA = 1, MODE_INTER = 2, MODE_SKIP = 3 };
 
@@ -45,8 +84,8 @@ struct Picture {
   std::vector<b265_ctb> ctbs;      // per CTB (raster)
 
   // ---- work lists ----
-  std::vector<b265_tu> tus;
-  std::vector<b265_coeff> coeffs;
+  PodBuf<b265_tu> tus;
+  PodBuf<b265_coeff> coeffs;
   std::vector<b265_pu> pus;
   std::vector<b265_pcm> pcms;
   std::vector<uint8_t> pcm_samples;

@@ -15,6 +15,19 @@
 #include <string.h>
 #include <algorithm>
 #include "cabac.h"
+#ifdef B265_PROF
+#include <x86intrin.h>
+#include <stdio.h>
+unsigned long long g_prof[16];
+struct ProfScope { int i; unsigned long long t; ProfScope(int k) : i(k), t(__rdtsc()) {} ~ProfScope() { g_prof[i] += __rdtsc() - t; } };
+#define PROF(k) ProfScope prof_scope_##k(k)
+#define PROF_T(v) unsigned long long v = __rdtsc()
+#define PROF_ADD(k, a, b) g_prof[k] += (b) - (a)
+#else
+#define PROF(k)
+#define PROF_T(v)
+#define PROF_ADD(k, a, b)
+#endif
 #include "picture.h"
 
 namespace b265h {
@@ -69,6 +82,36 @@ struct SigLut {
   }
 };
 const SigLut g_sig;
+
+// sig_coeff_flag context index (9.3.4.2.5) per SCAN POSITION of a 4x4 sub-block, including the context base:
+// [chroma][log2 size - 2][scanIdx][prevCsbf][sub-block index > 0][k]
+struct SigCtxTab {
+  uint8_t t[2][4][3][4][2][16];
+  SigCtxTab() {
+    for (int ch = 0; ch < 2; ch++)
+      for (int lg = 2; lg <= 5; lg++)
+        for (int scan = 0; scan < 3; scan++)
+          for (int prev = 0; prev < 4; prev++)
+            for (int nz = 0; nz < 2; nz++)
+              for (int k = 0; k < 16; k++) {
+                const int xP = g_scan.pos[2][scan][k] & 15, yP = g_scan.pos[2][scan][k] >> 4;
+                int sc;
+                if (lg == 2) sc = kCtxIdxMap4x4[(yP << 2) + xP];
+                else if (!nz && k == 0) sc = 0;
+                else {
+                  sc = g_sig.v[prev][(yP << 2) + xP];
+                  if (!ch) {
+                    if (nz) sc += 3;
+                    sc += lg == 3 ? (scan == 0 ? 9 : 15) : 21;
+                  } else {
+                    sc += lg == 3 ? 9 : 12;
+                  }
+                }
+                t[ch][lg - 2][scan][prev][nz][k] = (uint8_t)((ch ? CTX_SIG_COEFF + 27 : CTX_SIG_COEFF) + sc);
+              }
+  }
+};
+const SigCtxTab g_sigctx;
 
 const uint8_t kQpC[58] = {0,  1,  2,  3,  4,  5,  6,  7,  8,  9,  10, 11, 12, 13, 14, 15, 16, 17, 18, 19,
                           20, 21, 22, 23, 24, 25, 26, 27, 28, 29, 29, 30, 31, 32, 33, 33, 34, 34, 35, 35,
@@ -220,6 +263,7 @@ int SliceDec::coding_quadtree(int x0, int y0, int log2_cb, int depth) {
 
 // ---- QP derivation (8.6.1; transform.cc:31-200) ------------------------------------------------------
 void SliceDec::decode_qp(int xCU, int yCU, int log2_cb) {
+  PROF(3);
   const int qg_mask = (1 << pps.log2_min_cu_qp_delta) - 1;
   const int xQG = xCU & ~qg_mask, yQG = yCU & ~qg_mask;
   if (xQG != cur_qg_x || yQG != cur_qg_y) {
@@ -274,6 +318,7 @@ void SliceDec::decode_qp(int xCU, int yCU, int log2_cb) {
 // Called for every leaf TU. Edges on the CU boundary use the CU's left/top filter decision; edges
 // inside the CU are always filtered. Nothing is marked when the slice has deblocking disabled.
 void SliceDec::mark_tu_edges(int x0, int y0, int log2_ts, int xCU, int yCU, int log2_cb, bool cbf_luma) {
+  PROF(4);
   const int n_u = 1 << (log2_ts - 2);
   const int ux = x0 >> 2, uy = y0 >> 2;
   uint8_t* ui = pic.unit_info.data();
@@ -330,6 +375,7 @@ int SliceDec::read_pcm(int x0, int y0, int log2_cb) {
 
 // ---- coding unit (7.3.8.5) — intra only ---------------------------------------------------------------
 int SliceDec::coding_unit(int x0, int y0, int log2_cb) {
+  PROF(2);
   const int n_cbs = 1 << log2_cb;
   decode_qp(x0, y0, log2_cb);
   cu_tq_bypass = 0;
@@ -522,12 +568,18 @@ int SliceDec::transform_unit(int x0, int y0, int xBase, int yBase, int xCU, int 
 }
 
 // ---- residual coding (7.3.8.11, 9.3.4.2.4-7) -----------------------------------------------------------
+// The arithmetic decoder state is copied into a local for the duration of the block: the context
+// variables are bytes, so every context update would otherwise force the engine's registers back to
+// memory (char stores alias everything).
 int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_mode, b265_tu& tu) {
+  PROF(1);
   (void)x0; (void)y0;
+  Cabac cb = cabac;
+  Ctx* const cx = ctx;
   const int n = 1 << log2_ts;
   int tskip = 0;
   if (pps.transform_skip_enabled && !cu_tq_bypass && log2_ts <= pps.log2_max_transform_skip)
-    tskip = cabac.bin(ctx[CTX_TRANSFORM_SKIP + (cidx ? 1 : 0)]);
+    tskip = cb.bin(cx[CTX_TRANSFORM_SKIP + (cidx ? 1 : 0)]);
 
   // last significant coefficient position
   const int cmax = (log2_ts << 1) - 1;
@@ -535,18 +587,18 @@ int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_m
   if (cidx == 0) { off = 3 * (log2_ts - 2) + ((log2_ts - 1) >> 2); shift = (log2_ts + 1) >> 2; }
   else { off = 15; shift = log2_ts - 2; }
   int px = 0, py = 0;
-  while (px < cmax && cabac.bin(ctx[CTX_LAST_X + off + (px >> shift)])) px++;
-  while (py < cmax && cabac.bin(ctx[CTX_LAST_Y + off + (py >> shift)])) py++;
+  while (px < cmax && cb.bin(cx[CTX_LAST_X + off + (px >> shift)])) px++;
+  while (py < cmax && cb.bin(cx[CTX_LAST_Y + off + (py >> shift)])) py++;
   int last_x = px, last_y = py;
-  if (px > 3) { const int nb = (px >> 1) - 1; last_x = (1 << nb) * (2 + (px & 1)) + (int)cabac.bypass_bits(nb); }
-  if (py > 3) { const int nb = (py >> 1) - 1; last_y = (1 << nb) * (2 + (py & 1)) + (int)cabac.bypass_bits(nb); }
+  if (px > 3) { const int nb = (px >> 1) - 1; last_x = (1 << nb) * (2 + (px & 1)) + (int)cb.bypass_bits(nb); }
+  if (py > 3) { const int nb = (py >> 1) - 1; last_y = (1 << nb) * (2 + (py & 1)) + (int)cb.bypass_bits(nb); }
   int scan = 0;
   if (cu_pred_mode == MODE_INTRA && (log2_ts == 2 || (log2_ts == 3 && cidx == 0))) {
     if (intra_mode >= 6 && intra_mode <= 14) scan = 2;
     else if (intra_mode >= 22 && intra_mode <= 30) scan = 1;
   }
   if (scan == 2) std::swap(last_x, last_y);
-  if (last_x >= n || last_y >= n) return E_DECODING;
+  if (last_x >= n || last_y >= n) { cabac = cb; return E_DECODING; }
 
   const int lg_sb = log2_ts - 2, sbw = 1 << lg_sb;
   const uint8_t* sb_scan = g_scan.pos[lg_sb][scan];
@@ -560,45 +612,44 @@ int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_m
   const bool implicit_rdpcm_hv = cu_pred_mode == MODE_INTRA && sps.implicit_rdpcm && (tskip || cu_tq_bypass) &&
                                  (intra_mode == 10 || intra_mode == 26);
   const bool sign_hiding_ok = pps.sign_data_hiding && !cu_tq_bypass && !implicit_rdpcm_hv;
-  const int sig_base = cidx == 0 ? CTX_SIG_COEFF : CTX_SIG_COEFF + 27;
+  const int ch = cidx ? 1 : 0;
+  uint8_t ts_tab[16];
+  if (ts_ctx) memset(ts_tab, (cidx == 0 ? CTX_SIG_COEFF + 42 : CTX_SIG_COEFF + 27 + 16), 16);
+  const int csb_base = CTX_CODED_SUB_BLOCK + (cidx ? 2 : 0);
+  const int gt1_base = CTX_GT1 + (cidx ? 16 : 0), gt2_base = CTX_GT2 + (cidx ? 4 : 0);
   int c1 = 1;
   bool first_sb = true;
-  const size_t coeff_start = pic.coeffs.size();
+  // room for every coefficient of the block; the list grows by what is actually coded
+  b265_coeff* const out0 = pic.coeffs.room((size_t)n * n);
+  b265_coeff* out = out0;
 
   for (int i = last_sb; i >= 0; i--) {
+    PROF_T(p0);
     const int xS = sb_scan[i] & 15, yS = sb_scan[i] >> 4;
     const int prev_csbf = csbf[yS][xS + 1] | (csbf[yS + 1][xS] << 1);
     int infer_dc = 0, coded = 1;
     if (i < last_sb && i > 0) {
-      coded = cabac.bin(ctx[CTX_CODED_SUB_BLOCK + (prev_csbf ? 1 : 0) + (cidx ? 2 : 0)]);
+      coded = cb.bin(cx[csb_base + (prev_csbf ? 1 : 0)]);
       infer_dc = 1;
     }
     csbf[yS][xS] = (uint8_t)coded;
     if (!coded) continue;
 
-    uint8_t sig[16];
+    uint8_t sig[17];
     int nsig = 0, nstart = 15;
     if (i == last_sb) { sig[nsig++] = (uint8_t)last_pos; nstart = last_pos - 1; }
-    for (int k = nstart; k >= 0; k--) {
-      if (k == 0 && infer_dc) { sig[nsig++] = 0; break; }
-      const int xP = c_scan[k] & 15, yP = c_scan[k] >> 4;
-      int sc;
-      if (ts_ctx) sc = cidx == 0 ? 42 : 16;
-      else if (log2_ts == 2) sc = kCtxIdxMap4x4[(yP << 2) + xP];
-      else if (i == 0 && k == 0) sc = 0;
-      else {
-        sc = g_sig.v[prev_csbf][(yP << 2) + xP];
-        if (cidx == 0) {
-          if (i > 0) sc += 3;
-          sc += log2_ts == 3 ? (scan == 0 ? 9 : 15) : 21;
-        } else {
-          sc += log2_ts == 3 ? 9 : 12;
-        }
-      }
-      if (cabac.bin(ctx[sig_base + sc])) { sig[nsig++] = (uint8_t)k; infer_dc = 0; }
+    const uint8_t* tab = ts_ctx ? ts_tab : g_sigctx.t[ch][lg_sb][scan][prev_csbf][i > 0];
+    for (int k = nstart; k >= 1; k--) {   // branch-free append: the flag values are unpredictable
+      sig[nsig] = (uint8_t)k;
+      nsig += cb.bin(cx[tab[k]]);
+    }
+    if (nstart >= 0) {
+      if (infer_dc && nsig == 0) sig[nsig++] = 0;           // the only coefficient of a coded sub-block
+      else if (cb.bin(cx[tab[0]])) sig[nsig++] = 0;
     }
     if (!nsig) continue;
-
+    PROF_T(p1);
+    PROF_ADD(6, p0, p1);
     // greater1 / greater2 flags
     int ctx_set = (i == 0 || cidx > 0) ? 0 : 2;
     if (!first_sb && c1 == 0) ctx_set++;
@@ -607,34 +658,38 @@ int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_m
     int absv[16];
     int first_g1 = -1;
     const int ng1 = nsig < 8 ? nsig : 8;
+    Ctx* g1 = cx + gt1_base + ctx_set * 4;
+    static const uint8_t c1_next[2][4] = {{0, 2, 3, 3}, {0, 0, 0, 0}};   // 9.3.4.2.6
     for (int k = 0; k < ng1; k++) {
-      const int g = cabac.bin(ctx[CTX_GT1 + ctx_set * 4 + c1 + (cidx ? 16 : 0)]);
+      const int g = cb.bin(g1[c1]);
       absv[k] = 1 + g;
-      if (g) { c1 = 0; if (first_g1 < 0) first_g1 = k; }
-      else if (c1 > 0 && c1 < 3) c1++;
+      first_g1 = (g & (first_g1 < 0)) ? k : first_g1;
+      c1 = c1_next[g][c1];
     }
     for (int k = ng1; k < nsig; k++) absv[k] = 1;
-    if (first_g1 >= 0) absv[first_g1] += cabac.bin(ctx[CTX_GT2 + ctx_set + (cidx ? 4 : 0)]);
-
+    if (first_g1 >= 0) absv[first_g1] += cb.bin(cx[gt2_base + ctx_set]);
+    PROF_T(p2);
+    PROF_ADD(7, p1, p2);
     const bool sign_hidden = sign_hiding_ok && (sig[0] - sig[nsig - 1] > 3);
     const int nsign = nsig - (sign_hidden ? 1 : 0);
-    uint32_t signs = cabac.bypass_bits(nsign) << (16 - nsign);  // bit 15 = first coefficient
+    uint32_t signs = cb.bypass_bits(nsign) << (16 - nsign);  // bit 15 = first coefficient
 
     int rice = 0, sum_abs = 0;
+    const int sb_pos = (xS << 2) + ((yS << 2) << log2_ts);
     for (int k = 0; k < nsig; k++) {
       const int base = absv[k];
       const int thr = k < 8 ? (k == first_g1 ? 3 : 2) : 1;
       int a = base;
       if (base == thr) {
         int prefix = 0;
-        while (prefix < 32 && cabac.bypass()) prefix++;
-        if (prefix >= 32) return E_DECODING;
+        while (prefix < 32 && cb.bypass()) prefix++;
+        if (prefix >= 32) { cabac = cb; return E_DECODING; }
         int rem;
-        if (prefix <= 3) rem = (prefix << rice) + (int)cabac.bypass_bits(rice);
+        if (prefix <= 3) rem = (prefix << rice) + (int)cb.bypass_bits(rice);
         else {
           const int nb = prefix - 3 + rice;
-          if (nb > 24) return E_DECODING;
-          rem = (((1 << (prefix - 3)) + 3 - 1) << rice) + (int)cabac.bypass_bits(nb);
+          if (nb > 24) { cabac = cb; return E_DECODING; }
+          rem = (((1 << (prefix - 3)) + 3 - 1) << rice) + (int)cb.bypass_bits(nb);
         }
         a = base + rem;
         if (a > 3 * (1 << rice)) rice = rice < 4 ? rice + 1 : 4;
@@ -646,14 +701,18 @@ int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_m
       int v = neg ? -a : a;
       if (v > 32767) v = 32767;
       if (v < -32768) v = -32768;
-      const int xC = (xS << 2) + (c_scan[sig[k]] & 15), yC = (yS << 2) + (c_scan[sig[k]] >> 4);
-      b265_coeff c;
-      c.level = (int16_t)v;
-      c.pos = (uint16_t)(xC + (yC << log2_ts));
-      pic.coeffs.push_back(c);
+      const int p = c_scan[sig[k]];
+      out->level = (int16_t)v;
+      out->pos = (uint16_t)(sb_pos + (p & 15) + ((p >> 4) << log2_ts));
+      out++;
     }
+    PROF_T(p3);
+    PROF_ADD(8, p2, p3);
   }
-  tu.ncoeff = (uint16_t)(pic.coeffs.size() - coeff_start);
+  cabac = cb;
+  const size_t ncoded = (size_t)(out - out0);
+  pic.coeffs.n += ncoded;
+  tu.ncoeff = (uint16_t)ncoded;
   uint8_t fl = B265_TU_INTRA_CU;
   if (cidx == 0 && log2_ts == 2) fl |= B265_TU_DST;
   if (tskip) fl |= B265_TU_SKIP;
@@ -666,6 +725,7 @@ int SliceDec::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_m
 
 // ---- CTU and slice segment data (7.3.8.1, 7.3.8.2; slice.cc:4640-4830) -------------------------------
 int SliceDec::decode_ctu() {
+  PROF(0);
   const int rx = ctb_rs % sps.ctbs_w, ry = ctb_rs / sps.ctbs_w;
   pic.ctb_slice_addr[ctb_rs] = sh.slice_addr_rs;
   pic.ctbs[ctb_rs].addr_ts = ctb_ts;
@@ -758,6 +818,7 @@ static int decode_slice_unit(Picture& pic, const SliceUnit& unit, PicDecodeState
 }
 
 int decode_picture_slices(Picture& pic) {
+  PROF(5);
   PicDecodeState st;
   const Sps& sps = *pic.sps;
   st.wpp.assign((size_t)sps.ctbs_h * CTX_COUNT, 0);
