@@ -33,5 +33,5 @@ for nb in batches:
     for s in sids:
         ctx.surface_release(s)
     print(json.dumps({"stream": name, "batch": nb, "upload_ms": t_up * 1e3, "tus": sum(j.n_tus for j in js),
-                      "stages_ms[mc,res,intra,dbk,sao,total]": [round(x, 3) for x in ts[-1]], "first": [round(x, 3) for x in ts[0]]}))
+                      "stages_ms[mc,res+avail,intra,dbk,sao,total]": [round(x, 3) for x in ts[-1]], "first": [round(x, 3) for x in ts[0]]}))
 ctx.close()

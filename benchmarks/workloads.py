@@ -28,11 +28,16 @@ STREAM_WL = {
 }
 
 
+def _dist_device():
+    import torch.distributed as dist
+    return "cuda" if dist.get_backend() == "nccl" else "cpu"
+
+
 def _barrier_max(world, value):
     if world == 1:
         return value
     import torch, torch.distributed as dist
-    t = torch.tensor([value], dtype=torch.float64, device="cuda")
+    t = torch.tensor([value], dtype=torch.float64, device=_dist_device())
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
@@ -41,9 +46,87 @@ def _all_sum(world, value):
     if world == 1:
         return value
     import torch, torch.distributed as dist
-    t = torch.tensor([value], dtype=torch.float64, device="cuda")
+    t = torch.tensor([value], dtype=torch.float64, device=_dist_device())
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return float(t.item())
+
+
+# ---------------------------------------------------------------------------------------------
+# replicas: the path does not shard inside a picture, so N GPUs = N decoder instances fed
+# with independent streams or with the closed-GOP segments of one stream, dealt round-robin
+# ---------------------------------------------------------------------------------------------
+def split_idr_segments(data):
+    """Split an Annex-B stream into closed-GOP segments: every segment starts with the parameter sets seen
+    so far and one IDR/BLA picture (enc265 intra streams: every picture).  Returns a list of bytes."""
+    import re
+    starts = [m.start() for m in re.finditer(b"\x00\x00\x01", data)]
+    nals = []
+    for i, s in enumerate(starts):
+        e = starts[i + 1] if i + 1 < len(starts) else len(data)
+        while e > s + 3 and data[e - 1] == 0 and i + 1 < len(starts):
+            e -= 1   # zero byte(s) of the next 4-byte start code
+        nals.append(data[s:e])
+    params, segs, cur = {}, [], None
+    for n in nals:
+        t = (n[3] >> 1) & 0x3f
+        if t in (32, 33, 34):        # VPS / SPS / PPS
+            params[(t, n[5:6] if t == 34 else b"")] = n
+            if cur is not None:
+                cur.append(n)
+            continue
+        first_slice = t < 32 and len(n) > 5 and (n[5] & 0x80)
+        if 16 <= t <= 21 and first_slice:   # IRAP picture starts a new segment
+            if cur is not None:
+                segs.append(b"".join(cur))
+            cur = [b"\x00" + p for p in params.values()]
+        if cur is not None:
+            cur.append(b"\x00" + n if t >= 32 or first_slice else n)
+    if cur:
+        segs.append(b"".join(cur))
+    return segs
+
+
+def deal(items, world, rank):
+    """round-robin share of `items` for `rank`, with the original indices (outputs are re-ordered by index)"""
+    return [(i, it) for i, it in enumerate(items) if i % world == rank]
+
+
+def run_parse_replicas(a, rank, world, local):
+    """Host-only replica run (no GPU): every rank decodes its share of the closed-GOP segments of a golden
+    stream with a parse-only decoder; used by the world_size-2 gloo test of the N>1 host logic."""
+    from libde265_b200.decoder import Decoder
+    name = "tiny_416x240_q30"
+    data = _stream_bytes(name, False)
+    gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    segs = split_idr_segments(data)
+    mine = deal(segs, world, rank)
+    dec = Decoder(device=local, threads=1, batch=4, parse_only=True)
+    t0 = time.perf_counter()
+    got = []
+    for _ in range(a.steps):
+        got = []
+        for idx, seg in mine:
+            dec.lib.de265_reset(dec.h)
+            pocs = []
+            dec.decode_stream(seg, on_picture=lambda img: pocs.append(dec.lib.b265_de265_image_poc(img)))
+            got.append((idx, len(pocs)))
+    dt = time.perf_counter() - t0
+    dec.close()
+    dt = _barrier_max(world, dt)
+    frames = _all_sum(world, float(sum(n for _, n in got)))
+    gathered = [got]
+    if world > 1:
+        import torch.distributed as dist
+        gathered = [None] * world
+        dist.all_gather_object(gathered, got)
+    order = sorted(x for g in gathered for x in g)
+    assert [i for i, _ in order] == list(range(len(segs))), "segments lost or duplicated across ranks"
+    assert int(frames) == gold["frames"], "replicas decoded %d pictures, stream has %d" % (frames, gold["frames"])
+    return {"metric": "parsed frames/s (host only, replicas)", "value": frames * a.steps / dt, "unit": "frames/s",
+            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": dt / a.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "syntax only", "data": "synthetic",
+            "config": {"workload": "parse_replicas: closed-GOP segments of %s dealt round-robin over %d ranks" % (name, world),
+                       "segments": len(segs)}}
 
 
 def _stream_bytes(name, patched):
@@ -125,14 +208,24 @@ def cpu_port_stream(wl):
 # =====================================================================================================
 # our arm: stream workloads
 # =====================================================================================================
+_TU_DT = np.dtype([('x', '<u2'), ('y', '<u2'), ('cidx_log2', 'u1'), ('flags', 'u1'), ('qp', 'u1'), ('intra_mode', 'u1'),
+                   ('coeff_off', '<u4'), ('ncoeff', '<u2'), ('reserved', '<u2')])
+
+
 def _job_algorithmic_bytes(J):
-    """SURVEY §8d: intra (fused with residual add) writes 1.5*W*H and reads 4 B per non-zero coefficient;
+    """SURVEY §8d per picture (DESIGN.md "algorithmic bytes"):
+    residual pre-pass: 4 B per non-zero coefficient read + 2 B per sample of a coded TB written (int16 plane);
+    intra wavefront: 1.5*W*H samples written + 2 B per sample of a coded TB read;
     deblocking run as two passes reads+writes the picture twice (4P)."""
     P = J.width * J.height * 3 // 2
     from libde265_b200 import lib as L
-    intra = P + 4 * J.n_coeffs
+    tus = np.ctypeslib.as_array(C.cast(J.tus, C.POINTER(C.c_uint8)), shape=(J.n_tus * 16,)).view(_TU_DT)
+    coded = tus[tus['ncoeff'] > 0]
+    coded_samples = int((1 << (2 * (coded['cidx_log2'].astype(np.int64) >> 2))).sum())
+    res = 4 * J.n_coeffs + 2 * coded_samples
+    intra = P + 2 * coded_samples
     dbk = 4 * P if (J.flags & L.FRAME_DEBLOCK) else 0
-    return intra, dbk
+    return res, intra, dbk
 
 
 def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
@@ -160,8 +253,8 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         jobs.append(J)
     batch = ctx.upload_frames(jobs)
     ctx.sync()
-    bytes_intra = sum(_job_algorithmic_bytes(J)[0] for J in jobs)
-    bytes_dbk = sum(_job_algorithmic_bytes(J)[1] for J in jobs)
+    ab = [_job_algorithmic_bytes(J) for J in jobs]
+    bytes_res, bytes_intra, bytes_dbk = (sum(x[i] for x in ab) for i in range(3))
     for _ in range(a.warmup):
         ctx.run_batch(batch)
     ctx.sync()
@@ -219,6 +312,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     e2e_fps = world * frames_step * a.steps / e2e_s
 
     peak, peak_src = measured_peaks()
+    res_gbs = bytes_res / stage[1] / 1e6 if stage[1] > 0 else 0.0
     intra_gbs = bytes_intra / stage[2] / 1e6 if stage[2] > 0 else 0.0
     dbk_gbs = bytes_dbk / stage[3] / 1e6 if stage[3] > 0 and bytes_dbk else None
     res = {
@@ -227,13 +321,14 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
         "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": kbatch,
                    "mpixel_per_s": value * W * H / 1e6,
-                   "value_is": "reconstruction kernels (intra wavefront + residual, deblock V/H) on a batch of %d pictures "
+                   "value_is": "reconstruction kernels (residual pre-pass, intra wavefront, deblock bS+V+H) on a batch of %d pictures "
                                "whose work lists are resident in HBM" % kbatch,
                    "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
                          % (kbatch * W * H * 3 // 2 >> 20),
                    "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
                              "2 CUDA contexts, batch 16; %d frames per step" % (threads, frames_step),
-                   "host_cores": cores, "stage_ms[pcm+mc,inter_res,intra,deblock,sao,total]": [round(x, 3) for x in stage]},
+                   "host_cores": cores,
+                   "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage]},
         "e2e": {"value": e2e_fps, "unit": "frames/s",
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) / a.steps),
@@ -242,9 +337,11 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         "gpu_launches": int(launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_intra_wavefront", "achieved": intra_gbs, "peak": peak, "unit": "GB/s",
                      "frac": intra_gbs / peak, "traffic": None, "peak_source": peak_src,
-                     "note": "dependency-latency bound (CTB anti-diagonal wavefront), not bandwidth bound; "
-                             "algorithmic bytes = 1.5*W*H written + 4 B per coefficient per picture",
-                     "per_kernel_gbs": {"k_intra_wavefront": round(intra_gbs, 1),
+                     "note": "largest share of the step; dependency-latency bound (CTB anti-diagonal wavefront, one warp "
+                             "walks a CTB), not bandwidth bound; algorithmic bytes per picture = 1.5*W*H written + 2 B per "
+                             "sample of a coded TB read; time = CUDA events around this launch only",
+                     "per_kernel_gbs": {"k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1),
+                                        "k_intra_wavefront": round(intra_gbs, 1),
                                         "deblock(bs+V+H luma/chroma, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None}},
     }
     if rank == 0 and world == 1:
@@ -425,12 +522,16 @@ DEFAULT_WORKLOAD = "stream_4k"
 
 
 def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
+    wl = a.workload or DEFAULT_WORKLOAD
     if world > 1:
         import torch, torch.distributed as dist
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl")
-    wl = a.workload or DEFAULT_WORKLOAD
-    if wl in STREAM_WL:
+        backend = os.environ.get("B265_DIST_BACKEND", "gloo" if wl == "parse_replicas" else "nccl")
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+        dist.init_process_group(backend)
+    if wl == "parse_replicas":
+        res = run_parse_replicas(a, rank, world, local)
+    elif wl in STREAM_WL:
         res = run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks)
     elif wl == "idct_sweep":
         res = run_sweep(a, rank, world, local, ClockSampler, measured_peaks)

@@ -256,7 +256,8 @@ B265_API int  b265_upload_frames(b265_ctx* ctx, const b265_frame_job* jobs, int 
 B265_API int  b265_run_batch(b265_ctx* ctx, b265_batch* batch);
 B265_API void b265_free_batch(b265_ctx* ctx, b265_batch* batch);
 /* per-stage device time of the last b265_run_batch with timing enabled (ms):
- * [0] pcm+mc [1] inter residual [2] intra wavefront [3] deblock (bs+V+H) [4] sao [5] total */
+ * [0] pcm+mc [1] residual (inter in place, intra to scratch) + availability masks [2] intra wavefront
+ * [3] deblock (bs+V+H) [4] sao [5] total */
 B265_API int  b265_set_stage_timing(b265_ctx* ctx, int enable);
 B265_API int  b265_get_stage_times(b265_ctx* ctx, float ms[6]);
 

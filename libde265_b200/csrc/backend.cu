@@ -70,6 +70,7 @@ int b265_create(int device, b265_ctx** out) {
   }
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
+  cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
   for (auto& e : ctx->stage_ev) cudaEventCreate(&e);
   *out = ctx;
   return B265_OK;
@@ -91,6 +92,7 @@ void b265_destroy(b265_ctx* ctx) {
   if (ctx->h_stage.p) cudaFreeHost(ctx->h_stage.p);
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
+  if (ctx->ev_sync) cudaEventDestroy(ctx->ev_sync);
   for (auto& e : ctx->stage_ev) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -98,7 +100,14 @@ void b265_destroy(b265_ctx* ctx) {
 
 int b265_sync(b265_ctx* ctx) {
   if (!ctx) return B265_ERR_INVALID_ARG;
-  CK(cudaStreamSynchronize(ctx->stream));
+  // the host cores belong to the CABAC parse threads: wait on a blocking-sync event (the calling thread sleeps)
+  // rather than cudaStreamSynchronize, which spins
+  if (ctx->ev_sync) {
+    CK(cudaEventRecord(ctx->ev_sync, ctx->stream));
+    CK(cudaEventSynchronize(ctx->ev_sync));
+  } else {
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
   return B265_OK;
 }
 

@@ -28,6 +28,7 @@ struct b265_ctx {
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t ev_sync = nullptr;   // blocking-sync event: b265_sync() sleeps instead of spinning on a host core
   cudaEvent_t stage_ev[8] = {};
   bool stage_timing = false;
   float stage_ms[6] = {0, 0, 0, 0, 0, 0};

@@ -341,7 +341,6 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
       ctx->launches++;
       CK_LAUNCH("k_residual_sparse");
     }
-  if (tm) cudaEventRecord(ctx->stage_ev[2], st);
   for (int s = 0; s < 4; s++)
     if (b->n_ires[s]) {
       launch_residual_sparse(st, 2 + s, b->d_frames, b->d_ires_order[s], b->n_ires[s], ctx->sm_count, true);
@@ -352,6 +351,9 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
     launch_intra_prep(st, b->d_frames, b->n_frames, b->max_tus);
     ctx->launches++;
     CK_LAUNCH("k_intra_prep");
+  }
+  if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
+  if (b->n_tickets) {
     launch_intra(st, b->d_frames, b->d_tickets, b->n_tickets, b->d_ticket, ctx->sm_count, b->wave_width, b->log2_ctb);
     ctx->launches++;
     CK_LAUNCH("k_intra_wavefront");
@@ -392,7 +394,7 @@ int b265_submit_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs) {
   CK(cudaSetDevice(ctx->device));
   // the previous submission's staging must be drained before it is freed
   if (ctx->submit_batch) {
-    CK(cudaStreamSynchronize(ctx->stream));
+    { int rs = b265_sync(ctx); if (rs) return rs; }
     b265_free_batch(ctx, ctx->submit_batch);
     ctx->submit_batch = nullptr;
   }
