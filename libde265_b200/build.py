@@ -14,7 +14,8 @@ OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libb265.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-Wall,-Wno-unused-function"]
+COMMON = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC,-fvisibility=hidden,-Wall,-Wno-unused-function"] + \
+    os.environ.get("B265_NVCC_FLAGS", "").split()   # tuning experiments, e.g. -DINTRA_MIN_CTAS=6
 
 
 def _sources():

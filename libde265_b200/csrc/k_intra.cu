@@ -30,6 +30,9 @@
 
 
 #define INTRA_WARPS 4   // one warp per SM sub-partition; several CTAs per SM when the batch is large
+#ifndef INTRA_MIN_CTAS
+#define INTRA_MIN_CTAS 4  // resident CTAs per SM the register budget is sized for
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // k_intra_prep: availability mask of every intra TB (one thread per TU), FrameDev::tb_mask[tu]
@@ -222,7 +225,7 @@ __device__ __forceinline__ void fill_edges(const IntraGeom& g, const CtbEdges& E
 // TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 8 x uint64 {t_ticket, t_deps, t_tile, t_tbs, t_pub,
 // n_tbs, gather, filter} + 4 more {predict, add+store, globaltimer, sm id}: 12 x uint64 per ticket, SM cycles
 template <bool TRACE>
-__global__ void __launch_bounds__(INTRA_WARPS * 32, 4)
+__global__ void __launch_bounds__(INTRA_WARPS * 32, INTRA_MIN_CTAS)
 k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __restrict__ tickets, int n_tickets,
                   unsigned* __restrict__ ticket, unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
