@@ -39,6 +39,14 @@ __device__ __forceinline__ uint8_t ld_relaxed_u8(const uint8_t* p) {
   asm volatile("ld.relaxed.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return (uint8_t)v;
 }
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const void* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(void* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
 __device__ __forceinline__ void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 __device__ __forceinline__ void st_release_u8(uint8_t* p, uint8_t v) {
   asm volatile("st.release.gpu.global.u8 [%0], %1;" ::"l"(p), "r"((unsigned)v) : "memory");
@@ -70,7 +78,9 @@ struct FrameDev {
   int n_tus;
   uint64_t* tb_mask;          // per TU: availability mask of the intra TB's neighbouring units (k_intra_prep)
   int16_t* resid[3];          // residuals of the coded intra TBs (same geometry/pitch as plane[], in samples)
-  uint8_t* done[3];           // intra CTB-wavefront completion flags, one byte per CTB of the plane (raster)
+  uint8_t* done[3];           // per CTB of the plane (raster): 1 = no intra ticket, its samples are final before the wavefront
+  uint8_t* mbox[3];           // intra wavefront border mailboxes: per CTB [bottom row S][right column S] as 8-byte words
+                              // {4 samples, tag}; zero before the launch, written once by the CTB's warp
   int done_pitch[3];          // = ctbs_w
   uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal
   uint32_t* motion;           // per 4x4 luma unit: 4 words {ref ids, mv0, mv1, flags} rasterised from PUs

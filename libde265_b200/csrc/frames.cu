@@ -23,8 +23,8 @@ struct b265_batch {
   uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
   IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
   unsigned* d_ticket = nullptr;
-  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // bs maps cleared per run
-  uint8_t* d_done_init = nullptr;     uint8_t* d_done = nullptr;  size_t done_bytes = 0;  // CTB flags: init -> live per run
+  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // bs maps + border mailboxes, cleared per run
+  uint8_t* d_done_init = nullptr;     size_t done_bytes = 0;   // per CTB plane: 1 = no intra ticket (read-only)
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
   int max_wave = 0;
   int wave_width = 0;                 // largest number of tickets in one wave
@@ -161,9 +161,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   b->upload_bytes = P.off;
   // device-only scratch after the uploaded part
   const size_t o_ticket = P.take(256);
-  const size_t o_done = P.take(done_total);
   const size_t o_zero = P.off;
-  struct SOff { size_t done[3], bs, tmp[3], motion, resid[3], tb_mask; int dp[3]; };
+  struct SOff { size_t done[3], bs, tmp[3], motion, resid[3], tb_mask, mbox[3]; int dp[3]; };
   std::vector<SOff> so(n_jobs);
   {
     size_t acc = 0;
@@ -172,8 +171,11 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
       for (int c = 0; c < 3; c++) {
         so[j].dp[c] = cw_;
-        so[j].done[c] = o_done + acc;
+        so[j].done[c] = o_done_init + acc;   // read-only during the run: 1 = no ticket for this CTB plane
         acc += (size_t)cw_ * ch_;
+        // border mailbox of the intra wavefront: per CTB 2*S samples in flag-in-data form (8 B = 4 samples + tag)
+        const int S = (1 << J.log2_ctb) >> ((c && J.chroma_format_idc) ? 1 : 0);
+        so[j].mbox[c] = (c == 0 || J.chroma_format_idc) ? P.take((size_t)cw_ * ch_ * 4 * S) : 0;
       }
       so[j].bs = P.take((size_t)((J.width + 3) >> 2) * ((J.height + 3) >> 2));
     }
@@ -241,7 +243,6 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   for (int s = 0; s < 4; s++) b->d_ires_order[s] = (uint32_t*)(D + o_ires[s]);
   b->d_tickets = (IntraTicket*)(D + o_tickets);
   b->d_done_init = D + o_done_init;
-  b->d_done = D + o_done;
   b->d_ticket = (unsigned*)(D + o_ticket);
   b->d_zero_begin = D + o_zero;
   static const b265_slice default_slice = {0, 2, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, {}, {}};
@@ -271,6 +272,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       f.pitch[c] = S.pitch[c];
       f.plane[c] = (so[j].tmp[c] && (J.flags & B265_FRAME_SAO)) ? D + so[j].tmp[c] : S.plane[c];
       f.done[c] = D + so[j].done[c];
+      f.mbox[c] = so[j].mbox[c] ? D + so[j].mbox[c] : nullptr;
       f.resid[c] = so[j].resid[c] ? (int16_t*)(D + so[j].resid[c]) : nullptr;
       f.done_pitch[c] = so[j].dp[c];
     }
@@ -323,7 +325,6 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   const bool tm = ctx->stage_timing;
   if (tm) cudaEventRecord(ctx->stage_ev[0], st);
   if (b->zero_bytes) CK(cudaMemsetAsync(b->d_zero_begin, 0, b->zero_bytes, st));
-  if (b->done_bytes) CK(cudaMemcpyAsync(b->d_done, b->d_done_init, b->done_bytes, cudaMemcpyDeviceToDevice, st));
   if (b->max_pcms) {
     launch_pcm(st, b->d_frames, b->n_frames, b->max_pcms);
     ctx->launches++;

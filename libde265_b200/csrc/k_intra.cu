@@ -162,64 +162,110 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
   }
 }
 
-// Wait until the (up to four) flags polled by lanes 0..3 are set.  The loop is executed by the WHOLE warp
-// with a warp-uniform exit condition: a per-lane polling loop leaves the warp split into independently
-// scheduled groups, which then walk the TBs separately and pay the slow path of every warp collective.
-// Acquire loads: the poll that sees the flag set orders the sample loads that follow (no separate fence
-// on the path between two dependent CTBs); the vote extends the ordering to the other lanes.
-__device__ __forceinline__ void wait_flags(const uint8_t* flag, bool polls, unsigned sleep_ns) {
-  for (;;) {
-    unsigned v = 1;
-    if (polls) v = ld_acquire_u8(flag);
-    if (__all_sync(B265_FULL_MASK, v != 0)) break;
-    if (sleep_ns) __nanosleep(sleep_ns);
-  }
-}
-
-// Copy the samples bordering the CTB (and, for CTBs that also hold inter/PCM samples, the edge rows/columns
-// of the CTB itself) from L2 into the edge store.  Called by the whole warp after the neighbour flags have
-// been acquired.  Loads are issued back to back (one L2 round trip), then stored.
-__device__ __forceinline__ void fill_edges(const IntraGeom& g, const CtbEdges& E, bool interior) {
+// ---- border exchange between CTBs: flag-in-data mailboxes ---------------------------------------------
+// A CTB's warp posts the CTB's bottom row and right column (the only samples later CTBs can read) as
+// 8-byte words {4 samples, tag != 0} written with ONE 64-bit store each: a reader that sees the tag has
+// the samples, so neither side needs a fence (the scheme of low-latency collective protocols).  The
+// mailboxes are zeroed before the launch.  Layout per CTB: S/4 words bottom row, S/4 words right column.
+// Neighbours without a ticket (inter/PCM CTBs, done[] == 1) were finished by earlier launches: their
+// samples are read from the plane.
+//
+// The polling loop is executed by the WHOLE warp with a warp-uniform exit: a per-lane loop leaves the
+// warp split into independently scheduled groups, which then walk the TBs separately and pay the slow
+// path of every warp collective (measured: 3x).
+__device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges& E, const uint8_t* done, const uint8_t* mbox,
+                                              int ctbs_w, bool interior, unsigned sleep_ns) {
   const int lane = lane_id();
-  const int S = E.S, pitch = g.pitch;
+  const int S = E.S, q = S / 4, pitch = g.pitch;
   const int W = (g.width + g.sh) >> g.sh, H = (g.height + g.sh) >> g.sh;
   const uint8_t* org = g.plane + (size_t)E.y0 * pitch + E.x0;
-  // row -1: columns 0..2S-1 as words (the plane width is a multiple of 4): S/2 <= 32 words; corner by lane 31
-  uint32_t top = 0, corner = 0, left[2] = {0, 0};
-  const bool has_top = g.cy > 0 && lane < S / 2 && E.x0 + 4 * lane < W;
-  if (has_top) top = ld_cg_u32(org - pitch + 4 * lane);
-  const bool has_corner = g.cy > 0 && g.cx > 0 && lane == 31;
-  if (has_corner) corner = ld_cg_u8(org - pitch - 1);
-#pragma unroll
-  for (int k = 0; k < 2; k++) {  // column -1: S <= 64 rows
-    const int r = lane + 32 * k;
-    if (g.cx > 0 && r < S && E.y0 + r < H) left[k] = ld_cg_u8(org + (size_t)r * pitch - 1);
-  }
-  if (has_top) *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * lane) = top;
-  if (has_corner) E.rows[15] = (uint8_t)corner;
+  // slots: [0,q) upper CTB's bottom row, [q,2q) upper-right CTB's bottom row, [2q,3q) left CTB's right column,
+  // 3q: corner (last word of the upper-left CTB's bottom row); two slots per lane (3q+1 <= 49)
+  const uint8_t* src[2];
+  int kind[2];   // 0 nothing, 1 mailbox word, 2 plane (row word), 3 plane (column word, 4 strided bytes), 4 plane corner byte
+  int slotv[2];
 #pragma unroll
   for (int k = 0; k < 2; k++) {
-    const int r = lane + 32 * k;
-    if (g.cx > 0 && r < S) {
-      E.cols[r] = (uint8_t)left[k];
-      if ((r & 3) == 3) E.rows[((r + 1) >> 2) * E.rstride + 15] = (uint8_t)left[k];  // sample (-1, r) of the inner edge rows
+    const int slot = lane + 32 * k;
+    slotv[k] = slot;
+    kind[k] = 0;
+    src[k] = nullptr;
+    if (slot > 3 * q) continue;
+    const int piece = slot == 3 * q ? 3 : slot / q, w = slot == 3 * q ? q - 1 : slot % q;
+    // neighbour CTB of the piece
+    const int nx = g.cx + (piece == 1 ? 1 : (piece == 0 ? 0 : -1)), ny = g.cy - (piece == 2 ? 0 : 1);
+    // not usable for prediction (outside the picture, other slice/tile): never read, never waited for
+    if (!((g.nb >> (piece == 0 ? 2 : piece == 1 ? 3 : piece == 2 ? 0 : 1)) & 1)) continue;
+    const int nctb = ny * ctbs_w + nx;
+    if (__ldg(done + nctb) == 0) {   // the neighbour posts its borders in this launch
+      kind[k] = 1;
+      src[k] = mbox + (size_t)nctb * (4 * S) + (piece == 2 ? 2 * S : 0) + 8 * w;
+    } else if (piece == 2) {
+      if (E.y0 + 4 * w < H) { kind[k] = 3; src[k] = org + (size_t)(4 * w) * pitch - 1; }
+    } else if (piece == 3) {
+      kind[k] = 4; src[k] = org - pitch - 1;
+    } else {
+      const int x = (piece == 1 ? S : 0) + 4 * w;
+      if (E.x0 + x < W) { kind[k] = 2; src[k] = org - pitch + x; }
     }
   }
+  uint32_t val[2] = {0, 0};
+  bool have[2] = {kind[0] != 1, kind[1] != 1};
+  // plane reads (rare: mixed pictures)
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    if (kind[k] == 2) val[k] = ld_cg_u32(src[k]);
+    else if (kind[k] == 3) {
+      for (int i = 0; i < 4; i++) val[k] |= (uint32_t)ld_cg_u8(src[k] + (size_t)i * pitch) << (8 * i);
+    } else if (kind[k] == 4) val[k] = (uint32_t)ld_cg_u8(src[k]) << 24;
+  }
+  for (;;) {
+#pragma unroll
+    for (int k = 0; k < 2; k++)
+      if (!have[k]) {
+        const unsigned long long v = ld_relaxed_u64(src[k]);
+        if ((uint32_t)(v >> 32) != 0) { val[k] = (uint32_t)v; have[k] = true; }
+      }
+    if (__all_sync(B265_FULL_MASK, have[0] && have[1])) break;
+    if (sleep_ns) __nanosleep(sleep_ns);
+  }
+  // into the edge store
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    if (kind[k] == 0) continue;
+    const int slot = slotv[k];
+    if (slot < 2 * q) *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * slot) = val[k];
+    else if (slot < 3 * q) {
+      const int w = slot - 2 * q;
+      *reinterpret_cast<uint32_t*>(E.cols + 4 * w) = val[k];
+      E.rows[(w + 1) * E.rstride + 15] = (uint8_t)(val[k] >> 24);   // sample (-1, 4w+3) of the inner edge rows
+    } else E.rows[15] = (uint8_t)(val[k] >> 24);
+  }
   if (interior) {
-    // rows 4q-1 (q >= 1), columns 0..S-1
+    // CTBs that also hold inter/PCM samples: their edge rows 4q-1 (q >= 1) and columns 4q-1 come from the plane
     const int wpr = S / 4;
     for (int i = lane; i < (S / 4) * wpr; i += 32) {
-      const int q = 1 + i / wpr, w = i % wpr, r = 4 * q - 1;
+      const int qq = 1 + i / wpr, w = i % wpr, r = 4 * qq - 1;
       if (E.y0 + r < H && E.x0 + 4 * w < W)
-        *reinterpret_cast<uint32_t*>(E.rows + q * E.rstride + 16 + 4 * w) = ld_cg_u32(org + (size_t)r * pitch + 4 * w);
+        *reinterpret_cast<uint32_t*>(E.rows + qq * E.rstride + 16 + 4 * w) = ld_cg_u32(org + (size_t)r * pitch + 4 * w);
     }
-    // columns 4q-1 (q >= 1), rows 0..S-1
     for (int i = lane; i < (S / 4) * S; i += 32) {
-      const int q = 1 + i / S, r = i % S, cidx = 4 * q - 1;
-      if (E.y0 + r < H && E.x0 + cidx < W) E.cols[q * S + r] = ld_cg_u8(org + (size_t)r * pitch + cidx);
+      const int qq = 1 + i / S, r = i % S, cc = 4 * qq - 1;
+      if (E.y0 + r < H && E.x0 + cc < W) E.cols[qq * S + r] = ld_cg_u8(org + (size_t)r * pitch + cc);
     }
   }
   __syncwarp();
+}
+
+// post this CTB's bottom row and right column (edge store rows[S/4], cols[S/4]) to its mailbox
+__device__ __forceinline__ void post_borders(const CtbEdges& E, uint8_t* mbox, int ctb) {
+  const int lane = lane_id();
+  const int S = E.S, q = S / 4;
+  if (lane < 2 * q) {
+    const uint8_t* s = lane < q ? E.rows + q * E.rstride + 16 + 4 * lane : E.cols + q * S + 4 * (lane - q);
+    const unsigned long long v = (unsigned long long)*reinterpret_cast<const uint32_t*>(s) | (1ull << 32);
+    st_relaxed_u64(mbox + (size_t)ctb * (4 * S) + 8 * lane, v);
+  }
 }
 
 // TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 8 x uint64 {t_ticket, t_deps, t_tile, t_tbs, t_pub,
@@ -246,7 +292,8 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
   IntraGeom g;
   int ctbs_w = 1;
   const b265_ctb* __restrict__ ctbs = nullptr;
-  uint8_t* done = nullptr;
+  const uint8_t* done = nullptr;
+  uint8_t* mbox = nullptr;
   const uint4* tus4 = nullptr;
   const uint2* masks = nullptr;
   auto load_constants = [&](const IntraTicket& k) {
@@ -256,6 +303,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     ctbs_w = f->ctbs_w;
     ctbs = f->ctbs;
     done = f->done[c];
+    mbox = f->mbox[c];
     tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
     masks = reinterpret_cast<const uint2*>(f->tb_mask);
     g.sh = (c && f->cw) ? 1 : 0;
@@ -296,20 +344,19 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     E.cols = my_edges + (E.S / 4 + 1) * E.rstride;
     E.x0 = cx * E.S;
     E.y0 = cy * E.S;
-    // neighbours: lane 0 left, 1 upper-left, 2 upper, 3 upper-right; lane 4 reads this CTB's own record
+    // neighbouring CTBs usable for prediction: lane 0 left, 1 upper-left, 2 upper, 3 upper-right; lane 4 = this CTB
     {
       const int nx = cx + (lane == 3 ? 1 : (lane == 2 || lane == 4 ? 0 : -1)), ny = cy - (lane == 0 || lane == 4 ? 0 : 1);
       const bool exists = lane < 5 && nx >= 0 && ny >= 0 && nx < ctbs_w;
       b265_ctb rec = {0, 0, 0};
       if (exists && ctbs) rec = ctbs[ny * ctbs_w + nx];
-      wait_flags(done + ny * ctbs_w + nx, exists && lane < 4, sleep_ns);
       const int my_ts = __shfl_sync(B265_FULL_MASK, rec.addr_ts, 4);
       const int my_slice = __shfl_sync(B265_FULL_MASK, (int)rec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)rec.tile, 4);
       const bool usable = exists && lane < 4 && (!ctbs || (rec.slice == my_slice && rec.tile == my_tile_id && rec.addr_ts < my_ts));
-      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;   // (bar.warp.sync semantics: the acquire of lanes 0-3 covers the warp)
+      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;
     }
     if (TRACE) tr1 = clock64();
-    fill_edges(g, E, (tk.flags & B265_TICKET_MIXED) != 0);
+    fetch_borders(g, E, done, mbox, ctbs_w, (tk.flags & B265_TICKET_MIXED) != 0, sleep_ns);
     if (TRACE) tr2 = clock64();
     // the next ticket's record travels while the TBs are processed
     t_next = __shfl_sync(B265_FULL_MASK, t_next, 0);
@@ -350,16 +397,14 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     }
     if (TRACE) tr3 = clock64();
     // next ticket's picture constants: issued before the release store so that both round trips overlap
-    uint8_t* my_flag = done + tk.ctb;
+    uint8_t* my_mbox = mbox;
+    const int my_ctb = (int)tk.ctb;
     const unsigned t_cur = t;
     t = t_next;
     tk = tk_next;
     if (t < (unsigned)n_tickets) load_constants(tk);
-    // publish: every sample of this CTB plane is final (pre-deblock) now
-    // (bar.warp.sync orders the other lanes' stores before lane 0's release store, which is cumulative)
-    __syncwarp();
-    if (lane == 0) st_release_u8(my_flag, 1);
-    __syncwarp();
+    // post the borders later CTBs read (the picture itself is complete at the end of the launch)
+    post_borders(E, my_mbox, my_ctb);
     if (TRACE && lane == 0) {
       unsigned smid;
       asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
