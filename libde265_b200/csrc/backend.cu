@@ -28,6 +28,7 @@ int b265_fail(b265_ctx* ctx, int status, const char* what, cudaError_t e) {
   if (ctx) {
     ctx->last_error = std::string(what) + ": " + cudaGetErrorString(e);
   }
+  if (getenv("B265_DEBUG")) fprintf(stderr, "b265: %s: %s\n", what, cudaGetErrorString(e));
   if (e == cudaErrorMemoryAllocation) return B265_ERR_OUT_OF_MEMORY;
   return status;
 }

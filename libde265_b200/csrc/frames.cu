@@ -4,6 +4,8 @@
 // (by size) and the intra CTB tickets (one per picture/CTB/plane holding intra TBs, counting-sorted by
 // the CTB anti-diagonal wave = ctbX + 2*ctbY); pack every list of every frame into ONE pinned staging
 // buffer and ship it with ONE cudaMemcpyAsync.  Device work: see b265_run_batch.
+#include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <vector>
@@ -51,8 +53,15 @@ extern "C" void b265_free_batch(b265_ctx* ctx, b265_batch* b) {
   delete b;
 }
 
+// argument validation failures are reported with their line when B265_DEBUG is set
+static int reject(int line, int code) {
+  static const bool verbose = getenv("B265_DEBUG") != nullptr;
+  if (verbose) fprintf(stderr, "b265: frames.cu:%d rejects the job (error %d)\n", line, code);
+  return code;
+}
+
 static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b265_batch* b) {
-  if (n_jobs > 255) return B265_ERR_INVALID_ARG;
+  if (n_jobs > 255) return reject(__LINE__, B265_ERR_INVALID_ARG);
   b->n_frames = n_jobs;
   b->frames.assign(n_jobs, FrameDev());
   struct Key { uint32_t wave; IntraTicket t; };
@@ -67,7 +76,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
     if (J.bit_depth != 8 || J.chroma_format_idc > 1 || J.n_tus >= (1 << 24) || J.n_pus >= (1 << 24))
-      return B265_ERR_UNSUPPORTED;
+      return reject(__LINE__, B265_ERR_UNSUPPORTED);
     const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
     const int nctb = cw_ * ch_;
     ctb_first.assign(nctb, 0);
@@ -75,18 +84,18 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     ctb_has.assign(nctb, 0);
     ctb_area.assign((size_t)3 * nctb, 0);
     b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
-    if (J.log2_ctb < 4 || J.log2_ctb > 6) return B265_ERR_INVALID_ARG;
+    if (J.log2_ctb < 4 || J.log2_ctb > 6) return reject(__LINE__, B265_ERR_INVALID_ARG);
     int cur = -1;
     for (int i = 0; i < J.n_tus; i++) {
       const b265_tu& t = J.tus[i];
       const int c = t.cidx_log2 & 3, lg = (t.cidx_log2 >> 2) & 7;
-      if (lg < 2 || lg > 5 || c > 2) return B265_ERR_INVALID_ARG;
+      if (lg < 2 || lg > 5 || c > 2) return reject(__LINE__, B265_ERR_INVALID_ARG);
       const int sh = (c && J.chroma_format_idc) ? 1 : 0;
       const int bx = (t.x << sh) >> J.log2_ctb, by = (t.y << sh) >> J.log2_ctb;
-      if (bx >= cw_ || by >= ch_) return B265_ERR_INVALID_ARG;
+      if (bx >= cw_ || by >= ch_) return reject(__LINE__, B265_ERR_INVALID_ARG);
       const int ctb = by * cw_ + bx;
       if (ctb != cur) {
-        if (ctb_count[ctb]) return B265_ERR_INVALID_ARG;  // TUs of a CTB must be contiguous (decoding order)
+        if (ctb_count[ctb]) return reject(__LINE__, B265_ERR_INVALID_ARG);  // TUs of a CTB must be contiguous (decoding order)
         ctb_first[ctb] = (uint32_t)i;
         cur = ctb;
       }
@@ -205,7 +214,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       if (!need[j]) continue;
       const b265_frame_job& J = jobs[j];
       if (J.dst_surface < 0 || J.dst_surface >= (int)ctx->surfaces.size() || !ctx->surfaces[J.dst_surface].used)
-        return B265_ERR_INVALID_ARG;
+        return reject(__LINE__, B265_ERR_INVALID_ARG);
       const Surface& S = ctx->surfaces[J.dst_surface];
       so[j].resid[0] = P.take((size_t)2 * S.pitch[0] * J.height);
       if (J.chroma_format_idc) {
@@ -264,9 +273,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     cp(fo[j].pcm_samples, J.pcm_samples, (size_t)J.n_pcm_samples);
     FrameDev& f = b->frames[j];
     if (J.dst_surface < 0 || J.dst_surface >= (int)ctx->surfaces.size() || !ctx->surfaces[J.dst_surface].used)
-      return B265_ERR_INVALID_ARG;
+      return reject(__LINE__, B265_ERR_INVALID_ARG);
     const Surface& S = ctx->surfaces[J.dst_surface];
-    if (S.width != J.width || S.height != J.height) return B265_ERR_INVALID_ARG;
+    if (S.width != J.width || S.height != J.height) return reject(__LINE__, B265_ERR_INVALID_ARG);
     for (int c = 0; c < 3; c++) {
       f.out[c] = S.plane[c];
       f.pitch[c] = S.pitch[c];
@@ -304,7 +313,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.n_refs = std::min(J.n_refs, 16);
     for (int r = 0; r < f.n_refs; r++) {
       const int sid = J.ref_surfaces[r];
-      if (sid < 0 || sid >= (int)ctx->surfaces.size() || !ctx->surfaces[sid].used) return B265_ERR_INVALID_ARG;
+      if (sid < 0 || sid >= (int)ctx->surfaces.size() || !ctx->surfaces[sid].used) return reject(__LINE__, B265_ERR_INVALID_ARG);
       for (int c = 0; c < 3; c++) f.ref_plane[r][c] = ctx->surfaces[sid].plane[c];
       f.ref_poc[r] = J.ref_poc[r];
     }
@@ -375,7 +384,7 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
 extern "C" {
 
 int b265_upload_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b265_batch** out) {
-  if (!ctx || !jobs || n_jobs <= 0 || !out) return B265_ERR_INVALID_ARG;
+  if (!ctx || !jobs || n_jobs <= 0 || !out) return reject(__LINE__, B265_ERR_INVALID_ARG);
   CK(cudaSetDevice(ctx->device));
   b265_batch* b = new b265_batch();
   int r = build_batch(ctx, jobs, n_jobs, b);
@@ -385,13 +394,13 @@ int b265_upload_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
 }
 
 int b265_run_batch(b265_ctx* ctx, b265_batch* batch) {
-  if (!ctx || !batch) return B265_ERR_INVALID_ARG;
+  if (!ctx || !batch) return reject(__LINE__, B265_ERR_INVALID_ARG);
   CK(cudaSetDevice(ctx->device));
   return run_batch(ctx, batch);
 }
 
 int b265_submit_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs) {
-  if (!ctx || !jobs || n_jobs <= 0) return B265_ERR_INVALID_ARG;
+  if (!ctx || !jobs || n_jobs <= 0) return reject(__LINE__, B265_ERR_INVALID_ARG);
   CK(cudaSetDevice(ctx->device));
   // the previous submission's staging must be drained before it is freed
   if (ctx->submit_batch) {
@@ -408,13 +417,13 @@ int b265_submit_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs) {
 }
 
 int b265_set_stage_timing(b265_ctx* ctx, int enable) {
-  if (!ctx) return B265_ERR_INVALID_ARG;
+  if (!ctx) return reject(__LINE__, B265_ERR_INVALID_ARG);
   ctx->stage_timing = enable != 0;
   return B265_OK;
 }
 
 int b265_get_stage_times(b265_ctx* ctx, float ms[6]) {
-  if (!ctx || !ms) return B265_ERR_INVALID_ARG;
+  if (!ctx || !ms) return reject(__LINE__, B265_ERR_INVALID_ARG);
   for (int i = 0; i < 6; i++) ms[i] = ctx->stage_ms[i];
   return B265_OK;
 }

@@ -7,6 +7,7 @@
 #pragma once
 #include <stdint.h>
 #include <string.h>
+#include "bits.h"
 
 namespace b265h {
 
@@ -59,7 +60,17 @@ extern const uint8_t g_cabac_next_lps[64];
 extern const uint8_t g_cabac_renorm[32];
 extern uint8_t g_cabac_next[256];   // next context byte, indexed by (ctx << 1) | decodedLps
 
+// what the syntax walk tells the engine about the bin(s) that follow; the decoder ignores it, the
+// test-stream generator uses it to keep randomly drawn values legal
+enum Hint { HINT_PCM_FLAG, HINT_QP_DELTA_SUFFIX, HINT_COEFF_REMAINING, HINT_END_OF_SEGMENT, HINT_END_OF_SUBSET };
+
 struct Cabac {
+  typedef Cabac Local;            // residual_coding works on a register copy of the engine
+  struct Setup {};
+  void setup(const Setup&) {}
+  void commit(Cabac& dst) const { dst = *this; }
+  static inline void hint(int, int) {}
+  static inline void set_ctx_base(const Ctx*) {}
   const uint8_t* cur = nullptr;
   const uint8_t* end = nullptr;
   uint32_t range = 510;   // after start(): kept in [256, 510] between decisions
@@ -131,6 +142,19 @@ struct Cabac {
     if (n >= 3) return (v << n) | bypass_chunk(n);
     while (n-- > 0) v = (v << 1) | (uint32_t)bypass();
     return v;
+  }
+  // PCM sample data (7.3.8.7): byte-aligned raw bits at the current position, then re-initialisation.
+  // Appends the samples (shifted to the full bit depth) to `out`; false when the data ends early.
+  template <class Vec>
+  bool pcm_samples(int n_luma, int bits_luma, int shift_luma, int n_chroma, int bits_chroma, int shift_chroma, Vec& out) {
+    BitReader br(cur, (size_t)(end - cur));
+    for (int i = 0; i < n_luma; i++) out.push_back((uint8_t)(br.u(bits_luma) << shift_luma));
+    for (int i = 0; i < n_chroma; i++) out.push_back((uint8_t)(br.u(bits_chroma) << shift_chroma));
+    if (br.err) return false;
+    br.align();
+    cur += br.pos >> 3;
+    start();
+    return true;
   }
   inline int terminate() {
     range -= 2;

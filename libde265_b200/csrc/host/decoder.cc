@@ -11,6 +11,7 @@
 // so the CPU parses picture N+k while the GPU reconstructs picture N.  There is no CPU pixel path:
 // if the CUDA context cannot be created every decode call fails with
 // DE265_ERROR_LIBRARY_INITIALIZATION_FAILED.
+#include <stdio.h>
 #include <string.h>
 #include <stdlib.h>
 #include <chrono>
@@ -178,6 +179,7 @@ struct Decoder {
   void parse_one(de265_image* img) {
     const double t0 = now_s();
     int err = decode_picture_slices(img->pic);
+    if (err && getenv("B265_DEBUG")) fprintf(stderr, "b265: slice data of picture %llu: error %d\n", (unsigned long long)img->pic.decode_index, err);
     img->pic.error = err;
     img->pic.parse_seconds = now_s() - t0;
     img->pic.release_parse_state();
@@ -380,6 +382,7 @@ struct Decoder {
         }
         if (r == B265_OK) r = b265_sync(gpu);
         for (de265_image* img : good) {
+          if (r != B265_OK && getenv("B265_DEBUG")) fprintf(stderr, "b265: back end status %d: %s\n", r, b265_last_error(gpu));
           if (r != B265_OK) img->pic.error = r == B265_ERR_OUT_OF_MEMORY ? DE265_ERROR_OUT_OF_MEMORY : DE265_ERROR_UNSPECIFIED_DECODING_ERROR;
           b265_surface_release(gpu, img->pic.surface);
           img->pic.surface = -1;

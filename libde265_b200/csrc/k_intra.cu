@@ -420,8 +420,10 @@ static int tile_bytes_for(int log2_ctb) { return (ctb_edges_bytes(1 << log2_ctb)
 int intra_max_resident_ctas(int sm_count, int log2_ctb) {
   int per_sm = 0;
   const size_t dyn = (size_t)INTRA_WARPS * tile_bytes_for(log2_ctb);
-  cudaFuncSetAttribute(k_intra_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
-  cudaFuncSetAttribute(k_intra_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
+  // the opt-in limit is a property of the function, not of a launch: always allow the largest CTB size
+  const size_t dyn_max = (size_t)INTRA_WARPS * tile_bytes_for(6);
+  cudaFuncSetAttribute(k_intra_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
+  cudaFuncSetAttribute(k_intra_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intra_wavefront<false>, INTRA_WARPS * 32, dyn);
   if (per_sm < 1) per_sm = 1;
   return per_sm * sm_count;

@@ -73,6 +73,33 @@ def test_parser_matches_reference_md5(name, max_frames):
         assert got[i] == gold["md5"][i], "frame %d of %s" % (i, name)
 
 
+def generated_streams():
+    """random-syntax streams of tools/streamgen (tools/make_gen_streams.py): SAO, PCM, transform skip, cu_qp_delta,
+    scaling lists, tiles, wavefronts, (dependent) slice segments, deblocking overrides, range-extension flags"""
+    return sorted(f[:-len(".md5.json")] for f in os.listdir(STREAMS) if f.startswith("gen_") and f.endswith(".md5.json"))
+
+
+@pytest.mark.parametrize("name", generated_streams())
+def test_parser_matches_reference_md5_generated(name):
+    data, gold = load_stream(name)
+    got = parse_and_reconstruct(data)
+    assert len(got) == gold["frames"]
+    for i in range(gold["frames"]):
+        assert got[i] == gold["md5"][i], "frame %d of %s" % (i, name)
+
+
+def test_generated_streams_cover_the_tools():
+    """the catalogue really switches the tools on (guards against a silently reduced golden set)"""
+    names = generated_streams()
+    assert len(names) >= 40
+    args = [json.load(open(os.path.join(STREAMS, n + ".md5.json")))["args"] for n in names]
+    for key in ("sao", "pcm", "tskip", "cu_qp_delta", "sign_hiding", "tq_bypass", "wpp", "dep_slices", "dbk_override",
+                "rext_implicit_rdpcm", "chroma_qp_offset_list"):
+        assert sum(1 for a in args if a.get(key)) >= 2, key
+    assert {a.get("scaling", 0) for a in args} >= {0, 1, 2, 3}
+    assert sum(1 for a in args if a.get("tile_cols", 1) * a.get("tile_rows", 1) > 1) >= 3
+
+
 def test_parser_threads_same_result():
     data = open(os.path.join(STREAMS, "tiny_416x240_q30.bin"), "rb").read()
     assert parse_and_reconstruct(data, threads=0) == parse_and_reconstruct(data, threads=3)

@@ -1,0 +1,141 @@
+#!/usr/bin/env python3
+"""Random-syntax test streams (tools/streamgen) and their golden MD5s from the unmodified reference decoder.
+
+Test infrastructure.  Runs only in the build container (needs oracle/_ref/dec265 built from /root/reference);
+the outputs `tests/golden/streams/gen_*.bin` + `gen_*.md5.json` are committed, the GPU box needs neither the
+generator nor the reference.  The named streams switch on the coding tools the reference's encoder cannot
+produce (SAO, PCM, transform skip, cu_qp_delta, scaling lists, tiles, wavefronts, slices and dependent slice
+segments, deblocking overrides, range-extension flags); the `fuzz_*` streams draw a whole configuration at random.
+"""
+import argparse, json, os, random, subprocess, sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from tools.make_streams import OUT, ref_md5  # noqa: E402
+
+GEN = os.path.join(ROOT, "tools", "streamgen", "b265_streamgen")
+HOST = os.path.join(ROOT, "libde265_b200", "csrc", "host")
+
+
+def build_generator():
+    src = [os.path.join(ROOT, "tools", "streamgen", "streamgen.cc"), os.path.join(HOST, "params.cc"),
+           os.path.join(HOST, "cabac.cc")]
+    deps = src + [os.path.join(HOST, f) for f in ("slice_syntax.h", "cabac.h", "picture.h", "params.h", "bits.h")]
+    if os.path.exists(GEN) and all(os.path.getmtime(GEN) >= os.path.getmtime(d) for d in deps):
+        return GEN
+    subprocess.run(["g++", "-std=c++17", "-O2", "-o", GEN] + src, check=True)
+    return GEN
+
+
+NAMED = {
+    # name: generator arguments
+    "gen_base_416x240": dict(seed=2, w=416, h=240, frames=3),
+    "gen_sao_200x136": dict(seed=3, w=200, h=136, sao=1),
+    "gen_pcm_128x96": dict(seed=5, w=128, h=96, pcm=1, pcm_bits_luma=5, pcm_bits_chroma=6, pcm_lf_disabled=1, sao=1),
+    "gen_pcm8_ctb16_200x136": dict(seed=30, w=200, h=136, ctb=4, sao=1, pcm=1, maxpcm=4),
+    "gen_tskip_rext_128x96": dict(seed=28, w=128, h=96, tskip=1, max_tskip=4, rext_rotation=1, rext_context=1,
+                                  rext_implicit_rdpcm=1, tq_bypass=1),
+    "gen_qpdelta_ctb64_256x128": dict(seed=8, w=256, h=128, ctb=6, cu_qp_delta=1, qp_delta_depth=2, sign_hiding=1),
+    "gen_chromaqp_128x96": dict(seed=29, w=128, h=96, chroma_qp_offset_list=1, cb_qp_offset=3, cr_qp_offset=-4,
+                                slice_chroma_offsets=1, cu_qp_delta=1, slice_ctbs=7),
+    "gen_scaling_sps_128x96": dict(seed=12, w=128, h=96, scaling=2),
+    "gen_scaling_pps_128x96": dict(seed=13, w=128, h=96, scaling=3, density=2.0),
+    "gen_scaling_default_128x96": dict(seed=11, w=128, h=96, scaling=1),
+    "gen_tiles_416x240": dict(seed=21, w=416, h=240, tile_cols=3, tile_rows=2, tiles_uniform=0, lf_across_tiles=0, sao=1),
+    "gen_wpp_256x192": dict(seed=22, w=256, h=192, wpp=1, sao=1),
+    "gen_slices_dep_256x192": dict(seed=24, w=256, h=192, slice_ctbs=4, dep_slices=1, sao=1, lf_across_slices=1),
+    "gen_slices_wpp_256x192": dict(seed=25, w=256, h=192, slice_ctbs=4, dep_slices=1, wpp=1),
+    "gen_slices_tiles_256x192": dict(seed=26, w=256, h=192, slice_ctbs=3, dep_slices=1, tile_cols=2, tile_rows=2, sao=1),
+    "gen_dbk_override_256x192": dict(seed=27, w=256, h=192, slice_ctbs=6, dbk_override=1, lf_across_slices=0, sao=1),
+    "gen_tb8_ctb64_320x192": dict(seed=31, w=320, h=192, ctb=6, mincb=4, mintb=3, sao=1, thdepth=3),
+    "gen_bypass_rdpcm_128x64": dict(seed=123, w=128, h=64, ctb=4, mincb=4, tq_bypass=1, rext_implicit_rdpcm=1),
+    # one large picture with everything the wavefront and the post filters have to get right at once
+    "gen_all_1280x720": dict(seed=77, w=1280, h=720, frames=2, sao=1, pcm=1, tskip=1, cu_qp_delta=1, sign_hiding=1,
+                             tq_bypass=1, scaling=3, slice_ctbs=60, dep_slices=1, dbk_override=1, lf_across_slices=1,
+                             p_pcm=0.03, p_tq_bypass=0.05),
+}
+
+
+def fuzz_config(seed):
+    """a whole configuration drawn at random, legal by construction (7.4.3.2, 7.4.3.3 range constraints)"""
+    rnd = random.Random(seed)
+    ctb = rnd.choice([4, 5, 5, 6])
+    mincb = rnd.choice([c for c in (3, 4, 5) if c <= ctb])
+    mintb = rnd.choice([t for t in (2, 3, 4) if t < mincb])
+    maxtb = rnd.choice([t for t in (3, 4, 5) if mintb <= t <= min(5, ctb)])
+    w = rnd.choice([64, 96, 128, 200, 256, 320, 416])
+    h = rnd.choice([64, 72, 96, 136, 192, 240])
+    m = 1 << mincb
+    w, h = max(m, w // m * m), max(m, h // m * m)
+    a = dict(seed=seed, w=w, h=h, ctb=ctb, mincb=mincb, mintb=mintb, maxtb=maxtb, frames=rnd.choice([1, 2, 3]),
+             thdepth=rnd.randint(0, min(4, ctb - mintb)))
+    cw, ch = -(-w >> ctb), -(-h >> ctb)
+    flag = lambda p=0.5: int(rnd.random() < p)
+    a["sao"], a["strong_intra"], a["sign_hiding"] = flag(), flag(), flag()
+    a["tq_bypass"], a["cip"] = flag(0.3), flag(0.3)
+    if flag(0.4):
+        lo, hi = min(mincb, 5), min(ctb, 5)
+        a.update(pcm=1, pcm_bits_luma=rnd.randint(1, 8), pcm_bits_chroma=rnd.randint(1, 8), pcm_lf_disabled=flag())
+        a["minpcm"] = rnd.randint(lo, hi)
+        a["maxpcm"] = rnd.randint(a["minpcm"], hi)
+    if flag(0.5):
+        a.update(tskip=1, max_tskip=min(maxtb, rnd.choice([2, 2, 3, 4, 5])))
+    if flag(0.4):
+        a.update(rext_rotation=flag(), rext_context=flag(), rext_implicit_rdpcm=flag())
+    if flag(0.5):
+        a.update(cu_qp_delta=1, qp_delta_depth=rnd.randint(0, ctb - mincb))
+    a.update(cb_qp_offset=rnd.randint(-6, 6), cr_qp_offset=rnd.randint(-6, 6), slice_chroma_offsets=flag())
+    if flag(0.3):
+        a.update(chroma_qp_offset_list=1, chroma_qp_offset_depth=rnd.randint(0, ctb - mincb))
+    a["scaling"] = rnd.choice([0, 0, 1, 2, 3])
+    a["init_qp"] = rnd.randint(15, 40)
+    a["qp_lo"] = rnd.randint(5, 30)
+    a["qp_hi"] = a["qp_lo"] + rnd.randint(0, 20)
+    par = rnd.choice(["none", "tiles", "wpp", "none"])
+    if par == "tiles" and cw * ch > 1:
+        a.update(tile_cols=rnd.randint(1, min(4, cw)), tile_rows=rnd.randint(1, min(3, ch)), tiles_uniform=flag(),
+                 lf_across_tiles=flag())
+    if par == "wpp":
+        a["wpp"] = 1
+    if flag(0.6):
+        a.update(slice_ctbs=rnd.randint(1, 12), dep_slices=flag(), lf_across_slices=flag())
+    a["dbk_control"] = flag(0.8)
+    if a["dbk_control"]:
+        a.update(dbk_override=flag(), dbk_disabled=flag(0.3), beta_div2=rnd.randint(-6, 6), tc_div2=rnd.randint(-6, 6))
+    a["density"] = rnd.choice([0.5, 1.0, 1.0, 1.5, 2.5])
+    a["p_split_cu"] = rnd.choice([0.3, 0.5, 0.7])
+    a["p_split_tu"] = rnd.choice([0.2, 0.4, 0.7])
+    a["p_big_coeff"] = rnd.choice([0.0, 0.01, 0.05])
+    return a
+
+
+FUZZ_SEEDS = list(range(1000, 1024))
+
+
+def catalogue():
+    c = dict(NAMED)
+    for s in FUZZ_SEEDS:
+        c["gen_fuzz_%d" % s] = fuzz_config(s)
+    return c
+
+
+def generate(name, args, out_dir=OUT):
+    path = os.path.join(out_dir, name + ".bin")
+    subprocess.run([build_generator(), path] + ["%s=%s" % kv for kv in args.items()], check=True)
+    md5 = ref_md5(path, args["w"], args["h"])
+    json.dump({"width": args["w"], "height": args["h"], "frames": len(md5), "generator": "tools/make_gen_streams.py",
+               "args": args, "md5": md5}, open(os.path.join(out_dir, name + ".md5.json"), "w"), indent=0)
+    return os.path.getsize(path), len(md5)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("names", nargs="*", default=[])
+    a = ap.parse_args()
+    cat = catalogue()
+    total = 0
+    for n in (a.names or cat):
+        size, frames = generate(n, cat[n])
+        total += size
+        print(n, size, "bytes", frames, "frames", flush=True)
+    print("total", total, "bytes")
