@@ -284,6 +284,55 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     ms_step = ms_total / a.steps
     value = world * kbatch / ms_step * 1e3
     ctx.free_batch(batch)
+    # ---- SAO leg: an enc265 stream cannot carry SAO syntax, so the deblocked pictures of
+    # this stream are filtered with synthetic per-CTB parameters (seed 5: 20 % off / 40 % band / 40 % edge,
+    # class U{0..3}, band position U{0..31}, |offset| <= 7 with the edge-offset sign convention)
+    sao_ms, sao_gbs = None, None
+    if patched:
+        keep = []
+        sjobs = []
+        rng = np.random.default_rng(5)
+        for J0 in jobs:
+            J = L.FrameJob()
+            C.memmove(C.byref(J), C.byref(J0), C.sizeof(L.FrameJob))
+            nctb = (-(-W >> J.log2_ctb)) * (-(-H >> J.log2_ctb))
+            sao = (L.SAO * nctb)()
+            raw = np.zeros((nctb, 18), np.int8)
+            typ = rng.choice([0, 1, 2], size=(nctb, 2), p=[0.2, 0.4, 0.4])
+            raw[:, 0] = typ[:, 0]; raw[:, 1] = typ[:, 1]; raw[:, 2] = typ[:, 1]
+            for c in range(3):
+                t = raw[:, c]
+                band = rng.integers(0, 32, nctb); eo = rng.integers(0, 4, nctb)
+                if c == 2:
+                    eo = raw[:, 4].copy()   # Cr shares Cb's edge class
+                raw[:, 3 + c] = np.where(t == 1, band, np.where(t == 2, eo, 0))
+                off = rng.integers(-7, 8, (nctb, 4))
+                edge = np.abs(off) * np.array([1, 1, -1, -1])
+                raw[:, 6 + 4 * c:10 + 4 * c] = np.where((t == 2)[:, None], edge, off) * (t != 0)[:, None]
+            C.memmove(sao, raw.ctypes.data, nctb * 18)
+            sl = (L.Slice * J.n_slices)()
+            C.memmove(sl, J.slices, C.sizeof(L.Slice) * J.n_slices)
+            for i in range(J.n_slices):
+                sl[i].sao_luma = 1; sl[i].sao_chroma = 1
+            J.sao = C.cast(sao, C.POINTER(L.SAO))
+            J.slices = C.cast(sl, C.POINTER(L.Slice))
+            J.flags |= L.FRAME_SAO
+            keep += [sao, sl]
+            sjobs.append(J)
+        sbatch = ctx.upload_frames(sjobs)
+        for _ in range(max(1, a.warmup)):
+            ctx.run_batch(sbatch)
+        ctx.sync()
+        ctx.lib.b265_set_stage_timing(ctx.h, 1)
+        ss = []
+        for _ in range(3):
+            ctx.flush_l2()
+            ctx.run_batch(sbatch)
+            ss.append(ctx.stage_times()[4])
+        ctx.lib.b265_set_stage_timing(ctx.h, 0)
+        sao_ms = float(np.mean(ss))
+        sao_gbs = kbatch * 2 * (W * H * 3 // 2) / sao_ms / 1e6
+        ctx.free_batch(sbatch)
     for s in sids:
         ctx.surface_release(s)
     ctx.close()
@@ -328,7 +377,8 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                    "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
                              "2 CUDA contexts, batch 16; %d frames per step" % (threads, frames_step),
                    "host_cores": cores,
-                   "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage]},
+                   "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage],
+                   "sao_leg_ms": round(sao_ms, 3) if sao_ms else None},
         "e2e": {"value": e2e_fps, "unit": "frames/s",
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) / a.steps),
@@ -342,7 +392,8 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                              "sample of a coded TB read; time = CUDA events around this launch only",
                      "per_kernel_gbs": {"k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1),
                                         "k_intra_wavefront": round(intra_gbs, 1),
-                                        "deblock(bs+V+H luma/chroma, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None}},
+                                        "deblock(bs+V+H luma/chroma, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None,
+                                        "sao(synthetic per-CTB parameters on the same pictures, 2P per picture)": round(sao_gbs, 1) if sao_gbs else None}},
     }
     if rank == 0 and world == 1:
         res["cpu_baseline"] = cpu_baseline_stream(wl)
@@ -518,6 +569,82 @@ def run_reference_sweep(a):
 # =====================================================================================================
 # dispatch
 # =====================================================================================================
+# our arm: motion compensation on synthetic PU lists
+# =====================================================================================================
+def run_mc(a, rank, world, local, ClockSampler, measured_peaks):
+    """1920x1080, three reference pictures (noise / smooth / noise), 8 pictures whose PU lists each tile the
+    frame once with every legal PU size, MV ~ U[-256,255] quarter samples with 5 % far off-picture, 40 % uni,
+    30 % bi, 15 % + 15 % weighted (tests/helpers.make_pu_list, the list the parity test uses), through the
+    frame-level path (b265_upload_frames / b265_run_batch) with the lists resident in HBM."""
+    from libde265_b200 import lib as L
+    from tests.helpers import make_pu_list, make_planes
+    W, H, layers = 1920, 1080, 8
+    rng = np.random.default_rng(3)
+    ctx = L.Context(local)
+    refs = [make_planes(rng, W, H, k) for k in ("noise", "smooth", "noise")]
+    ref_sids = []
+    for r in refs:
+        sid = ctx.surface_alloc(W, H)
+        ctx.surface_upload(sid, r)
+        ref_sids.append(sid)
+    jobs, keep, sids = [], [], []
+    alg = 0
+    n_pus = 0
+    for _ in range(layers):
+        pus, slices = make_pu_list(rng, W, H, len(refs))
+        J = L.FrameJob()
+        J.width, J.height, J.chroma_format_idc, J.bit_depth = W, H, 1, 8
+        J.log2_ctb, J.log2_min_cb, J.log2_min_tb = 6, 3, 2
+        sid = ctx.surface_alloc(W, H)
+        J.dst_surface = sid
+        sids.append(sid)
+        for i, r in enumerate(ref_sids):
+            J.ref_surfaces[i] = r
+            J.ref_poc[i] = i
+        J.n_refs = len(ref_sids)
+        J.pus = C.cast(pus, C.POINTER(L.PU)); J.n_pus = len(pus)
+        J.slices = C.cast(slices, C.POINTER(L.Slice)); J.n_slices = len(slices)
+        keep += [pus, slices]
+        jobs.append(J)
+        arr = np.ctypeslib.as_array(C.cast(pus, C.POINTER(C.c_uint8)), shape=(len(pus) * 24,)).reshape(-1, 24)
+        area = arr[:, 4].astype(np.int64) * arr[:, 5].astype(np.int64)
+        bi = (arr[:, 6] & 3) == 3
+        alg += int((area * np.where(bi, 4.5, 3.0)).sum())
+        n_pus += len(pus)
+    batch = ctx.upload_frames(jobs)
+    for _ in range(a.warmup):
+        ctx.run_batch(batch)
+    ctx.sync()
+    clocks = ClockSampler(local)
+    clocks.start()
+    launches0 = ctx.launches
+    ms = []
+    for _ in range(a.steps):
+        ctx.flush_l2()
+        ctx.timer_start()
+        ctx.run_batch(batch)
+        ms.append(ctx.timer_stop())
+    clk = clocks.stop()
+    launches = ctx.launches - launches0
+    ms_step = _barrier_max(world, float(np.mean(ms)))
+    ctx.free_batch(batch)
+    for s_ in sids + ref_sids:
+        ctx.surface_release(s_)
+    ctx.close()
+    peak, peak_src = measured_peaks()
+    gbs = alg / ms_step / 1e6
+    px = layers * W * H
+    return {"metric": "motion-compensated Mpixel/s", "value": world * px / ms_step / 1e3, "unit": "Mpixel/s", "n_gpus": world,
+            "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u8 pixels / int16 intermediates / int32 accumulators", "data": "synthetic",
+            "config": {"workload": "mc_pus: SURVEY 8d config 3, 1920x1080, 3 references, %d PUs in %d pictures" % (n_pus, layers),
+                       "l2": "L2 flushed before every timed step"},
+            "e2e": None, "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"bound": "hbm", "kernel": "k_mc", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "note": "algorithmic bytes = 3*w*h per uni-predicted PU (1.5 read + 1.5 written), 4.5*w*h per bi-predicted PU"}}
+
+
 DEFAULT_WORKLOAD = "stream_4k"
 
 
@@ -535,6 +662,8 @@ def run_ours(a, rank, world, local, ClockSampler, measured_peaks):
         res = run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks)
     elif wl == "idct_sweep":
         res = run_sweep(a, rank, world, local, ClockSampler, measured_peaks)
+    elif wl == "mc_pus":
+        res = run_mc(a, rank, world, local, ClockSampler, measured_peaks)
     else:
         raise SystemExit("unknown workload " + wl)
     if world > 1:

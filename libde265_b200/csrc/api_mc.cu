@@ -10,6 +10,15 @@ extern "C" int b265_mc_batch(b265_ctx* ctx, int mem, const b265_pu* pus, int n_p
       n_slices < 1 || width <= 0 || height <= 0)
     return B265_ERR_INVALID_ARG;
   if (n_pus == 0) return B265_OK;
+  std::vector<b265_pu> pieces;   // 16x16 pieces (pu_expand)
+  pieces.reserve((size_t)n_pus * 2);
+  for (int i = 0; i < n_pus; i++) {
+    const size_t at = pieces.size();
+    pieces.resize(at + pu_pieces(pus[i]));
+    pu_expand(pus[i], pieces.data() + at);
+  }
+  pus = pieces.data();
+  n_pus = (int)pieces.size();
   CK(cudaSetDevice(ctx->device));
   const bool chroma = dst_planes[1] != nullptr;
   const int cw = (width + 1) / 2, ch = (height + 1) / 2;

@@ -56,3 +56,19 @@ int b265_fail(b265_ctx* ctx, int status, const char* what, cudaError_t e);
   } while (0)
 
 int devbuf_reserve(b265_ctx* ctx, DevBuf* b, size_t bytes, bool host);
+
+// Prediction blocks larger than 16x16 are cut into 16x16 pieces when the lists are staged for the device: motion
+// compensation and the motion raster are per-sample functions of (position, motion), so the pieces give the same
+// result, and every work item of the MC kernel then costs one tile (balanced scheduling).
+static inline int pu_pieces(const b265_pu& pu) { return ((pu.w + 15) >> 4) * ((pu.h + 15) >> 4); }
+static inline int pu_expand(const b265_pu& pu, b265_pu* out) {
+  int n = 0;
+  for (int y = 0; y < pu.h; y += 16)
+    for (int x = 0; x < pu.w; x += 16) {
+      b265_pu q = pu;
+      q.x = (uint16_t)(pu.x + x); q.y = (uint16_t)(pu.y + y);
+      q.w = (uint8_t)(pu.w - x < 16 ? pu.w - x : 16); q.h = (uint8_t)(pu.h - y < 16 ? pu.h - y : 16);
+      out[n++] = q;
+    }
+  return n;
+}

@@ -67,6 +67,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   struct Key { uint32_t wave; IntraTicket t; };
   std::vector<Key> intra;
   std::vector<uint32_t> res[4], ires[4], mc;
+  std::vector<uint32_t> n_pieces(n_jobs, 0);
   std::vector<std::vector<uint8_t>> done_init(n_jobs);   // per frame: 3 planes x nctb, 1 = nothing to wait for
   std::vector<uint32_t> ctb_first, ctb_count;
   std::vector<uint8_t> ctb_has;
@@ -122,7 +123,13 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
           intra.push_back({wave, {(uint16_t)j, (uint8_t)c, fl, (uint32_t)ctb, ctb_first[ctb], ctb_count[ctb]}});
         }
     }
-    for (int i = 0; i < J.n_pus; i++) mc.push_back(((uint32_t)j << 24) | (uint32_t)i);
+    {  // one MC item per 16x16 piece of a prediction block (pu_expand)
+      uint32_t n = 0;
+      for (int i = 0; i < J.n_pus; i++)
+        for (int k = pu_pieces(J.pus[i]); k > 0; k--) mc.push_back(((uint32_t)j << 24) | n++);
+      if (n >= (1u << 24)) return reject(__LINE__, B265_ERR_UNSUPPORTED);
+      n_pieces[j] = n;
+    }
   }
   b->max_wave = max_wave;
   // ---- counting sort of the tickets by wave (stable) ----
@@ -157,7 +164,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     const int nctb = ((J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb) * ((J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb);
     fo[j].tus = P.take(sizeof(b265_tu) * (size_t)J.n_tus);
     fo[j].coeffs = P.take(sizeof(b265_coeff) * (size_t)J.n_coeffs);
-    fo[j].pus = P.take(sizeof(b265_pu) * (size_t)J.n_pus);
+    fo[j].pus = P.take(sizeof(b265_pu) * (size_t)n_pieces[j]);
     fo[j].slices = P.take(sizeof(b265_slice) * (size_t)std::max(1, J.n_slices));
     fo[j].ctbs = J.ctbs ? P.take(sizeof(b265_ctb) * (size_t)nctb) : 0;
     fo[j].sao = J.sao ? P.take(sizeof(b265_sao) * (size_t)nctb) : 0;
@@ -261,7 +268,10 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     const int nctb = nctb_w * nctb_h;
     cp(fo[j].tus, J.tus, sizeof(b265_tu) * (size_t)J.n_tus);
     cp(fo[j].coeffs, J.coeffs, sizeof(b265_coeff) * (size_t)J.n_coeffs);
-    cp(fo[j].pus, J.pus, sizeof(b265_pu) * (size_t)J.n_pus);
+    {
+      b265_pu* out = reinterpret_cast<b265_pu*>(H + fo[j].pus);
+      for (int i = 0; i < J.n_pus; i++) out += pu_expand(J.pus[i], out);
+    }
     if (J.n_slices > 0) cp(fo[j].slices, J.slices, sizeof(b265_slice) * (size_t)J.n_slices);
     else cp(fo[j].slices, &default_slice, sizeof(b265_slice));
     cp(fo[j].ctbs, J.ctbs, sizeof(b265_ctb) * (size_t)nctb);

@@ -48,3 +48,47 @@ def test_mc_all_phases_small_blocks(ctx, oracle):
         got = ctx.mc_batch(pus, slices, refs, [p.copy() for p in base], w, h)
         for c in range(3):
             assert np.array_equal(got[c], want[c])
+
+
+@pytest.mark.parametrize("w,h,seed", [(416, 240, 13), (1920, 1080, 14)])
+def test_mc_frame_path(ctx, oracle, w, h, seed):
+    """the same PU lists through the FRAME-level path (b265_submit_frames: references and destination are DPB
+    surfaces in HBM, lists uploaded with the job), two pictures per call"""
+    rng = np.random.default_rng(seed)
+    refs = [make_planes(rng, w, h, "noise"), make_planes(rng, w, h, "smooth")]
+    ref_sids = []
+    for r in refs:
+        sid = ctx.surface_alloc(w, h)
+        ctx.surface_upload(sid, r)
+        ref_sids.append(sid)
+    jobs, keep, want, sids = [], [], [], []
+    for k in range(2):
+        pus, slices = make_pu_list(rng, w, h, len(refs), coverage=0.9)
+        base = make_planes(rng, w, h, "noise")
+        sid = ctx.surface_alloc(w, h)
+        ctx.surface_upload(sid, base)
+        sids.append(sid)
+        exp = [p.copy() for p in base]
+        oracle_mc(oracle, pus, slices, refs, exp, w, h)
+        want.append(exp)
+        J = L.FrameJob()
+        J.width, J.height, J.chroma_format_idc, J.bit_depth = w, h, 1, 8
+        J.log2_ctb, J.log2_min_cb, J.log2_min_tb = 5, 3, 2
+        J.dst_surface = sid
+        for i, r in enumerate(ref_sids):
+            J.ref_surfaces[i] = r
+            J.ref_poc[i] = 10 + i
+        J.n_refs = len(ref_sids)
+        J.pus = C.cast(pus, C.POINTER(L.PU)); J.n_pus = len(pus)
+        J.slices = C.cast(slices, C.POINTER(L.Slice)); J.n_slices = len(slices)
+        keep += [pus, slices]
+        jobs.append(J)
+    ctx.submit_frames(jobs)
+    ctx.sync()
+    for k in range(2):
+        got = ctx.surface_download(sids[k], w, h)
+        for c in range(3):
+            bad = np.argwhere(got[c] != want[k][c])
+            assert bad.size == 0, "picture %d plane %d first mismatch at (y,x)=%s of %d" % (k, c, bad[0], len(bad))
+    for s in sids + ref_sids:
+        ctx.surface_release(s)
