@@ -11,15 +11,17 @@ ctx = L.Context(0)
 ctx.lib.b265_set_stage_timing(ctx.h, 1)
 batches = [int(x) for x in sys.argv[2].split(',')] if len(sys.argv) > 2 else [1, 2, 4, 8, 16]
 for nb in batches:
-    if nb > len(jobs):
-        break
     sids = []
     js = []
-    for oj in jobs[:nb]:
-        sid = ctx.surface_alloc(oj.job.width, oj.job.height)
-        oj.job.dst_surface = sid
+    import ctypes as C
+    for i in range(nb):   # the unique pictures of the stream, repeated
+        oj = jobs[i % len(jobs)]
+        J = L.FrameJob()
+        C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
+        sid = ctx.surface_alloc(J.width, J.height)
+        J.dst_surface = sid
         sids.append(sid)
-        js.append(oj.job)
+        js.append(J)
     t0 = time.perf_counter()
     b = ctx.upload_frames(js)
     ctx.sync()

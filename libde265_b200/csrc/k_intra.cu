@@ -184,14 +184,17 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   const uint8_t* src[2];
   int kind[2];   // 0 nothing, 1 mailbox word, 2 plane (row word), 3 plane (column word, 4 strided bytes), 4 plane corner byte
   int slotv[2];
+  const int lq = g.log2_ctb - g.sh - 2;   // q = 1 << lq
+  const bool two = 3 * q >= 32;           // more than 32 slots: only for 64-sample CTB planes
 #pragma unroll
   for (int k = 0; k < 2; k++) {
     const int slot = lane + 32 * k;
     slotv[k] = slot;
     kind[k] = 0;
     src[k] = nullptr;
+    if (k == 1 && !two) break;   // warp-uniform
     if (slot > 3 * q) continue;
-    const int piece = slot == 3 * q ? 3 : slot / q, w = slot == 3 * q ? q - 1 : slot % q;
+    const int piece = slot >> lq, w = slot == 3 * q ? q - 1 : slot & (q - 1);
     // neighbour CTB of the piece
     const int nx = g.cx + (piece == 1 ? 1 : (piece == 0 ? 0 : -1)), ny = g.cy - (piece == 2 ? 0 : 1);
     // not usable for prediction (outside the picture, other slice/tile): never read, never waited for
@@ -214,15 +217,18 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   // plane reads (rare: mixed pictures)
 #pragma unroll
   for (int k = 0; k < 2; k++) {
+    if (k == 1 && !two) break;
     if (kind[k] == 2) val[k] = ld_cg_u32(src[k]);
     else if (kind[k] == 3) {
       for (int i = 0; i < 4; i++) val[k] |= (uint32_t)ld_cg_u8(src[k] + (size_t)i * pitch) << (8 * i);
     } else if (kind[k] == 4) val[k] = (uint32_t)ld_cg_u8(src[k]) << 24;
   }
+  // every lane polls its own word(s): restricting the polling to one lane per neighbour, or pausing longer
+  // between polls, was measured slower at every batch size (the wavefront is bound by detection latency)
   for (;;) {
 #pragma unroll
     for (int k = 0; k < 2; k++)
-      if (!have[k]) {
+      if (!have[k] && (k == 0 || two)) {
         const unsigned long long v = ld_relaxed_u64(src[k]);
         if ((uint32_t)(v >> 32) != 0) { val[k] = (uint32_t)v; have[k] = true; }
       }
@@ -232,6 +238,7 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   // into the edge store
 #pragma unroll
   for (int k = 0; k < 2; k++) {
+    if (k == 1 && !two) break;
     if (kind[k] == 0) continue;
     const int slot = slotv[k];
     if (slot < 2 * q) *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * slot) = val[k];

@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libb265.so")
+LIB_PATH = os.environ.get("B265_LIB") or os.path.join(HERE, "libb265.so")   # B265_LIB: developer A/B runs
 
 B265_OK = 0
 MEM_HOST, MEM_DEVICE = 0, 1
