@@ -62,7 +62,7 @@ extern uint8_t g_cabac_next[256];   // next context byte, indexed by (ctx << 1) 
 
 // what the syntax walk tells the engine about the bin(s) that follow; the decoder ignores it, the
 // test-stream generator uses it to keep randomly drawn values legal
-enum Hint { HINT_PCM_FLAG, HINT_QP_DELTA_SUFFIX, HINT_COEFF_REMAINING, HINT_END_OF_SEGMENT, HINT_END_OF_SUBSET };
+enum Hint { HINT_PCM_FLAG, HINT_QP_DELTA_SUFFIX, HINT_COEFF_REMAINING, HINT_END_OF_SEGMENT, HINT_END_OF_SUBSET, HINT_MVD_SUFFIX };
 
 struct Cabac {
   typedef Cabac Local;            // residual_coding works on a register copy of the engine

@@ -21,9 +21,11 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <unordered_map>
 #include "../../../include/b265.h"
 #include "../../../include/de265.h"
 #include "picture.h"
+#include "dpb.h"
 
 using namespace b265h;
 
@@ -71,6 +73,19 @@ struct Decoder {
   int prev_tid0_poc_lsb = 0, prev_tid0_poc_msb = 0;
   bool first_picture = true, after_eos = true;
   uint64_t next_decode_index = 0;
+  // ---- reference pictures ----
+  Dpb dpb;
+  uint64_t next_uid = 1, gop_id = 0;
+  bool last_no_rasl_output = false;              // the last IRAP picture emptied the DPB
+  bool skip_rasl = false;
+  std::unordered_map<uint64_t, int> gop_ctx;     // reconstruction context the pictures of a GOP are pinned to (mu)
+  std::mutex rel_mu;
+  std::vector<std::pair<int, int>> to_release;   // (context, surface) of reference pictures nobody needs any more
+  static void recycle_cb(void* owner, int ctx, int surface) {
+    Decoder* d = static_cast<Decoder*>(owner);
+    std::lock_guard<std::mutex> l(d->rel_mu);
+    d->to_release.emplace_back(ctx, surface);
+  }
   // ---- pipeline ----
   std::mutex mu;
   std::condition_variable cv_parse, cv_recon, cv_done;
@@ -131,7 +146,8 @@ struct Decoder {
     cv_recon.notify_all();
     for (auto& t : workers) t.join();
     for (auto& t : recon_threads) t.join();
-    auto drop = [this](std::unique_ptr<de265_image>& i) { if (i) release_image(*i); };
+    dpb.clear();
+    auto drop = [this](std::unique_ptr<de265_image>& i) { if (i) { release_image(*i); i->pic.ref_pics.clear(); i->pic.self.reset(); } };
     for (auto& i : inflight) drop(i);
     for (auto& i : reorder) drop(i);
     for (auto& i : output) drop(i);
@@ -211,6 +227,7 @@ struct Decoder {
     if (!cur) return;
     de265_image* img = cur.get();
     img->pic.decode_index = next_decode_index++;
+    img->pic.self->decode_index = img->pic.decode_index;
     bool inline_parse;
     {
       std::lock_guard<std::mutex> l(mu);
@@ -251,6 +268,13 @@ struct Decoder {
     if (s.pcm_lf_disabled) fl |= B265_FRAME_PCM_LF_DISABLE;
     J.flags = fl;
     J.dst_surface = p.surface;
+    J.n_refs = (int)p.ref_pics.size();
+    for (int i = 0; i < J.n_refs; i++) {
+      // parse-only clients get the pictures' unique ids instead of surfaces (tests reconstruct with the CPU oracle)
+      J.ref_surfaces[i] = parse_only ? (int32_t)p.ref_pics[i]->uid : p.ref_pics[i]->surface;
+      J.ref_poc[i] = p.ref_pics[i]->poc;
+    }
+    if (parse_only) J.dst_surface = (int32_t)p.self->uid;
     J.tus = p.tus.data(); J.n_tus = (int)p.tus.size();
     J.coeffs = p.coeffs.data(); J.n_coeffs = (int)p.coeffs.size();
     J.pus = p.pus.data(); J.n_pus = (int)p.pus.size();
@@ -323,11 +347,30 @@ struct Decoder {
           size_t first = 0;
           while (first < inflight.size() && inflight[first]->state >= de265_image::TAKEN) first++;
           size_t n = 0;
+          // Reference pictures live in the surfaces of ONE context: the pictures between two DPB-emptying pictures
+          // (a "GOP") are pinned to the context that takes the first of them.  A batch never holds a picture
+          // together with one of its references (b265_submit_frames runs each stage for all pictures at once).
+          auto pinned_elsewhere = [&](const de265_image& im) {
+            auto it = gop_ctx.find(im.pic.gop);
+            return it != gop_ctx.end() && it->second != ci;
+          };
+          auto depends_on_batch = [&](const de265_image& im) {
+            if (n == 0) return false;
+            const uint64_t lo = inflight[first]->pic.decode_index;
+            for (const auto& r : im.pic.ref_pics) if (r && r->decode_index >= lo) return true;
+            return false;
+          };
+          bool wrong_ctx = false, dependent = false;
           while (first + n < inflight.size() && (int)n < max_batch && inflight[first + n]->state == de265_image::PARSED &&
                  inflight[first + n]->pic.width == inflight[first]->pic.width &&
-                 inflight[first + n]->pic.height == inflight[first]->pic.height)
+                 inflight[first + n]->pic.height == inflight[first]->pic.height) {
+            if (pinned_elsewhere(*inflight[first + n])) { wrong_ctx = true; break; }
+            if (depends_on_batch(*inflight[first + n])) { dependent = true; break; }
             n++;
-          const bool blocked = first + n < inflight.size() && inflight[first + n]->state == de265_image::PARSED;  // geometry change
+          }
+          if (wrong_ctx && n == 0) { cv_recon.wait(l); continue; }   // the other context's pictures come first
+          const bool blocked = dependent || wrong_ctx ||
+                               (first + n < inflight.size() && inflight[first + n]->state == de265_image::PARSED);  // geometry change
           bool take = n > 0 && ((int)n >= max_batch || draining || blocked || parse_only);
           if (!take && n > 0) {
             const double waited = now_s() - inflight[first]->parsed_at;
@@ -336,6 +379,7 @@ struct Decoder {
           }
           if (take) {
             for (size_t i = 0; i < n; i++) {
+              gop_ctx.emplace(inflight[first + i]->pic.gop, ci);
               inflight[first + i]->state = de265_image::TAKEN;
               batch.push_back(inflight[first + i].get());
             }
@@ -349,6 +393,16 @@ struct Decoder {
       std::vector<de265_image*> good;
       int njobs = 0;
       double d2h = 0, h2d = 0, t_submit = 0;
+      if (!parse_only && gpu) {   // surfaces of reference pictures that left the DPB
+        std::vector<std::pair<int, int>> rel;
+        {
+          std::lock_guard<std::mutex> rl(rel_mu);
+          for (size_t i = 0; i < to_release.size();)
+            if (to_release[i].first == ci) { rel.push_back(to_release[i]); to_release.erase(to_release.begin() + i); }
+            else i++;
+        }
+        for (auto& r : rel) b265_surface_release(gpu, r.second);
+      }
       for (de265_image* img : batch) {
         Picture& p = img->pic;
         if (parse_only) continue;
@@ -360,6 +414,17 @@ struct Decoder {
           p.error = DE265_ERROR_OUT_OF_MEMORY;
           continue;
         }
+        // a reference that failed (or was never reconstructed) cannot be read
+        bool refs_ok = true;
+        for (const auto& r : p.ref_pics) refs_ok &= r && r->surface >= 0 && r->ctx == ci;
+        if (!refs_ok) {
+          b265_surface_release(gpu, p.surface);
+          p.surface = -1;
+          p.error = DE265_ERROR_UNSPECIFIED_DECODING_ERROR;
+          continue;
+        }
+        p.self->ctx = ci;
+        p.self->surface = p.surface;   // the picture in HBM now belongs to the DPB entry (recycled when it dies)
         fill_job(*img, jobs[njobs++]);
         good.push_back(img);
       }
@@ -384,8 +449,9 @@ struct Decoder {
         for (de265_image* img : good) {
           if (r != B265_OK && getenv("B265_DEBUG")) fprintf(stderr, "b265: back end status %d: %s\n", r, b265_last_error(gpu));
           if (r != B265_OK) img->pic.error = r == B265_ERR_OUT_OF_MEMORY ? DE265_ERROR_OUT_OF_MEMORY : DE265_ERROR_UNSPECIFIED_DECODING_ERROR;
-          b265_surface_release(gpu, img->pic.surface);
           img->pic.surface = -1;
+          img->pic.ref_pics.clear();
+          img->pic.self.reset();
         }
       }
       {
@@ -498,6 +564,7 @@ struct Decoder {
     const bool no_rasl_output = idr || bla || (irap && (first_picture || after_eos));
     int msb;
     const int max_lsb = 1 << sps.log2_max_poc_lsb;
+    last_no_rasl_output = irap && no_rasl_output;
     if (irap && no_rasl_output) msb = 0;
     else {
       if (sh.poc_lsb < prev_tid0_poc_lsb && (prev_tid0_poc_lsb - sh.poc_lsb) >= max_lsb / 2) msb = prev_tid0_poc_msb + max_lsb;
@@ -581,7 +648,16 @@ struct Decoder {
       p.pic_output = sh.pic_output;
       p.init_maps();
       p.poc = compute_poc(sh, *pps->sps, type, tid);
-      if (type == NAL_RASL_N || type == NAL_RASL_R) p.pic_output = 0;  // no inter decoding: RASL never decodable
+      if ((type == NAL_RASL_N || type == NAL_RASL_R) && skip_rasl) p.pic_output = 0;   // leading pictures of a random access point
+      if (type >= NAL_BLA_W_LP && type <= NAL_RSV_IRAP_VCL23) skip_rasl = last_no_rasl_output;
+      dpb.apply_rps(sh, *pps->sps, p.poc, last_no_rasl_output);
+      if (last_no_rasl_output) gop_id++;
+      p.gop = gop_id;
+      p.self->poc = p.poc;
+      p.self->uid = next_uid++;
+      p.self->owner = this;
+      p.self->recycle = &Decoder::recycle_cb;
+      dpb.pics.push_back(p.self);
       const Sps& s = *pps->sps;
       if (s.scaling_list_enabled) {
         p.scaling = std::make_shared<b265_scaling>();
@@ -613,6 +689,9 @@ struct Decoder {
       memcpy(bs.offset, sh.pw.offset, sizeof(bs.offset));
       sh.slice_index = (int)p.slices.size();
       p.slices.push_back(bs);
+      SliceRefs sr;
+      dpb.build_lists(sh, p, sr);   // on failure the lists stay empty and the slice data is rejected
+      p.slice_refs.push_back(sr);
       prev_indep = sh;
       have_prev_indep = true;
     }
@@ -821,6 +900,8 @@ LIBDE265_API void de265_reset(de265_decoder_context* c) {
   d->after_eos = true;
   d->have_prev_indep = false;
   d->fatal_error = 0;
+  d->dpb.clear();
+  d->gop_ctx.clear();
 }
 
 LIBDE265_API const struct de265_image* de265_peek_next_picture(de265_decoder_context* c) {

@@ -53,6 +53,43 @@ struct PodBuf {
 
 enum PredMode : uint8_t { MODE_NONE = 0, MODE_INTRA = 1, MODE_INTER = 2, MODE_SKIP = 3 };
 
+// motion of one 4x4 luma unit (the reference's PBMotion, motion.h:36-44); pred_flags 0 = intra / not coded
+struct MotionInfo {
+  int16_t mv[2][2];     // [list][x,y] quarter samples
+  int8_t ref_idx[2];
+  uint8_t pred_flags;   // bit 0: L0, bit 1: L1
+  uint8_t pad;
+};
+
+// reference picture lists of one (independent) slice, resolved against the DPB (slice.h:237 RefPicList +
+// the POC / long-term marking the motion vector prediction compares, motion.cc:1020-1180)
+struct SliceRefs {
+  int n[2] = {0, 0};
+  int32_t poc[2][16];
+  uint8_t is_lt[2][16];
+  uint8_t slot[2][16];     // index into Picture::ref_pics (-> b265_frame_job.ref_surfaces)
+};
+
+// What later pictures need from a decoded picture: its identity in the DPB, where its samples live, and its
+// motion field for temporal motion vector prediction (8.5.3.2.8).  Shared between the API thread (DPB
+// bookkeeping), the parse workers (collocated motion) and the reconstruction threads (surfaces).
+struct RefPic {
+  int poc = 0;
+  uint64_t decode_index = 0;
+  uint64_t uid = 0;                // unique per decoder, never 0: identifies the picture to parse-only clients
+  bool is_ref = true, is_lt = false, needed_for_output = false;
+  int ctx = -1, surface = -1;      // reconstruction context / HBM surface (set by the reconstruction thread)
+  void* owner = nullptr;           // decoder that recycles the surface when the last reference drops
+  void (*recycle)(void* owner, int ctx, int surface) = nullptr;
+  volatile int parsed = 0;         // motion field complete (set by the parse worker)
+  volatile int failed = 0;
+  int u_w = 0, u_h = 0, ctbs_w = 0, log2_ctb = 4;
+  std::vector<MotionInfo> motion;  // per 4x4 unit
+  std::vector<uint16_t> ctb_slice; // per CTB: index into slice_refs
+  std::vector<SliceRefs> slice_refs;
+  ~RefPic() { if (recycle && surface >= 0) recycle(owner, ctx, surface); }
+};
+
 struct SliceUnit {                 // one slice segment NAL of the picture
   SliceHeader hdr;
   std::shared_ptr<const Pps> pps;
@@ -68,6 +105,7 @@ struct Picture {
   int64_t pts = 0;
   void* user_data = nullptr;
   uint64_t decode_index = 0;       // position in decoding order
+  uint64_t gop = 0;                // counts the pictures that empty the DPB (IDR / BLA / first CRA): no reference crosses it
 
   std::vector<SliceUnit> slice_units;
 
@@ -82,6 +120,11 @@ struct Picture {
   std::vector<uint8_t> unit_info;  // per 4x4 unit, B265_UNIT_* (-> b265_frame_job.unit_info)
   std::vector<int32_t> ctb_slice_addr;  // per CTB (raster): SliceAddrRS of the owning slice, -1 = not decoded
   std::vector<b265_ctb> ctbs;      // per CTB (raster)
+  // ---- inter prediction ----
+  std::shared_ptr<RefPic> self;                  // this picture as later pictures will see it
+  std::vector<std::shared_ptr<RefPic>> ref_pics; // distinct reference pictures of all slices (slot order)
+  std::vector<SliceRefs> slice_refs;             // per independent slice (same index as `slices`)
+  bool has_inter = false;
 
   // ---- work lists ----
   PodBuf<b265_tu> tus;
@@ -117,6 +160,11 @@ struct Picture {
     ctb_slice_addr.assign((size_t)s.ctbs_w * s.ctbs_h, -1);
     ctbs.assign((size_t)s.ctbs_w * s.ctbs_h, b265_ctb{0, 0, 0});
     sao.assign((size_t)s.ctbs_w * s.ctbs_h, b265_sao{});
+    self = std::make_shared<RefPic>();
+    self->u_w = u_w; self->u_h = u_h; self->ctbs_w = s.ctbs_w; self->log2_ctb = s.log2_ctb;
+    self->motion.assign((size_t)u_w * u_h, MotionInfo{{{0, 0}, {0, 0}}, {-1, -1}, 0, 0});
+    self->ctb_slice.assign((size_t)s.ctbs_w * s.ctbs_h, 0);
+    ref_pics.clear(); slice_refs.clear(); has_inter = false;
     tus.clear(); coeffs.clear(); pus.clear(); pcms.clear(); pcm_samples.clear(); slices.clear();
     tus.reserve((size_t)u_w * u_h / 4);
     coeffs.reserve((size_t)width * height / 8);

@@ -20,6 +20,10 @@ int decode_picture_slices(Picture& pic) {
     if (r && !err) err = r;
     if (r == E_NOT_IMPLEMENTED) break;
   }
+  // what later pictures need for temporal motion vector prediction
+  pic.self->slice_refs = pic.slice_refs;
+  if (err) pic.self->failed = 1;
+  pic.self->parsed = 1;
   return err;
 }
 

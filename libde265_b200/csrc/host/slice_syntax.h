@@ -19,6 +19,8 @@
 #pragma once
 #include <string.h>
 #include <algorithm>
+#include <chrono>
+#include <thread>
 #include "cabac.h"
 #ifdef B265_PROF
 #include <x86intrin.h>
@@ -180,6 +182,19 @@ struct SliceDec {
   void decode_qp(int xCU, int yCU, int log2_cb);
   int read_pcm(int x0, int y0, int log2_cb);
   void mark_tu_edges(int x0, int y0, int log2_ts, int xCU, int yCU, int log2_cb, bool cbf_luma);
+  // ---- inter prediction (7.3.8.6, 7.3.8.9, 8.5.3.2) ----
+  int cu_part_mode = 0;       // PartMode of the current CU (0 2Nx2N 1 2NxN 2 Nx2N 3 NxN 4 2NxnU 5 2NxnD 6 nLx2N 7 nRx2N)
+  int cu_ct_depth = 0;
+  const SliceRefs* refs = nullptr;
+  inline MotionInfo& motion_at(int x, int y) { return pic.self->motion[(size_t)(y >> 2) * pic.u_w + (x >> 2)]; }
+  bool pb_neighbour(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int xN, int yN, MotionInfo& out);
+  int prediction_unit(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, bool skip, int& merge_out);
+  void derive_merge(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int merge_idx, MotionInfo& out);
+  void derive_amvp(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int X, int ref_idx, int16_t cand[2][2]);
+  bool temporal_mv(int xPb, int yPb, int nPbW, int nPbH, int ref_idx, int X, int16_t mv[2]);
+  bool col_mv(const RefPic& col, int xCol, int yCol, int ref_idx, int X, int16_t mv[2]);
+  void mark_pu_edges(int x0, int y0, int nCbS, int part_mode);
+  int read_mvd(int16_t mvd[2]);
 };
 
 // ---- SAO syntax (7.3.8.3) --------------------------------------------------------------------------
@@ -379,7 +394,352 @@ int SliceDec<Eng>::read_pcm(int x0, int y0, int log2_cb) {
   return E_OK;
 }
 
-// ---- coding unit (7.3.8.5) — intra only ---------------------------------------------------------------
+// ---- inter prediction: neighbours, merge mode, AMVP, temporal candidates (8.5.3.2.1 - 8.5.3.2.9; the
+// reference's motion.cc:1020-2160) ------------------------------------------------------------------------------
+inline int mv_scale(int mv, int tb, int td) {   // (8-179)..(8-183)
+  td = clip3(-128, 127, td);
+  tb = clip3(-128, 127, tb);
+  const int tx = (16384 + (abs(td) >> 1)) / td;
+  const int dsf = clip3(-4096, 4095, (tb * tx + 32) >> 6);
+  const int p = dsf * mv;
+  return clip3(-32768, 32767, (p < 0 ? -1 : 1) * ((abs(p) + 127) >> 8));
+}
+inline bool same_motion(const MotionInfo& a, const MotionInfo& b) {
+  if (a.pred_flags != b.pred_flags) return false;
+  for (int l = 0; l < 2; l++)
+    if (a.pred_flags & (1 << l))
+      if (a.mv[l][0] != b.mv[l][0] || a.mv[l][1] != b.mv[l][1] || a.ref_idx[l] != b.ref_idx[l]) return false;
+  return true;
+}
+
+// 6.4.2 prediction block availability + "is inter coded"; fills `out` when usable
+template <class Eng>
+bool SliceDec<Eng>::pb_neighbour(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int xN, int yN,
+                                 MotionInfo& out) {
+  (void)xPb; (void)yPb;
+  const bool same_cb = xCb <= xN && yCb <= yN && xCb + nCbS > xN && yCb + nCbS > yN;
+  if (!same_cb) {
+    if (!available(xN, yN)) return false;
+    if (pic.pred_mode[cb_idx(xN, yN)] == MODE_NONE) return false;   // not decoded yet (z-scan order, 6.4.1)
+  } else if ((nPbW << 1) == nCbS && (nPbH << 1) == nCbS && partIdx == 1 && yCb + nPbH <= yN && xCb + nPbW > xN) {
+    return false;   // second block of an NxN split asking for the third
+  }
+  const MotionInfo& m = motion_at(xN, yN);
+  if (!m.pred_flags) return false;   // intra
+  out = m;
+  return true;
+}
+
+// collocated motion (8.5.3.2.9) of the block covering (xCol, yCol) in `col`
+template <class Eng>
+bool SliceDec<Eng>::col_mv(const RefPic& col, int xCol, int yCol, int ref_idx, int X, int16_t mv[2]) {
+  xCol = (xCol >> 4) << 4;
+  yCol = (yCol >> 4) << 4;
+  const MotionInfo& m = col.motion[(size_t)(yCol >> 2) * col.u_w + (xCol >> 2)];
+  if (!m.pred_flags) return false;
+  const SliceRefs& cr = col.slice_refs[col.ctb_slice[(size_t)(yCol >> col.log2_ctb) * col.ctbs_w + (xCol >> col.log2_ctb)]];
+  int l;
+  if (!(m.pred_flags & 1)) l = 1;
+  else if (!(m.pred_flags & 2)) l = 0;
+  else {
+    bool no_backward = true;   // DiffPicOrderCnt(aPic, currPic) <= 0 for every picture of both lists
+    for (int k = 0; k < 2; k++)
+      for (int i = 0; i < refs->n[k]; i++) no_backward &= refs->poc[k][i] <= pic.poc;
+    l = no_backward ? X : sh.collocated_from_l0;
+  }
+  const int ri = m.ref_idx[l];
+  if (ri < 0 || ri >= cr.n[l]) return false;
+  if ((refs->is_lt[X][ref_idx] != 0) != (cr.is_lt[l][ri] != 0)) return false;
+  const int col_diff = col.poc - cr.poc[l][ri], cur_diff = pic.poc - refs->poc[X][ref_idx];
+  if (refs->is_lt[X][ref_idx] || col_diff == cur_diff || col_diff == 0) {
+    mv[0] = m.mv[l][0]; mv[1] = m.mv[l][1];
+  } else {
+    mv[0] = (int16_t)mv_scale(m.mv[l][0], cur_diff, col_diff);
+    mv[1] = (int16_t)mv_scale(m.mv[l][1], cur_diff, col_diff);
+  }
+  return true;
+}
+
+// temporal luma motion vector prediction (8.5.3.2.8)
+template <class Eng>
+bool SliceDec<Eng>::temporal_mv(int xPb, int yPb, int nPbW, int nPbH, int ref_idx, int X, int16_t mv[2]) {
+  if (!sh.temporal_mvp_enabled) return false;
+  const int cl = (sh.slice_type == SLICE_B && !sh.collocated_from_l0) ? 1 : 0;
+  if (sh.collocated_ref_idx >= refs->n[cl]) return false;
+  const RefPic* col = pic.ref_pics[refs->slot[cl][sh.collocated_ref_idx]].get();
+  if (!col || col->failed || col->motion.empty() || col->u_w != pic.u_w || col->u_h != pic.u_h) return false;
+  const int xBr = xPb + nPbW, yBr = yPb + nPbH;
+  if ((yPb >> sps.log2_ctb) == (yBr >> sps.log2_ctb) && yBr < sps.height && xBr < sps.width)
+    if (col_mv(*col, xBr, yBr, ref_idx, X, mv)) return true;
+  return col_mv(*col, xPb + (nPbW >> 1), yPb + (nPbH >> 1), ref_idx, X, mv);
+}
+
+// merge mode (8.5.3.2.2 - 8.5.3.2.5)
+template <class Eng>
+void SliceDec<Eng>::derive_merge(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int merge_idx,
+                                 MotionInfo& out) {
+  const int orig_w = nPbW, orig_h = nPbH;
+  const int lvl = pps.log2_parallel_merge_level;
+  int part_mode = cu_part_mode;
+  if (lvl > 2 && nCbS == 8) { xPb = xCb; yPb = yCb; nPbW = nPbH = nCbS; partIdx = 0; part_mode = 0; }
+  MotionInfo list[6];
+  int n = 0;
+  const int max_cand = sh.max_num_merge_cand;
+  auto same_region = [&](int xN, int yN) { return (xPb >> lvl) == (xN >> lvl) && (yPb >> lvl) == (yN >> lvl); };
+  MotionInfo a1, b1, b0, a0, b2;
+  bool av_a1 = false, av_b1 = false, av_b0 = false, av_a0 = false, av_b2 = false;
+  {
+    const int xN = xPb - 1, yN = yPb + nPbH - 1;
+    if (!same_region(xN, yN) && !((part_mode == 2 || part_mode == 6 || part_mode == 7) && partIdx == 1))
+      av_a1 = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, xN, yN, a1);
+    if (av_a1) list[n++] = a1;
+  }
+  // pruning compares with the neighbour's AVAILABILITY (av_*), not with whether it entered the list (8.5.3.2.3)
+  {
+    const int xN = xPb + nPbW - 1, yN = yPb - 1;
+    if (!same_region(xN, yN) && !((part_mode == 1 || part_mode == 4 || part_mode == 5) && partIdx == 1))
+      av_b1 = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, xN, yN, b1);
+    if (av_b1 && !(av_a1 && same_motion(a1, b1))) list[n++] = b1;
+  }
+  {
+    const int xN = xPb + nPbW, yN = yPb - 1;
+    if (!same_region(xN, yN)) av_b0 = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, xN, yN, b0);
+    if (av_b0 && !(av_b1 && same_motion(b1, b0))) list[n++] = b0;
+  }
+  {
+    const int xN = xPb - 1, yN = yPb + nPbH;
+    if (!same_region(xN, yN)) av_a0 = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, xN, yN, a0);
+    if (av_a0 && !(av_a1 && same_motion(a1, a0))) list[n++] = a0;
+  }
+  if (n < 4) {
+    const int xN = xPb - 1, yN = yPb - 1;
+    if (!same_region(xN, yN)) av_b2 = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, xN, yN, b2);
+    if (av_b2 && !(av_a1 && same_motion(a1, b2)) && !(av_b1 && same_motion(b1, b2))) list[n++] = b2;
+  }
+  if (n > max_cand) n = max_cand;
+  if (n < max_cand) {   // temporal candidate, refIdx 0 in both lists
+    MotionInfo t = {{{0, 0}, {0, 0}}, {-1, -1}, 0, 0};
+    if (refs->n[0] > 0 && temporal_mv(xPb, yPb, nPbW, nPbH, 0, 0, t.mv[0])) { t.pred_flags |= 1; t.ref_idx[0] = 0; }
+    if (sh.slice_type == SLICE_B && refs->n[1] > 0 && temporal_mv(xPb, yPb, nPbW, nPbH, 0, 1, t.mv[1])) { t.pred_flags |= 2; t.ref_idx[1] = 0; }
+    if (t.pred_flags) list[n++] = t;
+  }
+  if (sh.slice_type == SLICE_B && n > 1 && n < max_cand) {   // combined bi-predictive candidates (8.5.3.2.4)
+    static const uint8_t l0c[12] = {0, 1, 0, 2, 1, 2, 0, 3, 1, 3, 2, 3}, l1c[12] = {1, 0, 2, 0, 2, 1, 3, 0, 3, 1, 3, 2};
+    const int orig = n;
+    for (int comb = 0; comb < orig * (orig - 1) && n < max_cand; comb++) {
+      const MotionInfo& c0 = list[l0c[comb]];
+      const MotionInfo& c1 = list[l1c[comb]];
+      if ((c0.pred_flags & 1) && (c1.pred_flags & 2) &&
+          (refs->poc[0][c0.ref_idx[0]] != refs->poc[1][c1.ref_idx[1]] || c0.mv[0][0] != c1.mv[1][0] || c0.mv[0][1] != c1.mv[1][1])) {
+        MotionInfo c = {{{c0.mv[0][0], c0.mv[0][1]}, {c1.mv[1][0], c1.mv[1][1]}}, {c0.ref_idx[0], c1.ref_idx[1]}, 3, 0};
+        list[n++] = c;
+      }
+    }
+  }
+  {   // zero candidates (8.5.3.2.5)
+    const int num_ref = sh.slice_type == SLICE_P ? refs->n[0] : std::min(refs->n[0], refs->n[1]);
+    int zero = 0;
+    while (n < max_cand) {
+      const int ri = zero < num_ref ? zero : 0;
+      MotionInfo z = {{{0, 0}, {0, 0}}, {(int8_t)ri, (int8_t)(sh.slice_type == SLICE_B ? ri : -1)}, (uint8_t)(sh.slice_type == SLICE_B ? 3 : 1), 0};
+      list[n++] = z;
+      zero++;
+    }
+  }
+  out = list[merge_idx < n ? merge_idx : n - 1];
+  if (out.pred_flags == 3 && orig_w + orig_h == 12) { out.pred_flags = 1; out.ref_idx[1] = -1; }   // 8x4 / 4x8: uni-prediction only
+}
+
+// AMVP candidate list (8.5.3.2.6, 8.5.3.2.7) for list X and reference index ref_idx
+template <class Eng>
+void SliceDec<Eng>::derive_amvp(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, int X, int ref_idx,
+                                int16_t cand[2][2]) {
+  const int Y = 1 - X;
+  const int target_poc = refs->poc[X][ref_idx];
+  const bool target_lt = refs->is_lt[X][ref_idx] != 0;
+  MotionInfo nb[5];
+  bool av[5];
+  const int pos[5][2] = {{xPb - 1, yPb + nPbH}, {xPb - 1, yPb + nPbH - 1},                       // A0, A1
+                         {xPb + nPbW, yPb - 1}, {xPb + nPbW - 1, yPb - 1}, {xPb - 1, yPb - 1}};  // B0, B1, B2
+  for (int k = 0; k < 5; k++) av[k] = pb_neighbour(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, pos[k][0], pos[k][1], nb[k]);
+  // candidate from a neighbour without scaling: same reference picture in either list
+  auto exact = [&](const MotionInfo& m, int16_t mv[2]) {
+    for (int t = 0; t < 2; t++) {
+      const int l = t ? Y : X;
+      if ((m.pred_flags & (1 << l)) && refs->poc[l][m.ref_idx[l]] == target_poc) {
+        mv[0] = m.mv[l][0]; mv[1] = m.mv[l][1];
+        return true;
+      }
+    }
+    return false;
+  };
+  // candidate with scaling: any reference of the same kind (long / short term)
+  auto scaled = [&](const MotionInfo& m, int16_t mv[2]) {
+    for (int t = 0; t < 2; t++) {
+      const int l = t ? Y : X;
+      if ((m.pred_flags & (1 << l)) && (refs->is_lt[l][m.ref_idx[l]] != 0) == target_lt) {
+        mv[0] = m.mv[l][0]; mv[1] = m.mv[l][1];
+        const int ref_poc = refs->poc[l][m.ref_idx[l]];
+        if (!target_lt && !refs->is_lt[l][m.ref_idx[l]] && ref_poc != target_poc) {
+          const int td = pic.poc - ref_poc, tb = pic.poc - target_poc;
+          if (td != 0) {
+            mv[0] = (int16_t)mv_scale(mv[0], tb, td);
+            mv[1] = (int16_t)mv_scale(mv[1], tb, td);
+          }
+        }
+        return true;
+      }
+    }
+    return false;
+  };
+  int16_t mva[2] = {0, 0}, mvb[2] = {0, 0};
+  bool has_a = false, has_b = false;
+  const bool is_scaled = av[0] || av[1];
+  for (int k = 0; k < 2 && !has_a; k++) if (av[k]) has_a = exact(nb[k], mva);
+  for (int k = 0; k < 2 && !has_a; k++) if (av[k]) has_a = scaled(nb[k], mva);
+  for (int k = 2; k < 5 && !has_b; k++) if (av[k]) has_b = exact(nb[k], mvb);
+  if (!is_scaled && has_b) { mva[0] = mvb[0]; mva[1] = mvb[1]; has_a = true; }
+  if (!is_scaled) {
+    has_b = false;
+    for (int k = 2; k < 5 && !has_b; k++) if (av[k]) has_b = scaled(nb[k], mvb);
+  }
+  int n = 0;
+  if (has_a) { cand[n][0] = mva[0]; cand[n][1] = mva[1]; n++; }
+  if (has_b && !(has_a && mva[0] == mvb[0] && mva[1] == mvb[1])) { cand[n][0] = mvb[0]; cand[n][1] = mvb[1]; n++; }
+  if (n < 2) {
+    int16_t mvc[2];
+    if (temporal_mv(xPb, yPb, nPbW, nPbH, ref_idx, X, mvc)) { cand[n][0] = mvc[0]; cand[n][1] = mvc[1]; n++; }
+  }
+  while (n < 2) { cand[n][0] = cand[n][1] = 0; n++; }
+}
+
+// mvd_coding (7.3.8.9)
+template <class Eng>
+int SliceDec<Eng>::read_mvd(int16_t mvd[2]) {
+  int gt0[2], gt1[2] = {0, 0};
+  gt0[0] = cabac.bin(ctx[CTX_ABS_MVD_GT0]);
+  gt0[1] = cabac.bin(ctx[CTX_ABS_MVD_GT0]);
+  if (gt0[0]) gt1[0] = cabac.bin(ctx[CTX_ABS_MVD_GT1]);
+  if (gt0[1]) gt1[1] = cabac.bin(ctx[CTX_ABS_MVD_GT1]);
+  for (int c = 0; c < 2; c++) {
+    int v = 0;
+    if (gt0[c]) {
+      v = 1;
+      if (gt1[c]) {   // abs_mvd_minus2: first-order Exp-Golomb, bypass
+        cabac.hint(HINT_MVD_SUFFIX, 0);
+        int k = 1, base = 0;
+        while (cabac.bypass()) {
+          base += 1 << k;
+          if (++k > 16) return E_DECODING;
+        }
+        v = 2 + base + (int)cabac.bypass_bits(k);
+      }
+      if (cabac.bypass()) v = -v;
+    }
+    if (v < -32768 || v > 32767) return E_DECODING;
+    mvd[c] = (int16_t)v;
+  }
+  return E_OK;
+}
+
+// prediction_unit (7.3.8.6) + motion vector derivation (8.5.3.2.1) + the PU work-list record (S3)
+template <class Eng>
+int SliceDec<Eng>::prediction_unit(int xCb, int yCb, int nCbS, int xPb, int yPb, int nPbW, int nPbH, int partIdx, bool skip,
+                                   int& merge_out) {
+  int merge = 1, merge_idx = 0;
+  if (!skip) merge = cabac.bin(ctx[CTX_MERGE_FLAG]);
+  merge_out = merge;
+  MotionInfo mi = {{{0, 0}, {0, 0}}, {-1, -1}, 0, 0};
+  if (merge) {
+    if (sh.max_num_merge_cand > 1) {
+      if (cabac.bin(ctx[CTX_MERGE_IDX])) {
+        merge_idx = 1;
+        while (merge_idx < sh.max_num_merge_cand - 1 && cabac.bypass()) merge_idx++;
+      }
+    }
+    derive_merge(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, merge_idx, mi);
+  } else {
+    int idc = 0;   // 0 L0, 1 L1, 2 BI
+    if (sh.slice_type == SLICE_B) {
+      if (nPbW + nPbH != 12 && cabac.bin(ctx[CTX_INTER_PRED_IDC + cu_ct_depth])) idc = 2;
+      else idc = cabac.bin(ctx[CTX_INTER_PRED_IDC + 4]);
+    }
+    int16_t mvd[2][2] = {{0, 0}, {0, 0}};
+    int mvp_flag[2] = {0, 0};
+    for (int X = 0; X < 2; X++) {
+      if (idc == 1 - X) continue;   // list not used
+      int ri = 0;
+      const int nref = sh.num_ref_idx[X];
+      if (nref > 1) {   // ref_idx_lX: truncated Rice, two context coded bins
+        while (ri < nref - 1) {
+          const int b = ri < 2 ? cabac.bin(ctx[CTX_REF_IDX + ri]) : cabac.bypass();
+          if (!b) break;
+          ri++;
+        }
+      }
+      if (ri >= refs->n[X]) return E_DECODING;
+      mi.ref_idx[X] = (int8_t)ri;
+      mi.pred_flags |= (uint8_t)(1 << X);
+      if (!(X == 1 && sh.mvd_l1_zero && idc == 2)) {
+        const int r = read_mvd(mvd[X]);
+        if (r) return r;
+      }
+      mvp_flag[X] = cabac.bin(ctx[CTX_MVP_FLAG]);
+    }
+    for (int X = 0; X < 2; X++) {
+      if (!(mi.pred_flags & (1 << X))) continue;
+      int16_t cand[2][2];
+      derive_amvp(xCb, yCb, nCbS, xPb, yPb, nPbW, nPbH, partIdx, X, mi.ref_idx[X], cand);
+      for (int c = 0; c < 2; c++) mi.mv[X][c] = (int16_t)(uint16_t)((int)cand[mvp_flag[X]][c] + mvd[X][c]);   // modulo 2^16 (8-272..8-275)
+    }
+  }
+#ifdef B265_PU_TRACE
+  fprintf(stderr, "PU %d %d %dx%d part %d merge %d idx %d pf %d ref %d %d mv %d %d %d %d\n", xPb, yPb, nPbW, nPbH, partIdx, merge, merge_idx,
+          mi.pred_flags, mi.ref_idx[0], mi.ref_idx[1], mi.mv[0][0], mi.mv[0][1], mi.mv[1][0], mi.mv[1][1]);
+#endif
+  // motion field
+  for (int y = 0; y < nPbH; y += 4) {
+    MotionInfo* row = &motion_at(xPb, yPb + y);
+    for (int x = 0; x < (nPbW >> 2); x++) row[x] = mi;
+  }
+  // work-list record
+  b265_pu pu;
+  memset(&pu, 0, sizeof(pu));
+  pu.x = (uint16_t)xPb; pu.y = (uint16_t)yPb; pu.w = (uint8_t)nPbW; pu.h = (uint8_t)nPbH;
+  pu.flags = mi.pred_flags;
+  pu.slice = (uint8_t)sh.slice_index;
+  for (int l = 0; l < 2; l++) {
+    if (!(mi.pred_flags & (1 << l))) continue;
+    pu.mv[l][0] = mi.mv[l][0]; pu.mv[l][1] = mi.mv[l][1];
+    pu.ref_idx[l] = mi.ref_idx[l];
+    pu.ref_slot[l] = refs->slot[l][mi.ref_idx[l]];
+  }
+  pic.pus.push_back(pu);
+  return E_OK;
+}
+
+// prediction-block edges inside a CU (deblock.cc:185-225): filtered like transform edges, strength from the motion
+template <class Eng>
+void SliceDec<Eng>::mark_pu_edges(int x0, int y0, int nCbS, int part_mode) {
+  if (sh.deblocking_disabled || part_mode == 0) return;
+  uint8_t* ui = pic.unit_info.data();
+  const int n_u = nCbS >> 2, ux = x0 >> 2, uy = y0 >> 2;
+  const int half = n_u >> 1, quarter = n_u >> 2;
+  int v_at = -1, h_at = -1;
+  switch (part_mode) {
+    case 1: h_at = half; break;
+    case 2: v_at = half; break;
+    case 3: h_at = half; v_at = half; break;
+    case 4: h_at = quarter; break;
+    case 5: h_at = half + quarter; break;
+    case 6: v_at = quarter; break;
+    default: v_at = half + quarter; break;
+  }
+  if (h_at > 0) for (int i = 0; i < n_u; i++) ui[(uy + h_at) * pic.u_w + ux + i] |= B265_UNIT_EDGE_H;
+  if (v_at > 0) for (int j = 0; j < n_u; j++) ui[(uy + j) * pic.u_w + ux + v_at] |= B265_UNIT_EDGE_V;
+}
+
+// ---- coding unit (7.3.8.5) ---------------------------------------------------------------------------------
 template <class Eng>
 int SliceDec<Eng>::coding_unit(int x0, int y0, int log2_cb) {
   PROF(2);
@@ -387,30 +747,96 @@ int SliceDec<Eng>::coding_unit(int x0, int y0, int log2_cb) {
   decode_qp(x0, y0, log2_cb);
   cu_tq_bypass = 0;
   if (pps.transquant_bypass_enabled) cu_tq_bypass = cabac.bin(ctx[CTX_CU_TQ_BYPASS]);
-  cu_pred_mode = MODE_INTRA;
-  int nxn = 0;
-  if (log2_cb == sps.log2_min_cb) nxn = !cabac.bin(ctx[CTX_PART_MODE]);
+  const int n_cb = 1 << (log2_cb - sps.log2_min_cb), ci0 = cb_idx(x0, y0);
+  const int n_u = n_cbs >> 2, ux = x0 >> 2, uy = y0 >> 2;
+  cu_ct_depth = pic.ct_depth[ci0];
+  int skip = 0;
+  if (sh.slice_type != SLICE_I) {
+    int inc = 0;
+    if (available(x0 - 1, y0) && (pic.cu_flags[cb_idx(x0 - 1, y0)] & 4)) inc++;
+    if (available(x0, y0 - 1) && (pic.cu_flags[cb_idx(x0, y0 - 1)] & 4)) inc++;
+    skip = cabac.bin(ctx[CTX_CU_SKIP + inc]);
+  }
+  int intra = 1, part_mode = 0;
+  if (!skip) {
+    if (sh.slice_type != SLICE_I) intra = cabac.bin(ctx[CTX_PRED_MODE]);
+    if (intra) {
+      if (log2_cb == sps.log2_min_cb) part_mode = cabac.bin(ctx[CTX_PART_MODE]) ? 0 : 3;
+    } else if (!cabac.bin(ctx[CTX_PART_MODE])) {   // part_mode binarisation of an inter CU (9.3.3.7)
+      if (log2_cb == sps.log2_min_cb) {
+        if (cabac.bin(ctx[CTX_PART_MODE + 1])) part_mode = 1;
+        else if (log2_cb == 3) part_mode = 2;
+        else part_mode = cabac.bin(ctx[CTX_PART_MODE + 2]) ? 2 : 3;
+      } else if (!sps.amp_enabled) {
+        part_mode = cabac.bin(ctx[CTX_PART_MODE + 1]) ? 1 : 2;
+      } else {
+        const int horizontal = cabac.bin(ctx[CTX_PART_MODE + 1]);
+        if (cabac.bin(ctx[CTX_PART_MODE + 3])) part_mode = horizontal ? 1 : 2;
+        else part_mode = (horizontal ? 4 : 6) + cabac.bypass();
+      }
+    }
+  } else {
+    intra = 0;
+  }
+  cu_pred_mode = intra ? MODE_INTRA : (skip ? MODE_SKIP : MODE_INTER);
+  cu_part_mode = part_mode;
+  const int nxn = intra && part_mode == 3;
   if (nxn && log2_cb == 3 && sps.log2_min_tb > 2) return E_DECODING;
   // metadata of the CB
-  {
-    const int n_cb = 1 << (log2_cb - sps.log2_min_cb), ci = cb_idx(x0, y0);
-    for (int j = 0; j < n_cb; j++) {
-      memset(&pic.pred_mode[ci + j * pic.cb_w], MODE_INTRA, n_cb);
-      memset(&pic.cu_flags[ci + j * pic.cb_w], cu_tq_bypass ? 2 : 0, n_cb);
+  for (int j = 0; j < n_cb; j++) {
+    memset(&pic.pred_mode[ci0 + j * pic.cb_w], cu_pred_mode, n_cb);
+    memset(&pic.cu_flags[ci0 + j * pic.cb_w], (cu_tq_bypass ? 2 : 0) | (skip ? 4 : 0), n_cb);
+  }
+  if (!intra) {
+    // ---- inter CU: prediction units, then the residual quadtree ----
+    if (!refs || refs->n[0] == 0) return E_DECODING;
+    pic.has_inter = true;
+    const uint8_t unit_bits = (uint8_t)(B265_UNIT_DONE | (cu_tq_bypass ? B265_UNIT_NOFILT : 0));
+    for (int j = 0; j < n_u; j++) memset(&pic.unit_info[(uy + j) * pic.u_w + ux], unit_bits, n_u);
+    int merge0 = 0, r = 0;
+    const int h = n_cbs >> 1, q = n_cbs >> 2, f = n_cbs;
+    // prediction blocks {x, y, w, h} of the partitioning modes (table 7-10)
+    const int parts[8][4][4] = {
+        {{0, 0, f, f}},                                             // 2Nx2N
+        {{0, 0, f, h}, {0, h, f, h}},                               // 2NxN
+        {{0, 0, h, f}, {h, 0, h, f}},                               // Nx2N
+        {{0, 0, h, h}, {h, 0, h, h}, {0, h, h, h}, {h, h, h, h}},   // NxN
+        {{0, 0, f, q}, {0, q, f, f - q}},                           // 2NxnU
+        {{0, 0, f, f - q}, {0, f - q, f, q}},                       // 2NxnD
+        {{0, 0, q, f}, {q, 0, f - q, f}},                           // nLx2N
+        {{0, 0, f - q, f}, {f - q, 0, q, f}}};                      // nRx2N
+    const int n_parts = part_mode == 0 ? 1 : (part_mode == 3 ? 4 : 2);
+    for (int i = 0; i < n_parts && !r; i++) {
+      int merge = 0;
+      r = prediction_unit(x0, y0, n_cbs, x0 + parts[part_mode][i][0], y0 + parts[part_mode][i][1], parts[part_mode][i][2],
+                          parts[part_mode][i][3], i, skip != 0, merge);
+      if (i == 0) merge0 = merge;
     }
+    if (r) return r;
+    mark_pu_edges(x0, y0, n_cbs, part_mode);
+    int rqt_root_cbf = 0;
+    if (!skip) {   // inferred 1 for a merged 2Nx2N CU
+      rqt_root_cbf = 1;
+      if (!(part_mode == 0 && merge0)) rqt_root_cbf = cabac.bin(ctx[CTX_RQT_ROOT_CBF]);
+    }
+    if (!rqt_root_cbf) {
+      mark_tu_edges(x0, y0, log2_cb, x0, y0, log2_cb, false);   // the CU boundary is still a block edge
+      return E_OK;
+    }
+    const int inter_split = sps.max_th_depth_inter == 0 && part_mode != 0;
+    return transform_tree(x0, y0, x0, y0, x0, y0, log2_cb, 0, 0, sps.max_th_depth_inter, inter_split, 1, 1, log2_cb);
   }
   int pcm = 0;
   if (!nxn && sps.pcm_enabled && log2_cb >= sps.log2_min_pcm && log2_cb <= sps.log2_max_pcm) {
     cabac.hint(HINT_PCM_FLAG, 0);
     pcm = cabac.terminate();
   }
-  const int n_u = n_cbs >> 2, ux = x0 >> 2, uy = y0 >> 2;
   uint8_t unit_bits = B265_UNIT_INTRA;
   if (cu_tq_bypass || (pcm && sps.pcm_lf_disabled)) unit_bits |= B265_UNIT_NOFILT;
   if (pcm) unit_bits |= B265_UNIT_DONE;
   for (int j = 0; j < n_u; j++) memset(&pic.unit_info[(uy + j) * pic.u_w + ux], unit_bits, n_u);
   if (pcm) {
-    const int n_cb = 1 << (log2_cb - sps.log2_min_cb), ci = cb_idx(x0, y0);
+    const int ci = ci0;
     for (int j = 0; j < n_cb; j++)
       for (int i = 0; i < n_cb; i++) pic.cu_flags[ci + j * pic.cb_w + i] |= 1;
     for (int j = 0; j < n_u; j++) memset(&pic.ipm[(uy + j) * pic.u_w + ux], 1, n_u);
@@ -550,7 +976,7 @@ int SliceDec<Eng>::transform_unit(int x0, int y0, int xBase, int yBase, int xCU,
   mark_tu_edges(x0, y0, log2_ts, xCU, yCU, log2_cb, cbf_luma != 0);
   // luma
   {
-    const int mode = pic.ipm[(y0 >> 2) * pic.u_w + (x0 >> 2)];
+    const int mode = cu_pred_mode == MODE_INTRA ? pic.ipm[(y0 >> 2) * pic.u_w + (x0 >> 2)] : B265_INTRA_NONE;
     int r = 0;
     b265_tu tu = {};
     tu.x = (uint16_t)x0; tu.y = (uint16_t)y0;
@@ -572,7 +998,7 @@ int SliceDec<Eng>::transform_unit(int x0, int y0, int xBase, int yBase, int xCU,
     b265_tu tu = {};
     tu.x = (uint16_t)xc; tu.y = (uint16_t)yc;
     tu.cidx_log2 = (uint8_t)(c | (lc << 2));
-    tu.intra_mode = (uint8_t)intra_chroma_mode;
+    tu.intra_mode = (uint8_t)(cu_pred_mode == MODE_INTRA ? intra_chroma_mode : B265_INTRA_NONE);
     tu.qp = (uint8_t)(c == 1 ? qp_cb_prime : qp_cr_prime);
     tu.coeff_off = (uint32_t)pic.coeffs.size();
     if (cbf) { int r = residual_coding(xc, yc, lc, c, intra_chroma_mode, tu); if (r) return r; }
@@ -588,7 +1014,6 @@ int SliceDec<Eng>::transform_unit(int x0, int y0, int xBase, int yBase, int xCU,
 template <class Eng>
 int SliceDec<Eng>::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_mode, b265_tu& tu) {
   PROF(1);
-  (void)x0; (void)y0;
   typename Eng::Local cb(cabac);
   Ctx* const cx = ctx;
   const int n = 1 << log2_ts;
@@ -729,12 +1154,16 @@ int SliceDec<Eng>::residual_coding(int x0, int y0, int log2_ts, int cidx, int in
   const size_t ncoded = (size_t)(out - out0);
   pic.coeffs.n += ncoded;
   tu.ncoeff = (uint16_t)ncoded;
-  uint8_t fl = B265_TU_INTRA_CU;
-  if (cidx == 0 && log2_ts == 2) fl |= B265_TU_DST;
+  const bool intra_cu = cu_pred_mode == MODE_INTRA;
+  uint8_t fl = intra_cu ? B265_TU_INTRA_CU : 0;
+  if (intra_cu && cidx == 0 && log2_ts == 2) fl |= B265_TU_DST;
   if (tskip) fl |= B265_TU_SKIP;
   if (cu_tq_bypass) fl |= B265_TU_BYPASS;
   if (implicit_rdpcm_hv) fl |= intra_mode == 26 ? B265_TU_RDPCM_V : B265_TU_RDPCM_H;
-  if (sps.transform_skip_rotation && log2_ts == 2) fl |= B265_TU_ROTATE;
+  // The reference decides the 4x4 rotation from the prediction mode found at the block's COMPONENT coordinates in
+  // the luma-resolution map (transform.cc:392-397 with slice.cc:3471): for chroma that is the CU covering
+  // (x/2, y/2), already decoded.  Kept as is: the reference is the oracle.
+  if (sps.transform_skip_rotation && log2_ts == 2 && pic.pred_mode[cb_idx(x0, y0)] == MODE_INTRA) fl |= B265_TU_ROTATE;
   tu.flags |= fl;
   return E_OK;
 }
@@ -748,12 +1177,15 @@ int SliceDec<Eng>::decode_ctu() {
   pic.ctbs[ctb_rs].addr_ts = ctb_ts;
   pic.ctbs[ctb_rs].slice = (uint16_t)slice_index;
   pic.ctbs[ctb_rs].tile = (uint16_t)pps.tile_id_rs[ctb_rs];
+  pic.self->ctb_slice[ctb_rs] = (uint16_t)slice_index;
   read_sao(rx, ry);
   return coding_quadtree(rx << sps.log2_ctb, ry << sps.log2_ctb, sps.log2_ctb, 0);
 }
 
 }  // namespace syn
 
+
+inline void wait_a_little() { std::this_thread::sleep_for(std::chrono::microseconds(50)); }
 
 struct PicDecodeState {
   std::vector<Ctx> wpp;       // per CTB row: contexts after the 2nd CTB of the row
@@ -769,7 +1201,19 @@ int decode_slice_unit(Picture& pic, const SliceUnit& unit, PicDecodeState& st, c
   const Sps& sps = d.sps;
   const Pps& pps = d.pps;
   const SliceHeader& sh = d.sh;
-  if (sh.slice_type != SLICE_I) return E_NOT_IMPLEMENTED;
+  if (sh.slice_type != SLICE_I) {
+    if (sps.explicit_rdpcm) return E_NOT_IMPLEMENTED;
+    if (sh.slice_index >= (int)pic.slice_refs.size()) return E_DECODING;
+    d.refs = &pic.slice_refs[sh.slice_index];
+    if (d.refs->n[0] < sh.num_ref_idx[0] || (sh.slice_type == SLICE_B && d.refs->n[1] < sh.num_ref_idx[1])) return E_DECODING;
+    if (sh.temporal_mvp_enabled) {   // the collocated picture's motion field must be complete (it precedes in decoding order)
+      const int cl = (sh.slice_type == SLICE_B && !sh.collocated_from_l0) ? 1 : 0;
+      if (sh.collocated_ref_idx < d.refs->n[cl]) {
+        const RefPic* col = pic.ref_pics[d.refs->slot[cl][sh.collocated_ref_idx]].get();
+        while (col && !col->parsed && !col->failed) wait_a_little();
+      }
+    }
+  }
   const int n_ctbs = sps.ctbs_w * sps.ctbs_h;
   d.slice_index = sh.slice_index;
   d.ctb_ts = pps.rs_to_ts[sh.segment_address];

@@ -14,13 +14,18 @@ from libde265_b200.decoder import Decoder
 STREAMS = os.path.join(GOLDEN, "streams")
 
 
-def oracle_planes(job):
+def oracle_planes(job, dpb=None):
+    """reconstruct one picture with the C oracle; `dpb` maps the ids a parse-only decoder puts into
+    ref_surfaces / dst_surface to the finished pictures (inter prediction)"""
     o = load_oracle()
     w, h = job.width, job.height
     planes = [np.zeros((h, w), np.uint8), np.zeros((h // 2, w // 2), np.uint8), np.zeros((h // 2, w // 2), np.uint8)]
     pp = (C.c_void_p * 3)(*[p.ctypes.data for p in planes])
     pitch = (C.c_int * 3)(w, w // 2, w // 2)
-    o.orc_reconstruct_frame(C.byref(job), pp, pitch, None)
+    refs = None
+    if job.n_refs:
+        refs = (C.c_void_p * (3 * job.n_refs))(*[p.ctypes.data for i in range(job.n_refs) for p in dpb[job.ref_surfaces[i]]])
+    o.orc_reconstruct_frame(C.byref(job), pp, pitch, refs)
     if job.flags & L.FRAME_DEBLOCK:
         o.orc_deblock(C.byref(job), pp, pitch)
     if job.flags & L.FRAME_SAO:
@@ -28,18 +33,21 @@ def oracle_planes(job):
         op = (C.c_void_p * 3)(*[p.ctypes.data for p in outs])
         o.orc_sao(C.byref(job), pp, op, pitch)
         planes = outs
+    if dpb is not None:
+        dpb[job.dst_surface] = planes
     return planes
 
 
 def parse_and_reconstruct(data, threads=0, max_frames=None):
     dec = Decoder(parse_only=True, threads=threads)
     md5s = []
+    dpb = {}
 
     def on_pic(img):
         if max_frames is not None and len(md5s) >= max_frames:
             return
         job = dec.job_of(img)
-        md5s.append([hashlib.md5(p.tobytes()).hexdigest() for p in oracle_planes(job)])
+        md5s.append([hashlib.md5(p.tobytes()).hexdigest() for p in oracle_planes(job, dpb)])
 
     dec.decode_stream(data, on_picture=on_pic)
     dec.close()

@@ -53,11 +53,26 @@ NAMED = {
     "gen_all_1280x720": dict(seed=77, w=1280, h=720, frames=2, sao=1, pcm=1, tskip=1, cu_qp_delta=1, sign_hiding=1,
                              tq_bypass=1, scaling=3, slice_ctbs=60, dep_slices=1, dbk_override=1, lf_across_slices=1,
                              p_pcm=0.03, p_tq_bypass=0.05),
+    # ---- P and B slices: merge / AMVP / temporal candidates, AMP, weighted prediction, list modification ----
+    "gen_p_1ref_416x240": dict(seed=41, w=416, h=240, frames=4, inter=1, max_refs=1, p_bslice=0.0, p_islice=0.0),
+    "gen_b_tmvp_416x240": dict(seed=42, w=416, h=240, frames=6, inter=1, max_refs=3, tmvp=1, p_bslice=1.0, sao=1),
+    "gen_pb_amp_weighted_256x192": dict(seed=43, w=256, h=192, frames=5, inter=1, max_refs=3, tmvp=1, amp=1, weighted_pred=1,
+                                        weighted_bipred=1, lists_modification=1, num_ref_default_l0=2, num_ref_default_l1=3,
+                                        cabac_init_present=1, thdepth_inter=2),
+    "gen_pb_parmerge_ctb64_320x192": dict(seed=44, w=320, h=192, ctb=6, frames=4, inter=1, max_refs=2, tmvp=1, par_merge_level=4,
+                                          thdepth_inter=0, amp=1, cu_qp_delta=1, sign_hiding=1),
+    "gen_pb_slices_tiles_256x192": dict(seed=45, w=256, h=192, frames=5, inter=1, max_refs=2, tmvp=1, slice_ctbs=5, dep_slices=1,
+                                        tile_cols=2, tile_rows=2, sao=1, lf_across_slices=0, lf_across_tiles=0, dbk_override=1),
+    "gen_pb_wpp_cip_256x192": dict(seed=46, w=256, h=192, frames=5, inter=1, max_refs=2, wpp=1, cip=1, p_intra_cu=0.5, pcm=1,
+                                   tskip=1, tq_bypass=1, scaling=3),
+    "gen_pb_720p": dict(seed=47, w=1280, h=720, frames=4, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_bipred=1,
+                        slice_ctbs=200, p_skip=0.5),
 }
 
 
-def fuzz_config(seed):
-    """a whole configuration drawn at random, legal by construction (7.4.3.2, 7.4.3.3 range constraints)"""
+def fuzz_config(seed, inter=False):
+    """a whole configuration drawn at random, legal by construction (7.4.3.2, 7.4.3.3 range constraints);
+    inter: P and B slices on top (reference picture sets with negative pictures only)"""
     rnd = random.Random(seed)
     ctb = rnd.choice([4, 5, 5, 6])
     mincb = rnd.choice([c for c in (3, 4, 5) if c <= ctb])
@@ -102,6 +117,13 @@ def fuzz_config(seed):
     a["dbk_control"] = flag(0.8)
     if a["dbk_control"]:
         a.update(dbk_override=flag(), dbk_disabled=flag(0.3), beta_div2=rnd.randint(-6, 6), tc_div2=rnd.randint(-6, 6))
+    if inter:
+        a.update(inter=1, frames=rnd.choice([3, 4, 6]), max_refs=rnd.randint(1, 4), tmvp=flag(0.6), amp=flag(),
+                 thdepth_inter=rnd.randint(0, min(3, ctb - mintb)), weighted_pred=flag(0.4), weighted_bipred=flag(0.4),
+                 lists_modification=flag(0.4), par_merge_level=rnd.randint(2, ctb), cabac_init_present=flag(),
+                 num_ref_default_l0=rnd.randint(1, 3), num_ref_default_l1=rnd.randint(1, 3),
+                 p_bslice=rnd.choice([0.0, 0.5, 1.0]), p_islice=rnd.choice([0.0, 0.15]),
+                 p_skip=rnd.choice([0.1, 0.3, 0.6]), p_intra_cu=rnd.choice([0.0, 0.2, 0.5]), p_merge=rnd.choice([0.2, 0.5, 0.8]))
     a["density"] = rnd.choice([0.5, 1.0, 1.0, 1.5, 2.5])
     a["p_split_cu"] = rnd.choice([0.3, 0.5, 0.7])
     a["p_split_tu"] = rnd.choice([0.2, 0.4, 0.7])
@@ -110,12 +132,15 @@ def fuzz_config(seed):
 
 
 FUZZ_SEEDS = list(range(1000, 1024))
+FUZZ_INTER_SEEDS = list(range(2000, 2024))
 
 
 def catalogue():
     c = dict(NAMED)
     for s in FUZZ_SEEDS:
         c["gen_fuzz_%d" % s] = fuzz_config(s)
+    for s in FUZZ_INTER_SEEDS:
+        c["gen_fuzzpb_%d" % s] = fuzz_config(s, inter=True)
     return c
 
 

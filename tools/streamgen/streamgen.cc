@@ -15,6 +15,7 @@
 #include <string>
 #include <map>
 #include "../../libde265_b200/csrc/host/slice_syntax.h"
+#include "../../libde265_b200/csrc/host/dpb.h"
 
 using namespace b265h;
 
@@ -178,6 +179,12 @@ struct GenEngine {
         script.push_back(0);
         break;
       }
+      case HINT_MVD_SUFFIX: {        // abs_mvd_minus2 (EG1): keep motion vector differences moderate
+        const int k = s.rng->range(0, s.rng->chance(0.05) ? 9 : 4);
+        for (int i = 0; i < k; i++) script.push_back(1);
+        script.push_back(0);
+        break;
+      }
       case HINT_COEFF_REMAINING: {   // prefix of coeff_abs_level_remaining: levels stay inside 16 bits (7.4.9.11)
         int prefix = 0;
         if (s.rng->chance(s.p_big_coeff)) prefix = s.rng->range(7, 16 - arg);
@@ -287,6 +294,9 @@ struct StreamParams {
   int cb_qp_offset, cr_qp_offset, slice_chroma_offsets, tq_bypass, tile_cols, tile_rows, tiles_uniform, wpp;
   int lf_across_tiles, lf_across_slices, dbk_control, dbk_override_enabled, dbk_disabled, beta_div2, tc_div2;
   int chroma_qp_offset_list, diff_cu_chroma_qp_offset_depth;
+  // inter
+  int inter, th_depth_inter, amp, tmvp, weighted_pred, weighted_bipred, lists_modification, par_merge_level, cabac_init_present;
+  int num_ref_default[2];
   std::vector<int> col_w, row_h;   // explicit tile sizes (non-uniform)
 };
 
@@ -311,17 +321,17 @@ static std::vector<uint8_t> write_sps(const StreamParams& p, Rng& rng) {
   bw.u1(0);            // no conformance window
   bw.ue(0); bw.ue(0);  // 8 bit
   bw.ue(p.log2_max_poc_lsb - 4);
-  bw.u1(1); bw.ue(1); bw.ue(0); bw.ue(0);
+  bw.u1(1); bw.ue(p.inter ? 5 : 1); bw.ue(0); bw.ue(0);
   bw.ue(p.log2_min_cb - 3); bw.ue(p.log2_ctb - p.log2_min_cb);
   bw.ue(p.log2_min_tb - 2); bw.ue(p.log2_max_tb - p.log2_min_tb);
-  bw.ue(0);            // max_transform_hierarchy_depth_inter
+  bw.ue(p.th_depth_inter);
   bw.ue(p.th_depth_intra);
   bw.u1(p.scaling != 0);
   if (p.scaling) {
     bw.u1(p.scaling == 2);
     if (p.scaling == 2) scaling_list_data(bw, rng);
   }
-  bw.u1(0);            // amp
+  bw.u1(p.amp);
   bw.u1(p.sao);
   bw.u1(p.pcm);
   if (p.pcm) {
@@ -331,7 +341,7 @@ static std::vector<uint8_t> write_sps(const StreamParams& p, Rng& rng) {
   }
   bw.ue(0);            // no short-term RPS in the SPS
   bw.u1(0);            // no long-term pictures
-  bw.u1(0);            // temporal MVP
+  bw.u1(p.tmvp);
   bw.u1(p.strong_intra);
   bw.u1(0);            // VUI
   bw.u1(rext);
@@ -348,15 +358,15 @@ static std::vector<uint8_t> write_pps(const StreamParams& p, Rng& rng) {
   BitWriter bw;
   const bool tiles = p.tile_cols > 1 || p.tile_rows > 1;
   bw.ue(0); bw.ue(0);
-  bw.u1(p.dep_slices); bw.u1(0); bw.u(3, 0); bw.u1(p.sign_hiding); bw.u1(0);
-  bw.ue(0); bw.ue(0);
+  bw.u1(p.dep_slices); bw.u1(0); bw.u(3, 0); bw.u1(p.sign_hiding); bw.u1(p.cabac_init_present);
+  bw.ue(p.num_ref_default[0] - 1); bw.ue(p.num_ref_default[1] - 1);
   bw.se(p.init_qp - 26);
   bw.u1(p.cip); bw.u1(p.tskip);
   bw.u1(p.cu_qp_delta);
   if (p.cu_qp_delta) bw.ue(p.diff_cu_qp_delta_depth);
   bw.se(p.cb_qp_offset); bw.se(p.cr_qp_offset);
   bw.u1(p.slice_chroma_offsets);
-  bw.u1(0); bw.u1(0);
+  bw.u1(p.weighted_pred); bw.u1(p.weighted_bipred);
   bw.u1(p.tq_bypass);
   bw.u1(tiles); bw.u1(p.wpp);
   if (tiles) {
@@ -377,8 +387,8 @@ static std::vector<uint8_t> write_pps(const StreamParams& p, Rng& rng) {
   }
   bw.u1(p.scaling == 3);
   if (p.scaling == 3) scaling_list_data(bw, rng);
-  bw.u1(0);            // lists_modification_present
-  bw.ue(0);            // log2_parallel_merge_level - 2
+  bw.u1(p.lists_modification);
+  bw.ue(p.par_merge_level - 2);
   bw.u1(0);            // slice header extension
   const bool rext = (p.tskip && p.log2_max_tskip > 2) || p.chroma_qp_offset_list;
   bw.u1(rext);
@@ -410,6 +420,16 @@ struct SegmentParams {
   bool dbk_override = false, dbk_disabled = false;
   int beta_div2 = 0, tc_div2 = 0;
   bool lf_across = false;
+  // inter
+  int slice_type = SLICE_I;
+  int n_neg = 0, delta_poc_minus1[16], used[16];   // short-term RPS of the picture (negative pictures only)
+  bool tmvp = false, override_num_ref = false, mvd_l1_zero = false, cabac_init = false, col_from_l0 = true;
+  int num_ref[2] = {1, 1}, max_merge_cand = 5;
+  bool list_mod[2] = {false, false};
+  int list_entry[2][16];
+  // prediction weights
+  int luma_denom = 0, delta_chroma_denom = 0;
+  int lw_flag[2][16], cw_flag[2][16], d_lw[2][16], l_off[2][16], d_cw[2][16][2], d_coff[2][16][2];
 };
 
 static int ceil_log2(uint32_t v) { int n = 0; while ((1u << n) < v) n++; return n; }
@@ -426,13 +446,48 @@ static std::vector<uint8_t> write_slice_header(const Sps& sps, const Pps& pps, c
     bw.u(ceil_log2((uint32_t)(sps.ctbs_w * sps.ctbs_h)), (uint32_t)s.address);
   }
   if (!s.dependent) {
-    bw.ue(SLICE_I);
+    bw.ue((uint32_t)s.slice_type);
+    int n_curr = 0;
     if (s.nal_type != NAL_IDR_W_RADL && s.nal_type != NAL_IDR_N_LP) {
       bw.u(sps.log2_max_poc_lsb, (uint32_t)s.poc_lsb);
-      bw.u1(0);               // RPS coded in the slice header ...
-      bw.ue(0); bw.ue(0);     // ... and empty (the SPS holds no sets, so no inter-RPS flag)
+      bw.u1(0);               // RPS coded in the slice header (the SPS holds no sets, so no inter-RPS flag)
+      bw.ue((uint32_t)s.n_neg); bw.ue(0);
+      for (int i = 0; i < s.n_neg; i++) { bw.ue((uint32_t)s.delta_poc_minus1[i]); bw.u1(s.used[i]); n_curr += s.used[i]; }
+      if (sps.temporal_mvp_enabled) bw.u1(s.tmvp);
     }
     if (sps.sao_enabled) { bw.u1(s.sao_luma); bw.u1(s.sao_chroma); }
+    if (s.slice_type != SLICE_I) {
+      const int nl = s.slice_type == SLICE_B ? 2 : 1;
+      bw.u1(s.override_num_ref);
+      if (s.override_num_ref) for (int l = 0; l < nl; l++) bw.ue((uint32_t)s.num_ref[l] - 1);
+      if (pps.lists_modification_present && n_curr > 1) {
+        int nb = 0;
+        while ((1 << nb) < n_curr) nb++;
+        for (int l = 0; l < nl; l++) {
+          bw.u1(s.list_mod[l]);
+          if (s.list_mod[l]) for (int i = 0; i < s.num_ref[l]; i++) bw.u(nb, (uint32_t)s.list_entry[l][i]);
+        }
+      }
+      if (s.slice_type == SLICE_B) bw.u1(s.mvd_l1_zero);
+      if (pps.cabac_init_present) bw.u1(s.cabac_init);
+      if (s.tmvp) {
+        if (s.slice_type == SLICE_B) bw.u1(s.col_from_l0);
+        if ((s.col_from_l0 && s.num_ref[0] > 1) || (!s.col_from_l0 && s.num_ref[1] > 1)) bw.ue(0);   // collocated_ref_idx
+      }
+      if ((pps.weighted_pred && s.slice_type == SLICE_P) || (pps.weighted_bipred && s.slice_type == SLICE_B)) {
+        bw.ue((uint32_t)s.luma_denom);
+        bw.se(s.delta_chroma_denom);
+        for (int l = 0; l < nl; l++) {
+          for (int i = 0; i < s.num_ref[l]; i++) bw.u1(s.lw_flag[l][i]);
+          for (int i = 0; i < s.num_ref[l]; i++) bw.u1(s.cw_flag[l][i]);
+          for (int i = 0; i < s.num_ref[l]; i++) {
+            if (s.lw_flag[l][i]) { bw.se(s.d_lw[l][i]); bw.se(s.l_off[l][i]); }
+            if (s.cw_flag[l][i]) for (int j = 0; j < 2; j++) { bw.se(s.d_cw[l][i][j]); bw.se(s.d_coff[l][i][j]); }
+          }
+        }
+      }
+      bw.ue((uint32_t)(5 - s.max_merge_cand));
+    }
     bw.se(s.qp_delta);
     if (pps.slice_chroma_qp_offsets_present) { bw.se(s.cb_off); bw.se(s.cr_off); }
     if (pps.chroma_qp_offset_list_enabled) bw.u1(s.cu_chroma_qp_offset);
@@ -502,6 +557,17 @@ int main(int argc, char** argv) {
   p.beta_div2 = cfg.geti("beta_div2", 0); p.tc_div2 = cfg.geti("tc_div2", 0);
   p.chroma_qp_offset_list = cfg.geti("chroma_qp_offset_list", 0);
   p.diff_cu_chroma_qp_offset_depth = cfg.geti("chroma_qp_offset_depth", 1);
+  p.inter = cfg.geti("inter", 0);
+  p.th_depth_inter = cfg.geti("thdepth_inter", 1);
+  p.amp = cfg.geti("amp", 0);
+  p.tmvp = cfg.geti("tmvp", 0);
+  p.weighted_pred = cfg.geti("weighted_pred", 0); p.weighted_bipred = cfg.geti("weighted_bipred", 0);
+  p.lists_modification = cfg.geti("lists_modification", 0);
+  p.par_merge_level = cfg.geti("par_merge_level", 2);
+  p.cabac_init_present = cfg.geti("cabac_init_present", 0);
+  p.num_ref_default[0] = cfg.geti("num_ref_default_l0", 1); p.num_ref_default[1] = cfg.geti("num_ref_default_l1", 1);
+  const int max_refs = cfg.geti("max_refs", 3);
+  const double p_bslice = cfg.get("p_bslice", 0.5), p_islice = cfg.get("p_islice", 0.15);
   const int frames = cfg.geti("frames", 2);
   const int slice_ctbs = cfg.geti("slice_ctbs", 0);   // mean slice-segment length in CTBs (0 = one per picture)
   const int qp_lo = cfg.geti("qp_lo", 22), qp_hi = cfg.geti("qp_hi", 38);
@@ -560,10 +626,17 @@ int main(int argc, char** argv) {
   setp(CTX_SIG_COEFF, 44, std::min(0.9, 0.25 * density));
   setp(CTX_GT1, 24, 0.3);
   setp(CTX_GT2, 6, 0.3);
+  setp(CTX_CU_SKIP, 3, cfg.get("p_skip", 0.3));
+  setp(CTX_PRED_MODE, 1, cfg.get("p_intra_cu", 0.25));
+  setp(CTX_RQT_ROOT_CBF, 1, 0.6);
+  setp(CTX_MERGE_FLAG, 1, cfg.get("p_merge", 0.5));
+  setp(CTX_ABS_MVD_GT0, 1, 0.6);
   setp(CTX_CHROMA_QP_OFFSET_FLAG, 1, 0.6);
   setp(CTX_CHROMA_QP_OFFSET_IDX, 1, 0.5);
 
   int poc = 0;
+  size_t total_pus = 0;
+  Dpb dpb;
   for (int f = 0; f < frames; f++) {
     Picture pic;
     pic.sps = sps;
@@ -574,10 +647,33 @@ int main(int argc, char** argv) {
     st.wpp_valid.assign(sps->ctbs_h, 0);
     int nal_type = NAL_IDR_W_RADL;
     if (f > 0) {
-      const int r = (int)rng.below(8);
-      nal_type = r == 0 ? NAL_IDR_N_LP : (r == 1 ? NAL_CRA : (r == 2 ? NAL_TRAIL_N : NAL_TRAIL_R));
+      const int r = (int)rng.below(p.inter ? 16 : 8);
+      nal_type = r == 0 ? NAL_IDR_N_LP : (r == 1 ? NAL_CRA : (r == 2 && !p.inter ? NAL_TRAIL_N : NAL_TRAIL_R));
     }
-    if (nal_type == NAL_IDR_W_RADL || nal_type == NAL_IDR_N_LP) poc = 0; else poc++;
+    const bool idr = nal_type == NAL_IDR_W_RADL || nal_type == NAL_IDR_N_LP;
+    if (idr) poc = 0; else poc++;
+    pic.poc = poc;
+    pic.self->poc = poc;
+    // ---- reference picture set of the picture (negative pictures only: decoding order = output order) ----
+    SegmentParams rps_params;
+    bool pic_tmvp = false;
+    if (p.inter && nal_type == NAL_TRAIL_R) {
+      std::vector<int> pocs;
+      for (const auto& r : dpb.pics) pocs.push_back(r->poc);
+      std::sort(pocs.begin(), pocs.end(), [](int a, int b) { return a > b; });   // closest first
+      int prev = poc;
+      for (int q : pocs) {
+        if (rps_params.n_neg >= max_refs + 1 || !rng.chance(0.85)) continue;    // dropped from the DPB
+        rps_params.delta_poc_minus1[rps_params.n_neg] = prev - q - 1;
+        rps_params.used[rps_params.n_neg] = rng.chance(0.8);
+        rps_params.n_neg++;
+        prev = q;
+      }
+      pic_tmvp = p.tmvp && rng.chance(0.8);
+    }
+    int n_curr = 0;
+    for (int i = 0; i < rps_params.n_neg; i++) n_curr += rps_params.used[i];
+    bool rps_applied = false;
 
     // ---- slice segment plan in tile-scan order: (first, last) addresses + dependent flag -------------------
     struct Seg { int first_ts, last_ts; bool dependent; };
@@ -637,6 +733,39 @@ int main(int argc, char** argv) {
       sp.dependent = segs[si].dependent;
       sp.address = pps->ts_to_rs[segs[si].first_ts];
       sp.poc_lsb = poc & ((1 << sps->log2_max_poc_lsb) - 1);
+      sp.n_neg = rps_params.n_neg;
+      memcpy(sp.delta_poc_minus1, rps_params.delta_poc_minus1, sizeof(sp.delta_poc_minus1));
+      memcpy(sp.used, rps_params.used, sizeof(sp.used));
+      sp.tmvp = pic_tmvp;
+      if (!sp.dependent && n_curr > 0 && !rng.chance(p_islice)) {
+        sp.slice_type = rng.chance(p_bslice) ? SLICE_B : SLICE_P;
+        const int nl = sp.slice_type == SLICE_B ? 2 : 1;
+        sp.override_num_ref = rng.chance(0.6);
+        for (int l = 0; l < 2; l++) sp.num_ref[l] = sp.override_num_ref ? rng.range(1, std::min(4, n_curr + 1)) : pps->num_ref_idx_default[l];
+        if (pps->lists_modification_present && n_curr > 1)
+          for (int l = 0; l < nl; l++) {
+            sp.list_mod[l] = rng.chance(0.5);
+            // entry 0 stays the first picture of the initial list: every slice of a picture must name the same
+            // collocated picture (collocated_ref_idx is always 0 here)
+            for (int i = 0; i < sp.num_ref[l]; i++) sp.list_entry[l][i] = i == 0 ? 0 : rng.range(0, n_curr - 1);
+          }
+        sp.mvd_l1_zero = rng.chance(0.3);
+        sp.cabac_init = rng.chance(0.5);
+        sp.col_from_l0 = sp.slice_type == SLICE_P || rng.chance(0.5);
+        sp.max_merge_cand = rng.range(1, 5);
+        sp.luma_denom = rng.range(0, 7);
+        sp.delta_chroma_denom = rng.range(-sp.luma_denom, 7 - sp.luma_denom);
+        for (int l = 0; l < 2; l++)
+          for (int i = 0; i < 16; i++) {
+            sp.lw_flag[l][i] = rng.chance(0.6); sp.cw_flag[l][i] = rng.chance(0.6);
+            sp.d_lw[l][i] = rng.range(-128, 127); sp.l_off[l][i] = rng.range(-128, 127);
+            for (int j = 0; j < 2; j++) { sp.d_cw[l][i][j] = rng.range(-128, 127); sp.d_coff[l][i][j] = rng.range(-512, 511); }
+            if (rng.chance(0.5)) {   // moderate weights: the picture stays inside the sample range more often
+              sp.d_lw[l][i] = rng.range(-8, 8); sp.l_off[l][i] = rng.range(-10, 10);
+              for (int j = 0; j < 2; j++) { sp.d_cw[l][i][j] = rng.range(-8, 8); sp.d_coff[l][i][j] = rng.range(-20, 20); }
+            }
+          }
+      }
       if (!sp.dependent) {
         sp.sao_luma = sps->sao_enabled && rng.chance(0.8);
         sp.sao_chroma = sps->sao_enabled && rng.chance(0.8);
@@ -661,9 +790,17 @@ int main(int argc, char** argv) {
         const int r = parse_slice_header(br, nal_type, ps, n_slices ? &prev_independent : nullptr, {}, unit.hdr, pp);
         if (r) { fprintf(stderr, "streamgen: own slice header does not parse (%d)\n", r); return 1; }
       }
+      if (!rps_applied) {   // once per picture, from its first slice segment header
+        dpb.apply_rps(unit.hdr, *sps, poc, idr || f == 0);
+        dpb.pics.push_back(pic.self);
+        rps_applied = true;
+      }
       if (!sp.dependent) {
         unit.hdr.slice_index = n_slices++;
         prev_independent = unit.hdr;
+        SliceRefs sr;
+        if (!dpb.build_lists(unit.hdr, pic, sr)) { fprintf(stderr, "streamgen: reference picture missing\n"); return 1; }
+        pic.slice_refs.push_back(sr);
       }
       unit.hdr.data_offset = 0;
       unit.hdr.entry_points.clear();
@@ -690,7 +827,11 @@ int main(int argc, char** argv) {
       payload.insert(payload.end(), esc_data.begin(), esc_data.end());
       put_nal(stream, nal_type, payload);
     }
+    pic.self->slice_refs = pic.slice_refs;
+    pic.self->parsed = 1;
+    total_pus += pic.pus.size();
   }
+  if (cfg.geti("verbose", 0)) fprintf(stderr, "streamgen: %d pictures, %zu prediction units\n", frames, total_pus);
   FILE* fo = fopen(argv[1], "wb");
   if (!fo) { perror(argv[1]); return 1; }
   fwrite(stream.data(), 1, stream.size(), fo);
