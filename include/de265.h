@@ -214,7 +214,7 @@ LIBDE265_API void b265_de265_get_stats(de265_decoder_context*, double out[8]);
 /* Test/bench aid: decoders created while this is on only PARSE (CABAC + syntax -> work lists) and never
  * touch the GPU; returned images carry no pixels, their work lists are read with
  * b265_de265_image_job(ctx, img, struct b265_frame_job* out) declared in b265.h terms (pointers stay
- * valid until the image is released). */
+ * valid until the image is released).  Such decoders deliver the pictures in DECODING order. */
 LIBDE265_API void b265_de265_set_parse_only(int on);
 /* `out` is a b265_frame_job (b265.h); void* here so that de265.h stays free of b265.h types */
 LIBDE265_API int b265_de265_image_job(de265_decoder_context*, const struct de265_image*, void* out_b265_frame_job);

@@ -492,6 +492,10 @@ struct Decoder {
       release_locked(*img);
       return;
     }
+    if (parse_only) {   // parse-only clients (tests) get the pictures in DECODING order: they reconstruct with the CPU
+      output.push_back(std::move(img));   // oracle, which needs every reference before the picture that uses it
+      return;
+    }
     reorder.push_back(std::move(img));
     while ((int)reorder.size() > max_reorder) bump();
   }

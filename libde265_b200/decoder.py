@@ -62,6 +62,8 @@ def _bind():
     lib.b265_de265_get_stats.restype = None
     lib.b265_de265_image_job.argtypes = [vp, vp, C.POINTER(L.FrameJob)]
     lib.b265_de265_image_poc.argtypes = [vp]
+    lib.de265_get_image_NAL_header.argtypes = [vp, C.POINTER(C.c_int), vp, vp, vp]
+    lib.de265_get_image_NAL_header.restype = None
     _bound = True
     return lib
 

@@ -47,11 +47,18 @@ def parse_and_reconstruct(data, threads=0, max_frames=None):
         if max_frames is not None and len(md5s) >= max_frames:
             return
         job = dec.job_of(img)
+        nal = C.c_int(0)
+        dec.lib.de265_get_image_NAL_header(img, C.byref(nal), None, None, None)
+        if 16 <= nal.value <= 20:   # IDR / BLA: a new coded video sequence, output before anything that follows
+            group[0] += 1
+        order.append((group[0], dec.lib.b265_de265_image_poc(img), len(order)))
         md5s.append([hashlib.md5(p.tobytes()).hexdigest() for p in oracle_planes(job, dpb)])
 
+    group, order = [0], []
     dec.decode_stream(data, on_picture=on_pic)
     dec.close()
-    return md5s
+    # a parse-only decoder delivers in decoding order; the golden MD5s are in output order
+    return [md5s[i] for _, _, i in sorted(order)]
 
 
 def load_stream(name):

@@ -65,6 +65,11 @@ NAMED = {
                                         tile_cols=2, tile_rows=2, sao=1, lf_across_slices=0, lf_across_tiles=0, dbk_override=1),
     "gen_pb_wpp_cip_256x192": dict(seed=46, w=256, h=192, frames=5, inter=1, max_refs=2, wpp=1, cip=1, p_intra_cu=0.5, pcm=1,
                                    tskip=1, tq_bypass=1, scaling=3),
+    "gen_pb_reorder_416x240": dict(seed=48, w=416, h=240, frames=9, inter=1, reorder=1, max_refs=3, tmvp=1, p_bslice=0.8, sao=1),
+    "gen_pb_longterm_256x192": dict(seed=49, w=256, h=192, frames=12, inter=1, long_term=1, poc_bits=4, max_refs=2, tmvp=1,
+                                    lists_modification=1, weighted_pred=1),
+    "gen_pb_reorder_longterm_256x192": dict(seed=50, w=256, h=192, frames=13, inter=1, reorder=1, long_term=1, poc_bits=5,
+                                            max_refs=3, tmvp=1, amp=1, slice_ctbs=8),
     "gen_pb_720p": dict(seed=47, w=1280, h=720, frames=4, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_bipred=1,
                         slice_ctbs=200, p_skip=0.5),
 }
@@ -124,6 +129,10 @@ def fuzz_config(seed, inter=False):
                  num_ref_default_l0=rnd.randint(1, 3), num_ref_default_l1=rnd.randint(1, 3),
                  p_bslice=rnd.choice([0.0, 0.5, 1.0]), p_islice=rnd.choice([0.0, 0.15]),
                  p_skip=rnd.choice([0.1, 0.3, 0.6]), p_intra_cu=rnd.choice([0.0, 0.2, 0.5]), p_merge=rnd.choice([0.2, 0.5, 0.8]))
+        if flag(0.4):
+            a.update(reorder=1, frames=rnd.choice([5, 9]))      # output order differs from decoding order
+        if flag(0.4):
+            a.update(long_term=1, poc_bits=rnd.choice([4, 5, 8]), frames=max(a["frames"], 8))
     a["density"] = rnd.choice([0.5, 1.0, 1.0, 1.5, 2.5])
     a["p_split_cu"] = rnd.choice([0.3, 0.5, 0.7])
     a["p_split_tu"] = rnd.choice([0.2, 0.4, 0.7])

@@ -297,14 +297,15 @@ struct StreamParams {
   // inter
   int inter, th_depth_inter, amp, tmvp, weighted_pred, weighted_bipred, lists_modification, par_merge_level, cabac_init_present;
   int num_ref_default[2];
+  int reorder, long_term;
   std::vector<int> col_w, row_h;   // explicit tile sizes (non-uniform)
 };
 
-static std::vector<uint8_t> write_vps() {
+static std::vector<uint8_t> write_vps(int dpb_minus1 = 1, int reorder = 0) {
   BitWriter bw;
   bw.u(4, 0); bw.u1(1); bw.u1(1); bw.u(6, 0); bw.u(3, 0); bw.u1(1); bw.u(16, 0xffff);
   profile_tier_level(bw, 1);
-  bw.u1(1); bw.ue(1); bw.ue(0); bw.ue(0);
+  bw.u1(1); bw.ue(dpb_minus1); bw.ue(reorder); bw.ue(0);
   bw.u(6, 0); bw.ue(0); bw.u1(0); bw.u1(0);
   bw.trailing();
   return bw.b;
@@ -321,7 +322,7 @@ static std::vector<uint8_t> write_sps(const StreamParams& p, Rng& rng) {
   bw.u1(0);            // no conformance window
   bw.ue(0); bw.ue(0);  // 8 bit
   bw.ue(p.log2_max_poc_lsb - 4);
-  bw.u1(1); bw.ue(p.inter ? 5 : 1); bw.ue(0); bw.ue(0);
+  bw.u1(1); bw.ue(p.inter ? 6 : 1); bw.ue(p.reorder ? 3 : 0); bw.ue(0);
   bw.ue(p.log2_min_cb - 3); bw.ue(p.log2_ctb - p.log2_min_cb);
   bw.ue(p.log2_min_tb - 2); bw.ue(p.log2_max_tb - p.log2_min_tb);
   bw.ue(p.th_depth_inter);
@@ -340,7 +341,8 @@ static std::vector<uint8_t> write_sps(const StreamParams& p, Rng& rng) {
     bw.u1(p.pcm_lf_disabled);
   }
   bw.ue(0);            // no short-term RPS in the SPS
-  bw.u1(0);            // no long-term pictures
+  bw.u1(p.long_term);
+  if (p.long_term) bw.ue(0);   // none listed in the SPS
   bw.u1(p.tmvp);
   bw.u1(p.strong_intra);
   bw.u1(0);            // VUI
@@ -422,7 +424,9 @@ struct SegmentParams {
   bool lf_across = false;
   // inter
   int slice_type = SLICE_I;
-  int n_neg = 0, delta_poc_minus1[16], used[16];   // short-term RPS of the picture (negative pictures only)
+  int n_neg = 0, delta_poc_minus1[16], used[16];   // short-term RPS of the picture: negative pictures ...
+  int n_pos = 0, delta_pos_minus1[16], used_pos[16]; // ... and positive ones (streams with reordering)
+  int n_lt = 0, lt_lsb[16], lt_used[16], lt_msb_present[16], lt_msb_delta[16];   // long-term pictures
   bool tmvp = false, override_num_ref = false, mvd_l1_zero = false, cabac_init = false, col_from_l0 = true;
   int num_ref[2] = {1, 1}, max_merge_cand = 5;
   bool list_mod[2] = {false, false};
@@ -451,8 +455,19 @@ static std::vector<uint8_t> write_slice_header(const Sps& sps, const Pps& pps, c
     if (s.nal_type != NAL_IDR_W_RADL && s.nal_type != NAL_IDR_N_LP) {
       bw.u(sps.log2_max_poc_lsb, (uint32_t)s.poc_lsb);
       bw.u1(0);               // RPS coded in the slice header (the SPS holds no sets, so no inter-RPS flag)
-      bw.ue((uint32_t)s.n_neg); bw.ue(0);
+      bw.ue((uint32_t)s.n_neg); bw.ue((uint32_t)s.n_pos);
       for (int i = 0; i < s.n_neg; i++) { bw.ue((uint32_t)s.delta_poc_minus1[i]); bw.u1(s.used[i]); n_curr += s.used[i]; }
+      for (int i = 0; i < s.n_pos; i++) { bw.ue((uint32_t)s.delta_pos_minus1[i]); bw.u1(s.used_pos[i]); n_curr += s.used_pos[i]; }
+      if (sps.long_term_ref_pics_present) {
+        bw.ue((uint32_t)s.n_lt);
+        for (int i = 0; i < s.n_lt; i++) {
+          bw.u(sps.log2_max_poc_lsb, (uint32_t)s.lt_lsb[i]);
+          bw.u1(s.lt_used[i]);
+          bw.u1(s.lt_msb_present[i]);
+          if (s.lt_msb_present[i]) bw.ue((uint32_t)s.lt_msb_delta[i]);
+          n_curr += s.lt_used[i];
+        }
+      }
       if (sps.temporal_mvp_enabled) bw.u1(s.tmvp);
     }
     if (sps.sao_enabled) { bw.u1(s.sao_luma); bw.u1(s.sao_chroma); }
@@ -558,6 +573,8 @@ int main(int argc, char** argv) {
   p.chroma_qp_offset_list = cfg.geti("chroma_qp_offset_list", 0);
   p.diff_cu_chroma_qp_offset_depth = cfg.geti("chroma_qp_offset_depth", 1);
   p.inter = cfg.geti("inter", 0);
+  p.reorder = cfg.geti("reorder", 0);
+  p.long_term = cfg.geti("long_term", 0);
   p.th_depth_inter = cfg.geti("thdepth_inter", 1);
   p.amp = cfg.geti("amp", 0);
   p.tmvp = cfg.geti("tmvp", 0);
@@ -584,7 +601,7 @@ int main(int argc, char** argv) {
   }
 
   std::vector<uint8_t> stream;
-  put_nal(stream, NAL_VPS, escape(write_vps()));
+  put_nal(stream, NAL_VPS, escape(write_vps(p.inter ? 6 : 1, p.reorder ? 3 : 0)));
   const std::vector<uint8_t> sps_rbsp = write_sps(p, rng), pps_rbsp = write_pps(p, rng);
   put_nal(stream, NAL_SPS, escape(sps_rbsp));
   put_nal(stream, NAL_PPS, escape(pps_rbsp));
@@ -636,6 +653,7 @@ int main(int argc, char** argv) {
 
   int poc = 0;
   size_t total_pus = 0;
+  int anchor = 0, mini = 0;
   Dpb dpb;
   for (int f = 0; f < frames; f++) {
     Picture pic;
@@ -651,7 +669,14 @@ int main(int argc, char** argv) {
       nal_type = r == 0 ? NAL_IDR_N_LP : (r == 1 ? NAL_CRA : (r == 2 && !p.inter ? NAL_TRAIL_N : NAL_TRAIL_R));
     }
     const bool idr = nal_type == NAL_IDR_W_RADL || nal_type == NAL_IDR_N_LP;
-    if (idr) poc = 0; else poc++;
+    if (p.reorder && !idr && nal_type != NAL_TRAIL_R) nal_type = NAL_TRAIL_R;   // (no CRA inside a reordered group)
+    if (idr) { poc = 0; anchor = 0; mini = 0; }
+    else if (!p.reorder) poc++;
+    else {   // groups of four pictures decoded as anchor+4, +2, +1, +3 (output order differs from decoding order)
+      static const int step[4] = {4, 2, 1, 3};
+      poc = anchor + step[mini];
+      if (++mini == 4) { mini = 0; anchor += 4; }
+    }
     pic.poc = poc;
     pic.self->poc = poc;
     // ---- reference picture set of the picture (negative pictures only: decoding order = output order) ----
@@ -661,18 +686,59 @@ int main(int argc, char** argv) {
       std::vector<int> pocs;
       for (const auto& r : dpb.pics) pocs.push_back(r->poc);
       std::sort(pocs.begin(), pocs.end(), [](int a, int b) { return a > b; });   // closest first
+      int n_after = 0;
+      for (int q : pocs) n_after += q > poc;
+      if (p.long_term) {
+        const int max_lsb = 1 << sps->log2_max_poc_lsb;
+        std::vector<int> lts;
+        for (const auto& r : dpb.pics) {
+          if (r->poc > poc) continue;   // (pictures still to be output after this one stay short-term)
+          if (r->is_lt ? rng.chance(0.9) : rng.chance(0.2)) lts.push_back(r->poc);
+          else if (r->is_lt) pocs.erase(std::find(pocs.begin(), pocs.end(), r->poc));   // once long-term, never short-term again
+        }
+        std::sort(lts.begin(), lts.end(), [](int a, int b) { return a > b; });   // MSB cycles must not decrease
+        int acc = 0;
+        for (int q : lts) {
+          pocs.erase(std::find(pocs.begin(), pocs.end(), q));
+          if (rps_params.n_lt >= 2) continue;   // dropped
+          const int i = rps_params.n_lt++;
+          int same_lsb = 0;
+          for (const auto& r : dpb.pics) same_lsb += ((r->poc ^ q) & (max_lsb - 1)) == 0;
+          const int cycle = ((poc & ~(max_lsb - 1)) - (q & ~(max_lsb - 1))) / max_lsb;
+          rps_params.lt_lsb[i] = q & (max_lsb - 1);
+          rps_params.lt_used[i] = rng.chance(0.8);
+          rps_params.lt_msb_present[i] = same_lsb > 1 || rng.chance(0.4);
+          rps_params.lt_msb_delta[i] = cycle - acc;
+          if (rps_params.lt_msb_present[i]) acc = cycle;
+        }
+      }
       int prev = poc;
-      for (int q : pocs) {
-        if (rps_params.n_neg >= max_refs + 1 || !rng.chance(0.85)) continue;    // dropped from the DPB
+      for (int q : pocs) {   // pictures before this one in output order, closest first
+        if (q > poc) continue;
+        // in a reordered group the anchors and the group's earlier pictures must stay until the group is complete
+        const bool must_keep = p.reorder && q >= anchor - 4;
+        if (!must_keep && (rps_params.n_neg >= max_refs + 1 || !rng.chance(0.85))) continue;    // dropped from the DPB
+        if (rps_params.n_neg + rps_params.n_lt + n_after >= 6) continue;   // sps_max_dec_pic_buffering_minus1
         rps_params.delta_poc_minus1[rps_params.n_neg] = prev - q - 1;
         rps_params.used[rps_params.n_neg] = rng.chance(0.8);
         rps_params.n_neg++;
+        prev = q;
+      }
+      prev = poc;
+      for (auto it = pocs.rbegin(); it != pocs.rend(); ++it) {   // pictures after this one in output order, closest first
+        const int q = *it;
+        if (q < poc) continue;
+        rps_params.delta_pos_minus1[rps_params.n_pos] = q - prev - 1;
+        rps_params.used_pos[rps_params.n_pos] = rng.chance(0.8);
+        rps_params.n_pos++;
         prev = q;
       }
       pic_tmvp = p.tmvp && rng.chance(0.8);
     }
     int n_curr = 0;
     for (int i = 0; i < rps_params.n_neg; i++) n_curr += rps_params.used[i];
+    for (int i = 0; i < rps_params.n_pos; i++) n_curr += rps_params.used_pos[i];
+    for (int i = 0; i < rps_params.n_lt; i++) n_curr += rps_params.lt_used[i];
     bool rps_applied = false;
 
     // ---- slice segment plan in tile-scan order: (first, last) addresses + dependent flag -------------------
@@ -736,6 +802,13 @@ int main(int argc, char** argv) {
       sp.n_neg = rps_params.n_neg;
       memcpy(sp.delta_poc_minus1, rps_params.delta_poc_minus1, sizeof(sp.delta_poc_minus1));
       memcpy(sp.used, rps_params.used, sizeof(sp.used));
+      sp.n_lt = rps_params.n_lt;
+      memcpy(sp.lt_lsb, rps_params.lt_lsb, sizeof(sp.lt_lsb)); memcpy(sp.lt_used, rps_params.lt_used, sizeof(sp.lt_used));
+      memcpy(sp.lt_msb_present, rps_params.lt_msb_present, sizeof(sp.lt_msb_present));
+      memcpy(sp.lt_msb_delta, rps_params.lt_msb_delta, sizeof(sp.lt_msb_delta));
+      sp.n_pos = rps_params.n_pos;
+      memcpy(sp.delta_pos_minus1, rps_params.delta_pos_minus1, sizeof(sp.delta_pos_minus1));
+      memcpy(sp.used_pos, rps_params.used_pos, sizeof(sp.used_pos));
       sp.tmvp = pic_tmvp;
       if (!sp.dependent && n_curr > 0 && !rng.chance(p_islice)) {
         sp.slice_type = rng.chance(p_bslice) ? SLICE_B : SLICE_P;
