@@ -386,7 +386,10 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                 "host_parse_core_seconds_per_step": (s1["parse_s"] - s0["parse_s"]) / a.steps},
         "gpu_launches": int(launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_intra_wavefront", "achieved": intra_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": intra_gbs / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": intra_gbs / peak,
+                     # dram__bytes_read+write of one launch of this kernel on THIS workload, from the ncu --set full
+                     # capture summarised in profiles/r1_summary.md (r1_intra_final); other workloads: not captured
+                     "traffic": 1353.6e6 if wl == "stream_4k" else None, "peak_source": peak_src,
                      "note": "largest share of the step; dependency-latency bound (CTB anti-diagonal wavefront, one warp "
                              "walks a CTB), not bandwidth bound; algorithmic bytes per picture = 1.5*W*H written + 2 B per "
                              "sample of a coded TB read; time = CUDA events around this launch only",

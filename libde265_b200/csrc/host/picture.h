@@ -162,7 +162,7 @@ struct Picture {
     sao.assign((size_t)s.ctbs_w * s.ctbs_h, b265_sao{});
     self = std::make_shared<RefPic>();
     self->u_w = u_w; self->u_h = u_h; self->ctbs_w = s.ctbs_w; self->log2_ctb = s.log2_ctb;
-    self->motion.assign((size_t)u_w * u_h, MotionInfo{{{0, 0}, {0, 0}}, {-1, -1}, 0, 0});
+    self->motion.clear();   // allocated by the first P/B slice (an empty field reads as "all intra")
     self->ctb_slice.assign((size_t)s.ctbs_w * s.ctbs_h, 0);
     ref_pics.clear(); slice_refs.clear(); has_inter = false;
     tus.clear(); coeffs.clear(); pus.clear(); pcms.clear(); pcm_samples.clear(); slices.clear();

@@ -1204,6 +1204,7 @@ int decode_slice_unit(Picture& pic, const SliceUnit& unit, PicDecodeState& st, c
   if (sh.slice_type != SLICE_I) {
     if (sps.explicit_rdpcm) return E_NOT_IMPLEMENTED;
     if (sh.slice_index >= (int)pic.slice_refs.size()) return E_DECODING;
+    if (pic.self->motion.empty()) pic.self->motion.assign((size_t)pic.u_w * pic.u_h, MotionInfo{{{0, 0}, {0, 0}}, {-1, -1}, 0, 0});
     d.refs = &pic.slice_refs[sh.slice_index];
     if (d.refs->n[0] < sh.num_ref_idx[0] || (sh.slice_type == SLICE_B && d.refs->n[1] < sh.num_ref_idx[1])) return E_DECODING;
     if (sh.temporal_mvp_enabled) {   // the collocated picture's motion field must be complete (it precedes in decoding order)

@@ -76,7 +76,7 @@ __device__ __noinline__ uint32_t sao_edge_slow(const FrameDev& f, const b265_sao
 
 #define SAO_ROWS 8   // rows per thread (divides every CTB size of every component)
 
-__global__ void __launch_bounds__(256) k_sao(const FrameDev* __restrict__ frames) {
+__global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.z / 3];
   const uint32_t fflags = f.flags;
   const b265_sao* sao = f.sao;
