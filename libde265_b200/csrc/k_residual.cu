@@ -124,6 +124,8 @@ k_residual_sparse(const FrameDev* __restrict__ frames, const uint32_t* __restric
 void launch_residual_dense(cudaStream_t st, int log2, int kind, int rdpcm, int n_blocks,
                            const int16_t* coeffs, const uint8_t* qp, uint8_t* dst, int sm_count) {
   if (n_blocks <= 0) return;
+  // DCT / DST: the packed dp2a kernels (k_residual_dense.cu); skip / bypass / rdpcm: the generic kernel below
+  if (!rdpcm && launch_residual_dense_dct(st, log2, kind, n_blocks, coeffs, qp, dst, sm_count)) return;
   const int G = 32 >> log2;
   long long warps = ((long long)n_blocks + G - 1) / G;
   long long ctas = (warps + B265_WARPS_PER_CTA - 1) / B265_WARPS_PER_CTA;

@@ -1,0 +1,238 @@
+// k_residual_dense.cu — dense batch form of dequant + inverse DCT/DST + add (acceleration.h transform slots
+// `transform_add_8[4]` / `transform_4x4_dst_add_8`, acceleration.h:152-153; BASELINE config 2).
+// Block i has N*N int16 levels at coeffs + i*N*N and N*N pixels at dst + i*N*N; HBM traffic per block is
+// 2*N*N (levels) + N*N (prediction) + N*N (reconstruction) = 4*N*N bytes.
+//
+// The kernels are issue-bound integer code, so the design minimises instructions per sample:
+//  * both 1-D passes run on packed int16 pairs with dp2a (transform_packed.cuh);
+//  * the clip to 16 bit after dequantisation / after the first pass is the saturation of the pack instruction;
+//  * the final Clip1 + byte packing is cvt.pack.sat.u8;
+//  * 4x4: one lane owns a whole block in registers (no shared memory, no shuffles);
+//  * 8..32: N lanes per block.  Phase A: each lane loads two ROWS (ra, rb) of a pair word for a chunk of columns,
+//    dequantises and writes VERTICAL pairs {x[ra][c], x[rb][c]} to shared memory.  Phase B: lane = column, reads its
+//    N/2 pair words, first pass, writes the clipped int16 results to the slot of the row pass' pair order.
+//    Phase C: lane = row, reads N/2 pair words with 128-bit loads, second pass, adds the prediction row, stores.
+//    Zero-tail bounds (rows for B, columns for C) are reduced over the warp and select a shorter butterfly.
+#include "transform_packed.cuh"
+#include "kernels.h"
+
+#define DENSE_WARPS 8
+
+// ------------------------------------------------------------------------------------------------------
+// 4x4: one lane per block
+// ------------------------------------------------------------------------------------------------------
+template <bool DST>
+__global__ void __launch_bounds__(256)
+k_dense4(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint8_t* __restrict__ dst, int n_blocks) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_blocks; i += stride) {
+    const uint4* src = reinterpret_cast<const uint4*>(coeffs + i * 16);
+    const uint4 w0 = src[0], w1 = src[1];   // rows 0,1 / rows 2,3
+    const uint4 pr = *reinterpret_cast<const uint4*>(dst + i * 16);
+    const DequantK k = dequant_consts(qp ? (int)qp[i] : -1, 2);
+    const uint32_t r0[2] = {w0.x, w0.y}, r1[2] = {w0.z, w0.w}, r2[2] = {w1.x, w1.y}, r3[2] = {w1.z, w1.w};
+    // vertical pairs per column: P0 = (row1,row3), P1 = (row0,row2)
+    uint32_t PA[4], PB[4];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      PB[2 * h] = pack_sat16(dq(s16_lo(r0[h]), k), dq(s16_lo(r2[h]), k));
+      PB[2 * h + 1] = pack_sat16(dq(s16_hi(r0[h]), k), dq(s16_hi(r2[h]), k));
+      PA[2 * h] = pack_sat16(dq(s16_lo(r1[h]), k), dq(s16_lo(r3[h]), k));
+      PA[2 * h + 1] = pack_sat16(dq(s16_hi(r1[h]), k), dq(s16_hi(r3[h]), k));
+    }
+    int g[4][4];   // g[c][row]
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+      const uint32_t P[2] = {PA[c], PB[c]};
+      if (DST) idst4_packed(P, g[c], 64);
+      else IdctP<4, 4>::run(P, g[c], 64);
+    }
+    uint32_t o[4];
+    const uint32_t pw[4] = {pr.x, pr.y, pr.z, pr.w};
+#pragma unroll
+    for (int y = 0; y < 4; y++) {
+      const uint32_t P[2] = {pack_sat16(g[1][y] >> 7, g[3][y] >> 7), pack_sat16(g[0][y] >> 7, g[2][y] >> 7)};
+      int r[4];
+      if (DST) idst4_packed(P, r, 2048);
+      else IdctP<4, 4>::run(P, r, 2048);
+      o[y] = pack_sat8((r[0] >> 12) + (int)(pw[y] & 0xff), (r[1] >> 12) + (int)((pw[y] >> 8) & 0xff),
+                       (r[2] >> 12) + (int)((pw[y] >> 16) & 0xff), (r[3] >> 12) + (int)(pw[y] >> 24));
+    }
+    *reinterpret_cast<uint4*>(dst + i * 16) = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// 8x8 .. 32x32
+// ------------------------------------------------------------------------------------------------------
+template <int LOG2>
+struct DenseCfg {
+  static constexpr int N = 1 << LOG2;
+  static constexpr int G = 32 / N;                       // blocks per warp
+  static constexpr int CH = (N == 8) ? 4 : 8;            // columns per phase-A task
+  static constexpr int KCH = N / CH;                     // chunks per row
+  static constexpr int ROUNDS = (N / 2) * KCH / N;       // phase-A tasks per lane
+  static constexpr int GSW = N / 2 + (N >= 16 ? 4 : 0);  // phase-C row stride in words (conflict-free 128-bit reads)
+  // words per block: max(pair plane N*N/2, result plane N*GSW) + a bank offset between the blocks of a warp
+  static constexpr int BLKW = (N == 8) ? 40 : (N == 16) ? 208 : 640;
+  static constexpr int WARPW = G * BLKW;
+};
+
+template <int LOG2, int L>
+__device__ __forceinline__ void dense_cols(uint32_t* blk, int sub, int slot) {
+  constexpr int N = 1 << LOG2, GSW = DenseCfg<LOG2>::GSW;
+  uint32_t P[N / 2];
+#pragma unroll
+  for (int p = 0; p < N / 2; p++) P[p] = (pair_first(N, p) < L) ? blk[p * N + sub] : 0u;
+  int out[N];
+  IdctP<N, L>::run(P, out, 64);
+  __syncwarp();   // the result plane overlays the pair plane: every lane has read its words
+  int16_t* g = reinterpret_cast<int16_t*>(blk) + slot;
+#pragma unroll
+  for (int y = 0; y < N; y++) g[y * (2 * GSW)] = (int16_t)pack_sat16(out[y] >> 7, 0);
+}
+
+template <int LOG2, int L>
+__device__ __forceinline__ void dense_rows(const uint32_t* blk, int sub, const uint32_t* pred, uint8_t* drow, bool active) {
+  constexpr int N = 1 << LOG2, GSW = DenseCfg<LOG2>::GSW;
+  uint32_t P[N / 2];
+  const uint4* row = reinterpret_cast<const uint4*>(blk + sub * GSW);
+#pragma unroll
+  for (int q = 0; q < N / 8; q++) {
+    uint4 w = row[q];
+    P[4 * q] = w.x; P[4 * q + 1] = w.y; P[4 * q + 2] = w.z; P[4 * q + 3] = w.w;
+  }
+  int out[N];
+  IdctP<N, L>::run(P, out, 2048);
+  uint32_t o[N / 4];
+#pragma unroll
+  for (int q = 0; q < N / 4; q++) {
+    const uint32_t pw = pred[q];
+    o[q] = pack_sat8((out[4 * q] >> 12) + (int)(pw & 0xff), (out[4 * q + 1] >> 12) + (int)((pw >> 8) & 0xff),
+                     (out[4 * q + 2] >> 12) + (int)((pw >> 16) & 0xff), (out[4 * q + 3] >> 12) + (int)(pw >> 24));
+  }
+  if (active) {
+    if (N == 8) *reinterpret_cast<uint2*>(drow) = make_uint2(o[0], o[1]);
+    else {
+#pragma unroll
+      for (int q = 0; q < N / 16; q++) reinterpret_cast<uint4*>(drow)[q] = make_uint4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+    }
+  }
+}
+
+template <int LOG2>
+__global__ void __launch_bounds__(DENSE_WARPS * 32)
+k_dense(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint8_t* __restrict__ dst, int n_blocks) {
+  using Cfg = DenseCfg<LOG2>;
+  constexpr int N = Cfg::N, G = Cfg::G, CH = Cfg::CH, KCH = Cfg::KCH, ROUNDS = Cfg::ROUNDS;
+  __shared__ __align__(16) uint32_t smem[DENSE_WARPS][Cfg::WARPW];
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int grp = lane / N, sub = lane % N;
+  uint32_t* blk = smem[warp] + grp * Cfg::BLKW;
+  const int slot = pair_slot(N, sub);   // where column `sub` goes in the row pass' pair order
+  // phase-A tasks of this lane: pair word j (rows ra, rb), column chunk kc
+  int t_rows[ROUNDS], t_j[ROUNDS], t_c0[ROUNDS];
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    const int t = sub + N * r;
+    t_j[r] = t / KCH;
+    t_c0[r] = (t % KCH) * CH;
+    t_rows[r] = pair_rows(N, t_j[r]);
+  }
+  const int warps_total = gridDim.x * DENSE_WARPS;
+  for (long long base = (long long)(blockIdx.x * DENSE_WARPS + warp) * G; base < n_blocks; base += (long long)warps_total * G) {
+    const long long i = base + grp;
+    const bool active = i < n_blocks;
+    const long long ib = active ? i : 0;
+    // prediction row `sub` (needed last, requested first)
+    uint32_t pred[N / 4];
+    uint8_t* drow = dst + ib * (N * N) + sub * N;
+    if (N == 8) {
+      uint2 w = *reinterpret_cast<const uint2*>(drow);
+      pred[0] = w.x; pred[1] = w.y;
+    } else {
+#pragma unroll
+      for (int q = 0; q < N / 16; q++) {
+        uint4 w = reinterpret_cast<const uint4*>(drow)[q];
+        pred[4 * q] = w.x; pred[4 * q + 1] = w.y; pred[4 * q + 2] = w.z; pred[4 * q + 3] = w.w;
+      }
+    }
+    const DequantK k = dequant_consts(qp ? (int)qp[ib] : -1, LOG2);
+    // ---- phase A ----
+    uint32_t wa[ROUNDS][CH / 2], wb[ROUNDS][CH / 2];
+    const int16_t* cblk = coeffs + ib * (N * N);
+#pragma unroll
+    for (int r = 0; r < ROUNDS; r++) {
+      const int ra = t_rows[r] & 0xff, rb = t_rows[r] >> 8;
+      if (CH == 4) {
+        uint2 a = *reinterpret_cast<const uint2*>(cblk + ra * N + t_c0[r]);
+        uint2 b = *reinterpret_cast<const uint2*>(cblk + rb * N + t_c0[r]);
+        wa[r][0] = a.x; wa[r][1] = a.y; wb[r][0] = b.x; wb[r][1] = b.y;
+      } else {
+        uint4 a = *reinterpret_cast<const uint4*>(cblk + ra * N + t_c0[r]);
+        uint4 b = *reinterpret_cast<const uint4*>(cblk + rb * N + t_c0[r]);
+        wa[r][0] = a.x; wa[r][1] = a.y; wa[r][2] = a.z; wa[r][3] = a.w;
+        wb[r][0] = b.x; wb[r][1] = b.y; wb[r][2] = b.z; wb[r][3] = b.w;
+      }
+    }
+    int nrows = 0, ncols = 0;
+    __syncwarp();   // previous iteration's phase C has read the result plane
+#pragma unroll
+    for (int r = 0; r < ROUNDS; r++) {
+      const int ra = t_rows[r] & 0xff, rb = t_rows[r] >> 8;
+      uint32_t ora = 0, orb = 0;
+      uint32_t v[CH];
+#pragma unroll
+      for (int h = 0; h < CH / 2; h++) {
+        const uint32_t a = active ? wa[r][h] : 0u, b = active ? wb[r][h] : 0u;
+        ora |= a; orb |= b;
+        if (a | b) ncols = max(ncols, t_c0[r] + 2 * h + 2);
+        v[2 * h] = pack_sat16(dq(s16_lo(a), k), dq(s16_lo(b), k));
+        v[2 * h + 1] = pack_sat16(dq(s16_hi(a), k), dq(s16_hi(b), k));
+      }
+      if (ora) nrows = max(nrows, ra + 1);
+      if (orb) nrows = max(nrows, rb + 1);
+      uint4* d = reinterpret_cast<uint4*>(blk + t_j[r] * N + t_c0[r]);
+      d[0] = make_uint4(v[0], v[1], v[2], v[3]);
+      if (CH == 8) d[1] = make_uint4(v[4], v[5], v[6], v[7]);
+    }
+    nrows = __reduce_max_sync(B265_FULL_MASK, nrows);
+    ncols = __reduce_max_sync(B265_FULL_MASK, ncols);
+    __syncwarp();
+    // ---- phase B: first pass down the columns ----
+    if (N >= 32 && nrows > 16) dense_cols<LOG2, (N >= 32 ? 32 : N)>(blk, sub, slot);
+    else if (N >= 16 && nrows > 8) dense_cols<LOG2, (N >= 16 ? 16 : N)>(blk, sub, slot);
+    else if (nrows > 4) dense_cols<LOG2, 8>(blk, sub, slot);
+    else dense_cols<LOG2, 4>(blk, sub, slot);
+    __syncwarp();
+    // ---- phase C: second pass along the rows, add, store ----
+    if (N >= 32 && ncols > 16) dense_rows<LOG2, (N >= 32 ? 32 : N)>(blk, sub, pred, drow, active);
+    else if (N >= 16 && ncols > 8) dense_rows<LOG2, (N >= 16 ? 16 : N)>(blk, sub, pred, drow, active);
+    else if (ncols > 4) dense_rows<LOG2, 8>(blk, sub, pred, drow, active);
+    else dense_rows<LOG2, 4>(blk, sub, pred, drow, active);
+  }
+}
+
+// returns false when (log2, kind) has no fast kernel (skip / bypass: the generic kernel in k_residual.cu)
+bool launch_residual_dense_dct(cudaStream_t st, int log2, int kind, int n_blocks, const int16_t* coeffs,
+                               const uint8_t* qp, uint8_t* dst, int sm_count) {
+  if (kind != B265_TR_DCT && !(kind == B265_TR_DST && log2 == 2)) return false;
+  if (log2 == 2) {
+    long long ctas = ((long long)n_blocks + 255) / 256;
+    int grid = (int)min(ctas, (long long)sm_count * 16);
+    if (kind == B265_TR_DST) k_dense4<true><<<grid, 256, 0, st>>>(coeffs, qp, dst, n_blocks);
+    else k_dense4<false><<<grid, 256, 0, st>>>(coeffs, qp, dst, n_blocks);
+    return true;
+  }
+  const int G = 32 >> log2;
+  long long warps = ((long long)n_blocks + G - 1) / G;
+  long long ctas = (warps + DENSE_WARPS - 1) / DENSE_WARPS;
+  int grid = (int)min(ctas, (long long)sm_count * 16);
+  dim3 b(DENSE_WARPS * 32);
+  switch (log2) {
+    case 3: k_dense<3><<<grid, b, 0, st>>>(coeffs, qp, dst, n_blocks); break;
+    case 4: k_dense<4><<<grid, b, 0, st>>>(coeffs, qp, dst, n_blocks); break;
+    default: k_dense<5><<<grid, b, 0, st>>>(coeffs, qp, dst, n_blocks); break;
+  }
+  return true;
+}

@@ -6,6 +6,9 @@
 
 void launch_residual_dense(cudaStream_t st, int log2, int kind, int rdpcm, int n_blocks,
                            const int16_t* coeffs, const uint8_t* qp, uint8_t* dst, int sm_count);
+// packed dp2a kernels for kind DCT (all sizes) and DST 4x4 (k_residual_dense.cu); false = no fast kernel for this kind
+bool launch_residual_dense_dct(cudaStream_t st, int log2, int kind, int n_blocks, const int16_t* coeffs,
+                               const uint8_t* qp, uint8_t* dst, int sm_count);
 // to_scratch: write the residuals as int16 into FrameDev::resid (intra TBs, added later by the
 // wavefront) instead of adding them to the prediction already in the plane (inter TBs)
 void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order,
