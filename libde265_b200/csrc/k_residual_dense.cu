@@ -78,12 +78,25 @@ struct DenseCfg {
   static constexpr int WARPW = G * BLKW;
 };
 
+// pair words of column `sub` whose first row lies below L (compile-time selection; the others are zero)
+template <int N, int L, int P0 = 0>
+struct LoadPairs {
+  static __device__ __forceinline__ void run(uint32_t* P, const uint32_t* col) {
+    constexpr bool used = pair_first(N, P0) < L;
+    P[P0] = used ? col[P0 * N] : 0u;
+    LoadPairs<N, L, P0 + 1>::run(P, col);
+  }
+};
+template <int N, int L>
+struct LoadPairs<N, L, N / 2> {
+  static __device__ __forceinline__ void run(uint32_t*, const uint32_t*) {}
+};
+
 template <int LOG2, int L>
 __device__ __forceinline__ void dense_cols(uint32_t* blk, int sub, int slot) {
   constexpr int N = 1 << LOG2, GSW = DenseCfg<LOG2>::GSW;
   uint32_t P[N / 2];
-#pragma unroll
-  for (int p = 0; p < N / 2; p++) P[p] = (pair_first(N, p) < L) ? blk[p * N + sub] : 0u;
+  LoadPairs<N, L>::run(P, blk + sub);
   int out[N];
   IdctP<N, L>::run(P, out, 64);
   __syncwarp();   // the result plane overlays the pair plane: every lane has read its words
