@@ -18,6 +18,12 @@
 
 #define DENSE_WARPS 8
 
+// four reconstructed samples: Clip1(pred byte + (r >> 12)), packed
+__device__ __forceinline__ uint32_t add_pack4(const int* r, uint32_t pw) {
+  return pack_sat8((r[0] >> 12) + byte_of<0>(pw), (r[1] >> 12) + byte_of<1>(pw),
+                   (r[2] >> 12) + byte_of<2>(pw), (r[3] >> 12) + byte_of<3>(pw));
+}
+
 // ------------------------------------------------------------------------------------------------------
 // 4x4: one lane per block
 // ------------------------------------------------------------------------------------------------------
@@ -35,10 +41,10 @@ k_dense4(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uin
     uint32_t PA[4], PB[4];
 #pragma unroll
     for (int h = 0; h < 2; h++) {
-      PB[2 * h] = pack_sat16(dq(s16_lo(r0[h]), k), dq(s16_lo(r2[h]), k));
-      PB[2 * h + 1] = pack_sat16(dq(s16_hi(r0[h]), k), dq(s16_hi(r2[h]), k));
-      PA[2 * h] = pack_sat16(dq(s16_lo(r1[h]), k), dq(s16_lo(r3[h]), k));
-      PA[2 * h + 1] = pack_sat16(dq(s16_hi(r1[h]), k), dq(s16_hi(r3[h]), k));
+      PB[2 * h] = pack_sat16(dq_lo(r0[h], k), dq_lo(r2[h], k));
+      PB[2 * h + 1] = pack_sat16(dq_hi(r0[h], k), dq_hi(r2[h], k));
+      PA[2 * h] = pack_sat16(dq_lo(r1[h], k), dq_lo(r3[h], k));
+      PA[2 * h + 1] = pack_sat16(dq_hi(r1[h], k), dq_hi(r3[h], k));
     }
     int g[4][4];   // g[c][row]
 #pragma unroll
@@ -51,19 +57,74 @@ k_dense4(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uin
     const uint32_t pw[4] = {pr.x, pr.y, pr.z, pr.w};
 #pragma unroll
     for (int y = 0; y < 4; y++) {
-      const uint32_t P[2] = {pack_sat16(g[1][y] >> 7, g[3][y] >> 7), pack_sat16(g[0][y] >> 7, g[2][y] >> 7)};
+      const uint32_t P[2] = {pack_sat16(sra<7>(g[1][y]), sra<7>(g[3][y])), pack_sat16(sra<7>(g[0][y]), sra<7>(g[2][y]))};
       int r[4];
       if (DST) idst4_packed(P, r, 2048);
       else IdctP<4, 4>::run(P, r, 2048);
-      o[y] = pack_sat8((r[0] >> 12) + (int)(pw[y] & 0xff), (r[1] >> 12) + (int)((pw[y] >> 8) & 0xff),
-                       (r[2] >> 12) + (int)((pw[y] >> 16) & 0xff), (r[3] >> 12) + (int)(pw[y] >> 24));
+      o[y] = add_pack4(r, pw[y]);
     }
     *reinterpret_cast<uint4*>(dst + i * 16) = make_uint4(o[0], o[1], o[2], o[3]);
   }
 }
 
 // ------------------------------------------------------------------------------------------------------
-// 8x8 .. 32x32
+// 8x8: one lane per block as well (64 levels = 32 registers).  Columns are transformed in the pair order of the
+// row pass, two at a time, so the clipped first-pass results are packed straight into the row pass' pair words.
+// ------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_dense8(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint8_t* __restrict__ dst, int n_blocks) {
+  constexpr int KA[4] = {1, 5, 2, 0}, KB[4] = {3, 7, 6, 4};   // pair order of the 8-point transform
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_blocks; i += stride) {
+    const uint4* src = reinterpret_cast<const uint4*>(coeffs + i * 64);
+    uint32_t x[8][4];   // row r, word w = columns (2w, 2w+1)
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+      const uint4 w = __ldg(src + r);
+      x[r][0] = w.x; x[r][1] = w.y; x[r][2] = w.z; x[r][3] = w.w;
+    }
+    uint4* dp = reinterpret_cast<uint4*>(dst + i * 64);
+    uint32_t pw[16];   // row y = words 2y, 2y+1
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const uint4 w = dp[q];
+      pw[4 * q] = w.x; pw[4 * q + 1] = w.y; pw[4 * q + 2] = w.z; pw[4 * q + 3] = w.w;
+    }
+    const DequantK k = dequant_consts(qp ? (int)qp[i] : -1, 3);
+    uint32_t Q[4][8];
+#pragma unroll
+    for (int p = 0; p < 4; p++) {
+      int o[2][8];
+#pragma unroll
+      for (int h = 0; h < 2; h++) {
+        const int c = h ? KB[p] : KA[p];
+        uint32_t P[4];
+#pragma unroll
+        for (int v = 0; v < 4; v++) {
+          const uint32_t wa = x[KA[v]][c >> 1], wb = x[KB[v]][c >> 1];
+          P[v] = (c & 1) ? pack_sat16(dq_hi(wa, k), dq_hi(wb, k)) : pack_sat16(dq_lo(wa, k), dq_lo(wb, k));
+        }
+        IdctP<8, 8>::run(P, o[h], 64);
+      }
+#pragma unroll
+      for (int y = 0; y < 8; y++) Q[p][y] = pack_sat16(sra<7>(o[0][y]), sra<7>(o[1][y]));
+    }
+    uint32_t out[16];
+#pragma unroll
+    for (int y = 0; y < 8; y++) {
+      const uint32_t P[4] = {Q[0][y], Q[1][y], Q[2][y], Q[3][y]};
+      int r[8];
+      IdctP<8, 8>::run(P, r, 2048);
+      out[2 * y] = add_pack4(r, pw[2 * y]);
+      out[2 * y + 1] = add_pack4(r + 4, pw[2 * y + 1]);
+    }
+#pragma unroll
+    for (int q = 0; q < 4; q++) dp[q] = make_uint4(out[4 * q], out[4 * q + 1], out[4 * q + 2], out[4 * q + 3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// 16x16, 32x32 (and 8x8 with -DDENSE8_SMEM)
 // ------------------------------------------------------------------------------------------------------
 template <int LOG2>
 struct DenseCfg {
@@ -102,7 +163,7 @@ __device__ __forceinline__ void dense_cols(uint32_t* blk, int sub, int slot) {
   __syncwarp();   // the result plane overlays the pair plane: every lane has read its words
   int16_t* g = reinterpret_cast<int16_t*>(blk) + slot;
 #pragma unroll
-  for (int y = 0; y < N; y++) g[y * (2 * GSW)] = (int16_t)pack_sat16(out[y] >> 7, 0);
+  for (int y = 0; y < N; y++) g[y * (2 * GSW)] = (int16_t)pack_sat16(sra<7>(out[y]), 0);
 }
 
 template <int LOG2, int L>
@@ -121,8 +182,7 @@ __device__ __forceinline__ void dense_rows(const uint32_t* blk, int sub, const u
 #pragma unroll
   for (int q = 0; q < N / 4; q++) {
     const uint32_t pw = pred[q];
-    o[q] = pack_sat8((out[4 * q] >> 12) + (int)(pw & 0xff), (out[4 * q + 1] >> 12) + (int)((pw >> 8) & 0xff),
-                     (out[4 * q + 2] >> 12) + (int)((pw >> 16) & 0xff), (out[4 * q + 3] >> 12) + (int)(pw >> 24));
+    o[q] = add_pack4(out + 4 * q, pw);
   }
   if (active) {
     if (N == 8) *reinterpret_cast<uint2*>(drow) = make_uint2(o[0], o[1]);
@@ -200,8 +260,8 @@ k_dense(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint
         const uint32_t a = active ? wa[r][h] : 0u, b = active ? wb[r][h] : 0u;
         ora |= a; orb |= b;
         if (a | b) ncols = max(ncols, t_c0[r] + 2 * h + 2);
-        v[2 * h] = pack_sat16(dq(s16_lo(a), k), dq(s16_lo(b), k));
-        v[2 * h + 1] = pack_sat16(dq(s16_hi(a), k), dq(s16_hi(b), k));
+        v[2 * h] = pack_sat16(dq_lo(a, k), dq_lo(b, k));
+        v[2 * h + 1] = pack_sat16(dq_hi(a, k), dq_hi(b, k));
       }
       if (ora) nrows = max(nrows, ra + 1);
       if (orb) nrows = max(nrows, rb + 1);
@@ -237,6 +297,13 @@ bool launch_residual_dense_dct(cudaStream_t st, int log2, int kind, int n_blocks
     else k_dense4<false><<<grid, 256, 0, st>>>(coeffs, qp, dst, n_blocks);
     return true;
   }
+#ifndef DENSE8_SMEM
+  if (log2 == 3) {
+    long long ctas = ((long long)n_blocks + 127) / 128;
+    k_dense8<<<(int)min(ctas, (long long)sm_count * 32), 128, 0, st>>>(coeffs, qp, dst, n_blocks);
+    return true;
+  }
+#endif
   const int G = 32 >> log2;
   long long warps = ((long long)n_blocks + G - 1) / G;
   long long ctas = (warps + DENSE_WARPS - 1) / DENSE_WARPS;

@@ -160,22 +160,34 @@ __device__ __forceinline__ void idst4_packed(const uint32_t* P, int* out, int bi
 // Flat dequantisation (transform.cc:443-475, bit depth 8) as level*f + rnd >> sh with per-block constants:
 //   (level*ls*2^k + 2^(s-1)) >> s  ==  level*(ls << (k-s))                      for k >= s
 //                                  ==  (level*ls + 2^(s-1-k)) >> (s-k)          for k <  s      (s = log2-1)
+// The level is taken out of its packed word by the multiply itself: dp2a(word, {ls, 0}) = lo*ls, dp2a(word, {0, ls})
+// = hi*ls (ls <= 72 fits the signed byte), so no unpack instruction runs on the ALU pipe.
 struct DequantK {
-  int f, rnd, sh;
+  uint32_t sel_lo, sel_hi;   // dp2a selectors {ls, 0} / {0, ls}
+  int m, rnd, sh;            // (v*m + rnd) >> sh
 };
 __device__ __forceinline__ DequantK dequant_consts(int qp, int log2) {
   DequantK d;
   if (qp < 0) {  // coefficients are already dequantised
-    d.f = 1; d.rnd = 0; d.sh = 0;
+    d.sel_lo = 1; d.sel_hi = 1 << 8; d.m = 1; d.rnd = 0; d.sh = 0;
     return d;
   }
   const int k = (qp * 43) >> 8, rem = qp - 6 * k, s = log2 - 1;
-  const int ls = (int)((0x484039332D28ull >> (8 * rem)) & 0xff);   // {40,45,51,57,64,72}
-  d.f = ls << max(k - s, 0);
+  const uint32_t ls = (uint32_t)((0x484039332D28ull >> (8 * rem)) & 0xff);   // {40,45,51,57,64,72}
+  d.sel_lo = ls;
+  d.sel_hi = ls << 8;
+  d.m = 1 << max(k - s, 0);
   d.sh = max(s - k, 0);
   d.rnd = d.sh ? 1 << (d.sh - 1) : 0;
   return d;
 }
-__device__ __forceinline__ int dq(int level, const DequantK& d) { return (level * d.f + d.rnd) >> d.sh; }
-__device__ __forceinline__ int s16_lo(uint32_t w) { return (int)(int16_t)(w & 0xffff); }
-__device__ __forceinline__ int s16_hi(uint32_t w) { return (int)w >> 16; }
+__device__ __forceinline__ int dq_lo(uint32_t w, const DequantK& d) { return (dp2a(w, d.sel_lo, 0) * d.m + d.rnd) >> d.sh; }
+__device__ __forceinline__ int dq_hi(uint32_t w, const DequantK& d) { return (dp2a(w, d.sel_hi, 0) * d.m + d.rnd) >> d.sh; }
+// byte n of w, zero-extended, without touching the ALU pipe
+template <int n> __device__ __forceinline__ int byte_of(uint32_t w) { return (int)__dp4a(w, 1u << (8 * n), 0u); }
+// x >> s for a 32-bit x
+#ifdef DENSE_MULHI_SHIFT
+template <int s> __device__ __forceinline__ int sra(int x) { return __mulhi(x, 1 << (32 - s)); }
+#else
+template <int s> __device__ __forceinline__ int sra(int x) { return x >> s; }
+#endif
