@@ -185,9 +185,4 @@ __device__ __forceinline__ int dq_lo(uint32_t w, const DequantK& d) { return (dp
 __device__ __forceinline__ int dq_hi(uint32_t w, const DequantK& d) { return (dp2a(w, d.sel_hi, 0) * d.m + d.rnd) >> d.sh; }
 // byte n of w, zero-extended, without touching the ALU pipe
 template <int n> __device__ __forceinline__ int byte_of(uint32_t w) { return (int)__dp4a(w, 1u << (8 * n), 0u); }
-// x >> s for a 32-bit x
-#ifdef DENSE_MULHI_SHIFT
-template <int s> __device__ __forceinline__ int sra(int x) { return __mulhi(x, 1 << (32 - s)); }
-#else
-template <int s> __device__ __forceinline__ int sra(int x) { return x >> s; }
-#endif
+template <int s> __device__ __forceinline__ int sra(int x) { return x >> s; }   // (mulhi by 2^(32-s) measured: no gain)
