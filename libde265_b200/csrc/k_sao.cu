@@ -3,25 +3,15 @@
 // (:318-370): edge offset with picture/slice/tile boundary rules, band offset, pcm/bypass skip.
 // Quirk kept on purpose: the CTB's own slice address is looked up with COMPONENT coordinates through
 // a luma accessor (sao.cc:50-56), which only matters for chroma in multi-slice pictures.
-// One thread per aligned word of 4 horizontally adjacent samples, all four filtered at once with the byte-SIMD
-// instructions (compare masks, saturating add/sub, PRMT as a byte look-up table); neighbours come from up to
-// six more word loads that hit L1.  Words on the rim of a CTB whose neighbouring CTB belongs to another slice
+// One thread per aligned word of 4 horizontally adjacent samples x 8 rows, all four samples filtered at once (half2
+// compares, PRMT as a byte look-up table, 16-bit SIMD add+clip); neighbours come from up to six more word loads
+// that hit L1.  Words on the rim of a CTB whose neighbouring CTB belongs to another slice
 // or tile take the per-sample path with the reference's boundary rules.  Traffic 2P per picture (+ 18 B per CTB).
+#include <cuda_fp16.h>
 #include "transform.cuh"
 #include "kernels.h"
 
 __device__ __forceinline__ int sgn(int v) { return (v > 0) - (v < 0); }
-
-// bytes of `idx` (0..7 each) select bytes of the 8-entry table {lo, hi}
-__device__ __forceinline__ uint32_t lut8(uint32_t lo, uint32_t hi, uint32_t idx) {
-  const uint32_t sel = (idx & 0xf) | ((idx >> 4) & 0xf0) | ((idx >> 8) & 0xf00) | ((idx >> 12) & 0xf000);
-  return __byte_perm(lo, hi, sel);
-}
-// clip8(v + off) per byte, off signed
-__device__ __forceinline__ uint32_t add_offsets(uint32_t v, uint32_t off) {
-  const uint32_t pos = __vmaxs4(off, 0u), neg = __vmaxs4(__vneg4(off), 0u);
-  return __vsubus4(__vaddus4(v, pos), neg);
-}
 
 // the reference's per-sample edge-offset path (sao.cc:104-180) for one word; returns the filtered word
 __device__ __noinline__ uint32_t sao_edge_slow(const FrameDev& f, const b265_sao& s, const b265_slice& sl, int c, int x0, int y, int nvalid,
@@ -76,6 +66,145 @@ __device__ __noinline__ uint32_t sao_edge_slow(const FrameDev& f, const b265_sao
 
 #define SAO_ROWS 8   // rows per thread (divides every CTB size of every component)
 
+// ---- the per-word arithmetic.  sm_100 has no byte-SIMD ALU (vcmp4 / vadd4 / vaddus4 are emulated with 5-8
+// instructions each), so the edge category is computed on half2 lanes — 1024+b is the half 0x6400|b, one PRMT per two
+// samples — where [c > a] = sat(c - a) and [c >= a] = sat(c + 1 - a) are single HADD2.SAT instructions on the FMA
+// pipe, and the final clip8(c + offset) is one VIADDMNMX.S16x2.RELU per two samples. ----
+__device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+// samples 0,1 / 2,3 of a word as half2 (1024 + sample)
+__device__ __forceinline__ __half2 half_lo(uint32_t w) { return u2h(__byte_perm(w, 0x64646464u, 0x4140)); }
+__device__ __forceinline__ __half2 half_hi(uint32_t w) { return u2h(__byte_perm(w, 0x64646464u, 0x4342)); }
+// prmt with the full selector (__byte_perm masks the nibbles to 3 bits, which drops the sign-replication mode)
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+// clip8(sample + signed offset byte) for the four samples of a word
+__device__ __forceinline__ uint32_t add_offsets(uint32_t v, uint32_t off) {
+  // offsets sign-extended to 16 bit: selector nibble 8|k = byte k's sign replicated
+  const uint32_t r01 = __viaddmin_s16x2_relu(__byte_perm(v, 0, 0x4140), prmt(off, 0, 0x9180), 0x00ff00ffu);
+  const uint32_t r23 = __viaddmin_s16x2_relu(__byte_perm(v, 0, 0x4342), prmt(off, 0, 0xb3a2), 0x00ff00ffu);
+  return __byte_perm(r01, r23, 0x6420);
+}
+// edge offset of one word: c = centre samples, a / b = the two neighbours of every sample (sao.cc:168-175);
+// tab_lo/tab_hi = offsets indexed by edgeIdx + 2
+__device__ __forceinline__ uint32_t sao_edge_word(uint32_t c, uint32_t a, uint32_t b, uint32_t tab_lo, uint32_t tab_hi) {
+  const __half2 one = __floats2half2_rn(1.f, 1.f);
+  const __half2 wgt = __floats2half2_rn(1.f, 16.f), bias = __floats2half2_rn(1024.f, 1024.f);
+  uint32_t w[2];
+#pragma unroll
+  for (int h = 0; h < 2; h++) {
+    const __half2 ch = h ? half_hi(c) : half_lo(c), ah = h ? half_hi(a) : half_lo(a), bh = h ? half_hi(b) : half_lo(b);
+    const __half2 c1 = __hadd2(ch, one);
+    // edgeIdx + 2 = [c > a] + [c >= a] + [c > b] + [c >= b]
+    const __half2 t = __hadd2(__hsub2_sat(ch, ah), __hsub2_sat(c1, ah));
+    const __half2 u = __hadd2(__hsub2_sat(ch, bh), __hsub2_sat(c1, bh));
+    w[h] = h2u(__hfma2(__hadd2(t, u), wgt, bias));   // lanes {1024 + idx, 1024 + 16*idx}: the low bytes are idx, 16*idx
+  }
+  const uint32_t g = __byte_perm(w[0], w[1], 0x6240);   // {idx0, idx2, 16*idx1, 16*idx3}
+  const uint32_t sel = g | (g >> 16);                    // PRMT selector nibbles idx0..idx3 (upper bits are ignored)
+  return add_offsets(c, __byte_perm(tab_lo, tab_hi, sel));
+}
+// band offset of one word (sao.cc:182-251): kb = ((v >> 3) - band_position) & 31, offset[kb] for kb < 4
+__device__ __forceinline__ uint32_t sao_band_word(uint32_t c, uint32_t negpos4, uint32_t o4) {
+  const uint32_t kb = (((c >> 3) & 0x1f1f1f1fu) + negpos4) & 0x1f1f1f1fu;
+  const uint32_t ge4 = ((kb + 0x7c7c7c7cu) & 0x80808080u) >> 5;           // 4 where kb >= 4
+  const uint32_t idx = (kb & 0x03030303u) | ge4;                          // 0..3 -> offsets, 4..7 -> 0
+  const uint32_t n = (idx | (idx >> 4)) & 0x00ff00ffu;                    // nibble pairs in bytes 0 and 2
+  return add_offsets(c, __byte_perm(o4, 0u, __byte_perm(n, 0, 0x4420)));
+}
+
+struct SaoEdgeArgs {
+  const FrameDev* f; const b265_sao* s; const b265_slice* sl;
+  const uint8_t* in; uint8_t* out;
+  int pitch, c, x0, y0, H, rows, cy0, ch_;
+  uint32_t keep_x, tab_lo, tab_hi, nf[4];
+  bool has_l, has_r, any_nf, foreign, rim_lr;
+};
+// Threads of a CTB that has a neighbour CTB in another slice or tile (rare: multi-slice / tile pictures): plain row
+// loop, rim rows / rim words sample by sample with the reference's boundary rules, the others like the fast path.
+__device__ __noinline__ void sao_edge_rows_foreign(const SaoEdgeArgs& e, int cls) {
+  const int pitch = e.pitch, sh = e.c ? 1 : 0;
+  const int W = e.c ? e.f->cw : e.f->width;
+  for (int r = 0; r < e.rows; r++) {
+    const int y = e.y0 + r, cy = e.cy0 + r;
+    const uint8_t* p = e.in + (ptrdiff_t)r * pitch;
+    const uint32_t cc = *reinterpret_cast<const uint32_t*>(p);
+    uint32_t nofilt = e.any_nf ? (sh ? e.nf[r >> 1] : e.nf[r >> 2]) : 0u;
+    uint32_t res;
+    if (e.rim_lr || cy == 0 || cy == e.ch_ - 1) {
+      res = sao_edge_slow(*e.f, *e.s, *e.sl, e.c, e.x0, y, 4, cc, nofilt);
+      nofilt = 0;
+    } else {
+      // interior of the CTB: all neighbours exist (the word is not on the picture edge either)
+      auto word_at = [&](int dx, int dy) {   // the four samples at (x0 + dx .. x0 + dx + 3, y + dy), |dx| <= 1
+        const uint8_t* q = p + (ptrdiff_t)dy * pitch;
+        const uint32_t m = *reinterpret_cast<const uint32_t*>(q);
+        if (dx < 0) return __funnelshift_r(e.x0 > 0 ? *reinterpret_cast<const uint32_t*>(q - 4) : 0u, m, 24);
+        if (dx > 0) return __funnelshift_r(m, e.x0 + 4 < W ? *reinterpret_cast<const uint32_t*>(q + 4) : 0u, 8);
+        return m;
+      };
+      uint32_t a, b;
+      if (cls == 0) { a = word_at(-1, 0); b = word_at(1, 0); }
+      else if (cls == 1) { a = word_at(0, -1); b = word_at(0, 1); }
+      else if (cls == 2) { a = word_at(-1, -1); b = word_at(1, 1); }
+      else { a = word_at(1, -1); b = word_at(-1, 1); }
+      res = sao_edge_word(cc, a, b, e.tab_lo, e.tab_hi);
+    }
+    res = (res & ~nofilt) | (cc & nofilt);
+    *reinterpret_cast<uint32_t*>(e.out + (ptrdiff_t)r * pitch) = res;
+  }
+}
+
+// the thread's SAO_ROWS rows of one word with edge class CLS (0: horizontal, 1: vertical, 2: 135 deg, 3: 45 deg);
+// rolling window over the rows: previous / current / next (left, centre, right words)
+template <int CLS>
+__device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e) {
+  constexpr bool need_lr = CLS != 1, need_ud = CLS != 0, need_diag = CLS >= 2;
+  const int pitch = e.pitch;
+  const bool has_l = e.has_l, has_r = e.has_r;
+  uint32_t pl = 0, pc = 0, pr = 0, cl = 0, cc, cr = 0, nl = 0, nc = 0, nr = 0;
+  auto load_row3 = [&](const uint8_t* p, uint32_t& l, uint32_t& m, uint32_t& rt, bool lr) {
+    m = __ldg(reinterpret_cast<const uint32_t*>(p));
+    if (lr) {
+      l = has_l ? __ldg(reinterpret_cast<const uint32_t*>(p - 4)) : 0u;
+      rt = has_r ? __ldg(reinterpret_cast<const uint32_t*>(p + 4)) : 0u;
+    }
+  };
+  const uint8_t* prow = e.in;
+  uint8_t* orow = e.out;
+  const int rows = e.rows;   // 4 or 8: plane heights are multiples of 4 (coded size is a multiple of the 8x8 minimum CB)
+  const bool top = e.y0 == 0, bot = e.y0 + rows == e.H;
+  if (need_ud && !top) load_row3(prow - pitch, pl, pc, pr, need_diag);
+  load_row3(prow, cl, cc, cr, need_lr);
+  const int sh = e.c ? 1 : 0;
+#pragma unroll
+  for (int r = 0; r < SAO_ROWS; r++) {
+    if (r == 4 && rows == 4) break;
+    const bool last = (r == SAO_ROWS - 1) || (r == 3 && rows == 4);
+    if (!last || (need_ud && !bot)) load_row3(prow + pitch, nl, nc, nr, need_lr);
+    uint32_t nofilt = e.any_nf ? (sh ? e.nf[r >> 1] : e.nf[r >> 2]) : 0u;
+    uint32_t a, b;
+    if (CLS == 0) {
+      a = __funnelshift_r(cl, cc, 24);   // sample x-1
+      b = __funnelshift_r(cc, cr, 8);    // sample x+1
+    } else if (CLS == 1) { a = pc; b = nc; }
+    else if (CLS == 2) { a = __funnelshift_r(pl, pc, 24); b = __funnelshift_r(nc, nr, 8); }
+    else { a = __funnelshift_r(pc, pr, 8); b = __funnelshift_r(nl, nc, 24); }
+    uint32_t res = sao_edge_word(cc, a, b, e.tab_lo, e.tab_hi);
+    nofilt |= e.keep_x;
+    if (CLS != 0 && ((r == 0 && top) || (last && bot))) nofilt = 0xffffffffu;   // no row above / below
+    res = (res & ~nofilt) | (cc & nofilt);
+    *reinterpret_cast<uint32_t*>(orow) = res;
+    pl = cl; pc = cc; pr = cr;
+    cl = nl; cc = nc; cr = nr;
+    prow += pitch;
+    orow += pitch;
+  }
+}
+
 __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.z / 3];
   const uint32_t fflags = f.flags;
@@ -104,9 +233,9 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
   const b265_sao& s = sao[ctb];
   int type = s.type[c];
   if (!(c ? sl.sao_chroma : sl.sao_luma)) type = 0;
-  const int nvalid = min(4, W - x0);
+  // plane widths and heights are multiples of 4 (the coded size is a multiple of the 8x8 minimum coding block), so
+  // every word is complete and a thread has 4 or 8 rows
   const int rows = min(SAO_ROWS, H - y0);
-  // rows are padded to the pitch (a multiple of 4), so whole words can be read and written
   if (type == 0) {
     uint32_t v[SAO_ROWS];
 #pragma unroll
@@ -115,11 +244,49 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
     for (int r = 0; r < SAO_ROWS; r++) if (r < rows) *reinterpret_cast<uint32_t*>(out + (size_t)r * pitch) = v[r];
     return;
   }
-  const uint8_t* unit_info = f.unit_info;
-  const int upitch = f.width >> 2;
   const uint32_t o4 = (uint32_t)(uint8_t)s.offset[c][0] | ((uint32_t)(uint8_t)s.offset[c][1] << 8) |
                       ((uint32_t)(uint8_t)s.offset[c][2] << 16) | ((uint32_t)(uint8_t)s.offset[c][3] << 24);
   const int cls = s.band_eo[c];   // band position (type 1) or edge class (type 2)
+  // pcm (with pcm_loop_filter_disabled) / transquant-bypass samples are not filtered (sao.cc:112-117): the unit flags
+  // under this thread's samples, fetched once.  nf[q] covers rows [q*SAO_ROWS/4, (q+1)*SAO_ROWS/4) for chroma (one luma
+  // unit row = 2 chroma rows) and rows [4*(q&1), ..) for luma (nf[0], nf[1]).
+  uint32_t nf[4] = {0, 0, 0, 0};
+  bool any_nf = false;
+  if (const uint8_t* unit_info = f.unit_info) {
+    const int upitch = f.width >> 2;
+    if (!sh) {
+      const uint8_t* ui = unit_info + (size_t)(y0 >> 2) * upitch + (x0 >> 2);
+      nf[0] = (__ldg(ui) & B265_UNIT_NOFILT) ? 0xffffffffu : 0u;
+      if (rows > 4) nf[1] = (__ldg(ui + upitch) & B265_UNIT_NOFILT) ? 0xffffffffu : 0u;
+    } else {
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        if (2 * q < rows) {
+          const uint8_t* ui = unit_info + (size_t)((y0 >> 1) + q) * upitch + (x0 >> 1);
+          nf[q] = ((__ldg(ui) & B265_UNIT_NOFILT) ? 0x0000ffffu : 0u) |
+                  ((__ldg(ui + 1) & B265_UNIT_NOFILT) ? 0xffff0000u : 0u);
+        }
+      }
+    }
+    any_nf = (nf[0] | nf[1] | nf[2] | nf[3]) != 0;
+  }
+  if (type == 1) {
+    const uint32_t negpos4 = 0x01010101u * (uint32_t)((32 - cls) & 31);
+    uint32_t v[SAO_ROWS];
+#pragma unroll
+    for (int r = 0; r < SAO_ROWS; r++) if (r < rows) v[r] = __ldg(reinterpret_cast<const uint32_t*>(in + (size_t)r * pitch));
+#pragma unroll
+    for (int r = 0; r < SAO_ROWS; r++) {
+      if (r >= rows) break;
+      uint32_t res = sao_band_word(v[r], negpos4, o4);
+      if (any_nf) {
+        const uint32_t m = sh ? nf[r >> 1] : nf[r >> 2];
+        res = (res & ~m) | (v[r] & m);
+      }
+      *reinterpret_cast<uint32_t*>(out + (size_t)r * pitch) = res;
+    }
+    return;
+  }
   const int cx = x0 - (xCtb << lc), cy0 = y0 - (yCtb << lc);
   const int cw_ = min(1 << lc, W - (xCtb << lc)), ch_ = min(1 << lc, H - (yCtb << lc));
   // Edge offset next to a CTB of another slice or tile follows the reference's boundary rules sample by sample.
@@ -127,7 +294,7 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
   // sao.cc:50-56) differs in slice or tile; only words on the CTB rim can be affected.
   bool foreign = false;
   const bool rim_lr = cx == 0 || cx + 4 >= cw_;
-  if (type == 2 && ctbs && (rim_lr || cy0 == 0 || cy0 + SAO_ROWS >= ch_)) {
+  if (ctbs && (rim_lr || cy0 == 0 || cy0 + SAO_ROWS >= ch_)) {
     const int ctbs_h = f.ctbs_h;
     for (int dy = -1; dy <= 1; dy++)
       for (int dx = -1; dx <= 1; dx++) {
@@ -141,79 +308,28 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
       foreign |= ctbs[qy * ctbs_w + qx].slice != me.slice;
     }
   }
-  const uint32_t one = 0x01010101u;
   const uint32_t tab_lo = (o4 & 0xffffu) | ((o4 & 0x00ff0000u) << 8);   // edgeIdx + 2 -> {o0, o1, 0, o2 | o3}
   const uint32_t tab_hi = o4 >> 24;
   uint32_t keep_x = 0;   // bytes whose horizontal neighbour lies outside the picture stay unfiltered
-  if (type == 2 && cls != 1) {
+  if (cls != 1) {
     if (x0 == 0) keep_x |= 0x000000ffu;
-    if (x0 + nvalid >= W) keep_x |= 0xffu << (8 * (nvalid - 1));
+    if (x0 + 4 >= W) keep_x |= 0xff000000u;
   }
-  const bool has_l = x0 > 0, has_r = x0 + 4 < W;
-  const bool need_lr = type == 2 && cls != 1, need_ud = type == 2 && cls != 0, need_diag = type == 2 && cls >= 2;
-  // rolling window over the rows: previous / current / next (left, centre, right words)
-  uint32_t pl = 0, pc = 0, pr = 0, cl = 0, cc, cr = 0, nl = 0, nc = 0, nr = 0;
-  auto load_row3 = [&](int r, uint32_t& l, uint32_t& m, uint32_t& rt, bool lr) {
-    const uint8_t* p = in + (ptrdiff_t)r * pitch;
-    m = __ldg(reinterpret_cast<const uint32_t*>(p));
-    if (lr) {
-      l = has_l ? __ldg(reinterpret_cast<const uint32_t*>(p - 4)) : 0u;
-      rt = has_r ? __ldg(reinterpret_cast<const uint32_t*>(p + 4)) : 0u;
-    }
-  };
-  if (need_ud && y0 > 0) load_row3(-1, pl, pc, pr, need_diag);
-  load_row3(0, cl, cc, cr, need_lr);
+  SaoEdgeArgs e;
+  e.f = &f; e.s = &s; e.sl = &sl; e.in = in; e.out = out; e.pitch = pitch; e.c = c; e.x0 = x0; e.y0 = y0; e.H = H;
+  e.rows = rows; e.has_l = x0 > 0; e.has_r = x0 + 4 < W; e.keep_x = keep_x; e.tab_lo = tab_lo;
+  e.tab_hi = tab_hi; e.any_nf = any_nf; e.foreign = foreign; e.rim_lr = rim_lr; e.cy0 = cy0; e.ch_ = ch_;
 #pragma unroll
-  for (int r = 0; r < SAO_ROWS; r++) {
-    if (r >= rows) break;
-    const int y = y0 + r;
-    const bool has_dn = y + 1 < H;
-    if (r + 1 < SAO_ROWS || need_ud) {
-      if ((r + 1 < rows) || (need_ud && has_dn)) load_row3(r + 1, nl, nc, nr, need_lr);
-    }
-    uint32_t nofilt = 0;
-    if (unit_info) {   // pcm (with pcm_loop_filter_disabled) / transquant-bypass samples are not filtered (sao.cc:112-117)
-      const uint8_t* ui = unit_info + ((y << sh) >> 2) * upitch + ((x0 << sh) >> 2);
-      if (!sh) nofilt = (ui[0] & B265_UNIT_NOFILT) ? 0xffffffffu : 0u;
-      else nofilt = ((ui[0] & B265_UNIT_NOFILT) ? 0x0000ffffu : 0u) | ((nvalid > 2 && (ui[1] & B265_UNIT_NOFILT)) ? 0xffff0000u : 0u);
-    }
-    uint32_t res;
-    if (type == 1) {
-      // band offset: kb = ((v >> 3) - band_position) & 31, offset[kb] for kb < 4
-      const uint32_t kb = __vsub4((cc >> 3) & 0x1f1f1f1fu, one * cls) & 0x1f1f1f1fu;
-      res = add_offsets(cc, lut8(o4, 0u, __vminu4(kb, 0x04040404u)));
-    } else {
-      const int cy = cy0 + r;
-      if (foreign && (rim_lr || cy == 0 || cy == ch_ - 1)) {
-        res = sao_edge_slow(f, s, sl, c, x0, y, nvalid, cc, nofilt);
-        nofilt = 0;
-      } else {
-        uint32_t a, b, keep = keep_x;
-        if (cls == 0) {
-          a = __funnelshift_r(cl, cc, 24);   // sample x-1
-          b = __funnelshift_r(cc, cr, 8);    // sample x+1
-        } else {
-          if (y == 0 || !has_dn) keep = 0xffffffffu;
-          if (cls == 1) { a = pc; b = nc; }
-          else if (cls == 2) { a = __funnelshift_r(pl, pc, 24); b = __funnelshift_r(nc, nr, 8); }
-          else { a = __funnelshift_r(pc, pr, 8); b = __funnelshift_r(nl, nc, 24); }
-        }
-        // edgeIdx = sign(c-a) + sign(c-b)
-        uint32_t idx = 0x02020202u;
-        idx = __vadd4(idx, __vcmpgtu4(cc, a) & one);
-        idx = __vsub4(idx, __vcmpltu4(cc, a) & one);
-        idx = __vadd4(idx, __vcmpgtu4(cc, b) & one);
-        idx = __vsub4(idx, __vcmpltu4(cc, b) & one);
-        res = add_offsets(cc, lut8(tab_lo, tab_hi, idx));
-        nofilt |= keep;
-      }
-    }
-    res = (res & ~nofilt) | (cc & nofilt);
-    uint8_t* o = out + (size_t)r * pitch;
-    if (nvalid == 4) *reinterpret_cast<uint32_t*>(o) = res;
-    else for (int k = 0; k < nvalid; k++) o[k] = (res >> (8 * k)) & 0xff;
-    pl = cl; pc = cc; pr = cr;
-    cl = nl; cc = nc; cr = nr;
+  for (int q = 0; q < 4; q++) e.nf[q] = nf[q];
+  if (foreign) {
+    sao_edge_rows_foreign(e, cls);
+    return;
+  }
+  switch (cls) {
+    case 0: sao_edge_rows<0>(e); break;
+    case 1: sao_edge_rows<1>(e); break;
+    case 2: sao_edge_rows<2>(e); break;
+    default: sao_edge_rows<3>(e); break;
   }
 }
 
