@@ -158,48 +158,42 @@ __device__ __noinline__ void sao_edge_rows_foreign(const SaoEdgeArgs& e, int cls
   }
 }
 
-// the thread's SAO_ROWS rows of one word with edge class CLS (0: horizontal, 1: vertical, 2: 135 deg, 3: 45 deg);
-// rolling window over the rows: previous / current / next (left, centre, right words)
-template <int CLS>
-__device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e) {
-  constexpr bool need_lr = CLS != 1, need_ud = CLS != 0, need_diag = CLS >= 2;
+// The thread's SAO_ROWS rows of one word, edge class as DATA (0: horizontal, 1: vertical, 2: 135 deg, 3: 45 deg): the
+// lanes of a warp may belong to CTBs with different classes (chroma CTBs are 16 samples wide), and a class-specialised
+// walker would run once per class present in the warp.  Neighbour a of the word's samples is at (dx, dy), neighbour b at
+// (-dx, -dy); each neighbour word is funnel-shifted out of the two aligned words that hold it (both hit L1).
+__device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e, int cls) {
   const int pitch = e.pitch;
-  const bool has_l = e.has_l, has_r = e.has_r;
-  uint32_t pl = 0, pc = 0, pr = 0, cl = 0, cc, cr = 0, nl = 0, nc = 0, nr = 0;
-  auto load_row3 = [&](const uint8_t* p, uint32_t& l, uint32_t& m, uint32_t& rt, bool lr) {
-    m = __ldg(reinterpret_cast<const uint32_t*>(p));
-    if (lr) {
-      l = has_l ? __ldg(reinterpret_cast<const uint32_t*>(p - 4)) : 0u;
-      rt = has_r ? __ldg(reinterpret_cast<const uint32_t*>(p + 4)) : 0u;
-    }
-  };
-  const uint8_t* prow = e.in;
-  uint8_t* orow = e.out;
+  const int dx = (cls == 1) ? 0 : (cls == 3) ? 1 : -1, dy = (cls == 0) ? 0 : -1;
+  // words holding neighbour a: lo at byte offset a_lo, hi at a_hi (relative to the centre word), shifted right by a_sh
+  // bits; words outside the picture are never dereferenced (their samples are masked by keep_x)
+  const int l4 = e.has_l ? -4 : 0, r4 = e.has_r ? 4 : 0;
+  const int a_lo = dx < 0 ? l4 : 0, a_hi = dx > 0 ? r4 : 0, a_sh = dx < 0 ? 24 : dx > 0 ? 8 : 0;
+  const int b_lo = dx > 0 ? l4 : 0, b_hi = dx < 0 ? r4 : 0, b_sh = dx > 0 ? 24 : dx < 0 ? 8 : 0;
   const int rows = e.rows;   // 4 or 8: plane heights are multiples of 4 (coded size is a multiple of the 8x8 minimum CB)
   const bool top = e.y0 == 0, bot = e.y0 + rows == e.H;
-  if (need_ud && !top) load_row3(prow - pitch, pl, pc, pr, need_diag);
-  load_row3(prow, cl, cc, cr, need_lr);
+  const int up = dy * pitch;   // 0 or -pitch
+  const uint8_t* prow = e.in;
+  uint8_t* orow = e.out;
   const int sh = e.c ? 1 : 0;
+  auto ldw = [](const uint8_t* p) { return __ldg(reinterpret_cast<const uint32_t*>(p)); };
 #pragma unroll
   for (int r = 0; r < SAO_ROWS; r++) {
     if (r == 4 && rows == 4) break;
     const bool last = (r == SAO_ROWS - 1) || (r == 3 && rows == 4);
-    if (!last || (need_ud && !bot)) load_row3(prow + pitch, nl, nc, nr, need_lr);
+    // rows above / below the picture are not read: the whole row stays unfiltered then
+    const bool edge_row = dy != 0 && ((r == 0 && top) || (last && bot));
+    const uint8_t* pa = prow + ((r == 0 && top) ? 0 : up);
+    const uint8_t* pb = prow - ((last && bot) ? 0 : up);
+    const uint32_t cc = ldw(prow);
+    const uint32_t a = __funnelshift_r(ldw(pa + a_lo), ldw(pa + a_hi), a_sh);
+    const uint32_t b = __funnelshift_r(ldw(pb + b_lo), ldw(pb + b_hi), b_sh);
     uint32_t nofilt = e.any_nf ? (sh ? e.nf[r >> 1] : e.nf[r >> 2]) : 0u;
-    uint32_t a, b;
-    if (CLS == 0) {
-      a = __funnelshift_r(cl, cc, 24);   // sample x-1
-      b = __funnelshift_r(cc, cr, 8);    // sample x+1
-    } else if (CLS == 1) { a = pc; b = nc; }
-    else if (CLS == 2) { a = __funnelshift_r(pl, pc, 24); b = __funnelshift_r(nc, nr, 8); }
-    else { a = __funnelshift_r(pc, pr, 8); b = __funnelshift_r(nl, nc, 24); }
     uint32_t res = sao_edge_word(cc, a, b, e.tab_lo, e.tab_hi);
     nofilt |= e.keep_x;
-    if (CLS != 0 && ((r == 0 && top) || (last && bot))) nofilt = 0xffffffffu;   // no row above / below
+    if ((r == 0 || r == 3 || r == SAO_ROWS - 1) && edge_row) nofilt = 0xffffffffu;
     res = (res & ~nofilt) | (cc & nofilt);
     *reinterpret_cast<uint32_t*>(orow) = res;
-    pl = cl; pc = cc; pr = cr;
-    cl = nl; cc = nc; cr = nr;
     prow += pitch;
     orow += pitch;
   }
@@ -210,15 +204,28 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
   const uint32_t fflags = f.flags;
   const b265_sao* sao = f.sao;
   if (!(fflags & B265_FRAME_SAO) || !sao) return;
-  const int c = blockIdx.z % 3;
   const int fcw = f.cw;
-  if (c && !fcw) return;
+  const int cz = blockIdx.z % 3;
+  if (cz && !fcw) return;
+  // A block covers 128 x 64 samples of a plane with 8 warps.  Luma: each warp a 32 x 32 region (8 words x 4 row groups),
+  // so the lanes of a warp share one CTB's parameters wherever the CTB is at least 32 samples wide (no divergence on
+  // type / class).  Chroma: Cb and Cr share the SAO type and edge class (one syntax element, slice.cc:2735-2760), so a
+  // warp takes the SAME 32 x 16 region in both planes (lanes 0-15 Cb, 16-31 Cr); the blocks of grid plane z=1 cover the
+  // even 32-row bands, z=2 the odd ones.
+  const int wrp = threadIdx.y, lane = threadIdx.x;
+  int c, xw, yrow;
+  if (cz == 0) {
+    c = 0;
+    xw = (wrp & 3) * 8 + (lane & 7);
+    yrow = (blockIdx.y * 8 + (wrp >> 2) * 4 + (lane >> 3)) * SAO_ROWS;
+  } else {
+    c = 1 + (lane >> 4);
+    xw = (wrp & 3) * 8 + (lane & 7);
+    yrow = ((blockIdx.y * 2 + (cz - 1)) * 4 + (wrp >> 2) * 2 + ((lane >> 3) & 1)) * SAO_ROWS;
+  }
   const int sh = c ? 1 : 0;
   const int W = c ? fcw : f.width, H = c ? f.ch : f.height;
-  // a block covers 128 x 64 samples; each warp a 32 x 32 region of it (8 words x 4 row groups), so that the lanes of
-  // a warp share one CTB's parameters wherever the CTB is at least 32 samples wide (no divergence on type / class)
-  const int xw = (threadIdx.y & 3) * 8 + (threadIdx.x & 7), rg = (threadIdx.y >> 2) * 4 + (threadIdx.x >> 3);
-  const int x0 = (blockIdx.x * 32 + xw) << 2, y0 = (blockIdx.y * 8 + rg) * SAO_ROWS;
+  const int x0 = (blockIdx.x * 32 + xw) << 2, y0 = yrow;
   if (x0 >= W || y0 >= H) return;
   const int pitch = f.pitch[c];
   const uint8_t* in = f.plane[c] + (size_t)y0 * pitch + x0;
@@ -325,12 +332,7 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
     sao_edge_rows_foreign(e, cls);
     return;
   }
-  switch (cls) {
-    case 0: sao_edge_rows<0>(e); break;
-    case 1: sao_edge_rows<1>(e); break;
-    case 2: sao_edge_rows<2>(e); break;
-    default: sao_edge_rows<3>(e); break;
-  }
+  sao_edge_rows(e, cls);
 }
 
 void launch_sao(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h) {
