@@ -17,6 +17,7 @@ struct Staged {
   uint8_t* base = nullptr;
   size_t extra_off = 0;
   FrameDev f = {};
+  std::vector<uint2> sao_rec;   // host copy of the SAO control records, alive until push_framedev has synchronised
 };
 
 int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_maps, Staged& S) {
@@ -30,6 +31,7 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   const size_t o_sl = off; off += al256(sizeof(b265_slice) * (size_t)(J.n_slices > 0 ? J.n_slices : 1));
   const size_t o_ctb = off; off += J.ctbs ? al256(sizeof(b265_ctb) * nctb) : 0;
   const size_t o_sao = off; off += J.sao ? al256(sizeof(b265_sao) * nctb) : 0;
+  const size_t o_srec = off; off += J.sao ? al256(sizeof(uint2) * 3 * nctb) : 0;
   const size_t o_ui = off; off += J.unit_info ? al256(n_units) : 0;
   const size_t o_qp = off; off += J.qp_y ? al256(n_qp) : 0;
   const size_t o_scal = off; off += J.scaling ? al256(sizeof(b265_scaling)) : 0;
@@ -52,6 +54,11 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   else CK(up(o_sl, &default_slice, sizeof(b265_slice)));
   CK(up(o_ctb, J.ctbs, sizeof(b265_ctb) * nctb));
   CK(up(o_sao, J.sao, sizeof(b265_sao) * nctb));
+  if (J.sao) {
+    S.sao_rec.resize(3 * nctb);
+    sao_records(J, cw_, ch_, true, S.sao_rec.data());
+    CK(up(o_srec, S.sao_rec.data(), sizeof(uint2) * 3 * nctb));
+  }
   CK(up(o_ui, J.unit_info, n_units));
   CK(up(o_qp, J.qp_y, n_qp));
   CK(up(o_scal, J.scaling, sizeof(b265_scaling)));
@@ -69,6 +76,7 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   f.slices = (const b265_slice*)(D + o_sl);
   f.ctbs = J.ctbs ? (const b265_ctb*)(D + o_ctb) : nullptr;
   f.sao = J.sao ? (const b265_sao*)(D + o_sao) : nullptr;
+  f.sao_rec = J.sao ? (const uint2*)(D + o_srec) : nullptr;
   f.unit_info = J.unit_info ? D + o_ui : nullptr;
   f.qp_y = J.qp_y ? (const int8_t*)(D + o_qp) : nullptr;
   f.scaling = J.scaling ? (const b265_scaling*)(D + o_scal) : nullptr;

@@ -69,6 +69,7 @@ struct FrameDev {
   const b265_slice* slices;
   const b265_ctb* ctbs;       // may be NULL
   const b265_sao* sao;        // may be NULL
+  const uint2* sao_rec;       // [3][ctbs_w*ctbs_h] per plane and CTB {ctl, 4 offset bytes}, built on the host (sao_records)
   const uint8_t* unit_info;   // may be NULL
   const int8_t* qp_y;         // may be NULL
   const b265_scaling* scaling;
@@ -88,6 +89,11 @@ struct FrameDev {
   int ref_poc[16];
   int n_refs;
 };
+
+// sao_rec ctl word: bits 0-1 SaoTypeIdx (0 when the slice switches SAO off for the component), bits 2-6 band position /
+// edge class, bit 7 = a CTB around this one belongs to another slice or tile (edge offset then follows the reference's
+// boundary rules sample by sample on the CTB rim, sao.cc:119-164)
+#define B265_SAOREC_FOREIGN 0x80
 
 // one ticket of the intra CTB wavefront: plane `plane` of CTB `ctb` (raster) of frame `frame`; the CTB's
 // TUs are tus[tu_first .. tu_first+tu_count) in decoding order (all planes interleaved)

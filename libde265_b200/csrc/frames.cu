@@ -157,7 +157,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   size_t done_total = 0;
   for (int j = 0; j < n_jobs; j++) done_total += done_init[j].size();
   const size_t o_done_init = P.take(done_total);
-  struct FOff { size_t tus, coeffs, pus, slices, ctbs, sao, unit, qp, scaling, pcms, pcm_samples; };
+  struct FOff { size_t tus, coeffs, pus, slices, ctbs, sao, sao_rec, unit, qp, scaling, pcms, pcm_samples; };
   std::vector<FOff> fo(n_jobs);
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
@@ -168,6 +168,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     fo[j].slices = P.take(sizeof(b265_slice) * (size_t)std::max(1, J.n_slices));
     fo[j].ctbs = J.ctbs ? P.take(sizeof(b265_ctb) * (size_t)nctb) : 0;
     fo[j].sao = J.sao ? P.take(sizeof(b265_sao) * (size_t)nctb) : 0;
+    fo[j].sao_rec = (J.sao && (J.flags & B265_FRAME_SAO)) ? P.take(sizeof(uint2) * 3 * (size_t)nctb) : 0;
     fo[j].unit = J.unit_info ? P.take((size_t)(J.width >> 2) * (J.height >> 2)) : 0;
     fo[j].qp = J.qp_y ? P.take((size_t)(J.width >> J.log2_min_cb) * (J.height >> J.log2_min_cb)) : 0;
     fo[j].scaling = J.scaling ? P.take(sizeof(b265_scaling)) : 0;
@@ -276,6 +277,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     else cp(fo[j].slices, &default_slice, sizeof(b265_slice));
     cp(fo[j].ctbs, J.ctbs, sizeof(b265_ctb) * (size_t)nctb);
     cp(fo[j].sao, J.sao, sizeof(b265_sao) * (size_t)nctb);
+    if (J.sao && (J.flags & B265_FRAME_SAO)) sao_records(J, nctb_w, nctb_h, false, reinterpret_cast<uint2*>(H + fo[j].sao_rec));
     cp(fo[j].unit, J.unit_info, (size_t)(J.width >> 2) * (J.height >> 2));
     cp(fo[j].qp, J.qp_y, (size_t)(J.width >> J.log2_min_cb) * (J.height >> J.log2_min_cb));
     cp(fo[j].scaling, J.scaling, sizeof(b265_scaling));
@@ -308,6 +310,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.slices = (const b265_slice*)(D + fo[j].slices);
     f.ctbs = J.ctbs ? (const b265_ctb*)(D + fo[j].ctbs) : nullptr;
     f.sao = J.sao ? (const b265_sao*)(D + fo[j].sao) : nullptr;
+    f.sao_rec = (J.sao && (J.flags & B265_FRAME_SAO)) ? (const uint2*)(D + fo[j].sao_rec) : nullptr;
     f.unit_info = J.unit_info ? D + fo[j].unit : nullptr;
     f.qp_y = J.qp_y ? (const int8_t*)(D + fo[j].qp) : nullptr;
     f.scaling = J.scaling ? (const b265_scaling*)(D + fo[j].scaling) : nullptr;

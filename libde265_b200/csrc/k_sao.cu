@@ -162,20 +162,19 @@ __device__ __noinline__ void sao_edge_rows_foreign(const SaoEdgeArgs& e, int cls
 // lanes of a warp may belong to CTBs with different classes (chroma CTBs are 16 samples wide), and a class-specialised
 // walker would run once per class present in the warp.  Neighbour a of the word's samples is at (dx, dy), neighbour b at
 // (-dx, -dy); each neighbour word is funnel-shifted out of the two aligned words that hold it (both hit L1).
-__device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e, int cls) {
-  const int pitch = e.pitch;
+__device__ __forceinline__ void sao_edge_rows(const uint8_t* in, uint8_t* out, int pitch, const uint32_t (&v)[SAO_ROWS], int cls,
+                                              int rows, int y0, int H, bool has_l, bool has_r, uint32_t keep_x,
+                                              uint32_t tab_lo, uint32_t tab_hi, bool any_nf, const uint32_t (&nf)[4], int sh) {
   const int dx = (cls == 1) ? 0 : (cls == 3) ? 1 : -1, dy = (cls == 0) ? 0 : -1;
   // words holding neighbour a: lo at byte offset a_lo, hi at a_hi (relative to the centre word), shifted right by a_sh
   // bits; words outside the picture are never dereferenced (their samples are masked by keep_x)
-  const int l4 = e.has_l ? -4 : 0, r4 = e.has_r ? 4 : 0;
+  const int l4 = has_l ? -4 : 0, r4 = has_r ? 4 : 0;
   const int a_lo = dx < 0 ? l4 : 0, a_hi = dx > 0 ? r4 : 0, a_sh = dx < 0 ? 24 : dx > 0 ? 8 : 0;
   const int b_lo = dx > 0 ? l4 : 0, b_hi = dx < 0 ? r4 : 0, b_sh = dx > 0 ? 24 : dx < 0 ? 8 : 0;
-  const int rows = e.rows;   // 4 or 8: plane heights are multiples of 4 (coded size is a multiple of the 8x8 minimum CB)
-  const bool top = e.y0 == 0, bot = e.y0 + rows == e.H;
+  const bool top = y0 == 0, bot = y0 + rows == H;   // rows is 4 or 8
   const int up = dy * pitch;   // 0 or -pitch
-  const uint8_t* prow = e.in;
-  uint8_t* orow = e.out;
-  const int sh = e.c ? 1 : 0;
+  const uint8_t* prow = in;
+  uint8_t* orow = out;
   auto ldw = [](const uint8_t* p) { return __ldg(reinterpret_cast<const uint32_t*>(p)); };
 #pragma unroll
   for (int r = 0; r < SAO_ROWS; r++) {
@@ -185,12 +184,12 @@ __device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e, int cls) {
     const bool edge_row = dy != 0 && ((r == 0 && top) || (last && bot));
     const uint8_t* pa = prow + ((r == 0 && top) ? 0 : up);
     const uint8_t* pb = prow - ((last && bot) ? 0 : up);
-    const uint32_t cc = ldw(prow);
+    const uint32_t cc = v[r];
     const uint32_t a = __funnelshift_r(ldw(pa + a_lo), ldw(pa + a_hi), a_sh);
     const uint32_t b = __funnelshift_r(ldw(pb + b_lo), ldw(pb + b_hi), b_sh);
-    uint32_t nofilt = e.any_nf ? (sh ? e.nf[r >> 1] : e.nf[r >> 2]) : 0u;
-    uint32_t res = sao_edge_word(cc, a, b, e.tab_lo, e.tab_hi);
-    nofilt |= e.keep_x;
+    uint32_t nofilt = any_nf ? (sh ? nf[r >> 1] : nf[r >> 2]) : 0u;
+    uint32_t res = sao_edge_word(cc, a, b, tab_lo, tab_hi);
+    nofilt |= keep_x;
     if ((r == 0 || r == 3 || r == SAO_ROWS - 1) && edge_row) nofilt = 0xffffffffu;
     res = (res & ~nofilt) | (cc & nofilt);
     *reinterpret_cast<uint32_t*>(orow) = res;
@@ -202,8 +201,7 @@ __device__ __forceinline__ void sao_edge_rows(const SaoEdgeArgs& e, int cls) {
 __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.z / 3];
   const uint32_t fflags = f.flags;
-  const b265_sao* sao = f.sao;
-  if (!(fflags & B265_FRAME_SAO) || !sao) return;
+  if (!(fflags & B265_FRAME_SAO) || !f.sao_rec) return;
   const int fcw = f.cw;
   const int cz = blockIdx.z % 3;
   if (cz && !fcw) return;
@@ -230,30 +228,26 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
   const int pitch = f.pitch[c];
   const uint8_t* in = f.plane[c] + (size_t)y0 * pitch + x0;
   uint8_t* out = f.out[c] + (size_t)y0 * pitch + x0;
+  // plane widths and heights are multiples of 4 (the coded size is a multiple of the 8x8 minimum coding block), so
+  // every word is complete and a thread has 4 or 8 rows
+  const int rows = min(SAO_ROWS, H - y0);
+  // the centre words do not depend on the CTB's parameters: request them before the parameter record
+  uint32_t v[SAO_ROWS];
+#pragma unroll
+  for (int r = 0; r < SAO_ROWS; r++) v[r] = (r < 4 || rows > 4) ? __ldg(reinterpret_cast<const uint32_t*>(in + (ptrdiff_t)r * pitch)) : 0u;
   const int lc = f.log2_ctb - sh;  // CTB size in this component
   const int xCtb = x0 >> lc, yCtb = y0 >> lc;
   const int ctbs_w = f.ctbs_w;
   const int ctb = yCtb * ctbs_w + xCtb;
-  const b265_ctb* ctbs = f.ctbs;
-  const b265_ctb me = ctbs ? ctbs[ctb] : b265_ctb{0, 0, 0};
-  const b265_slice& sl = f.slices[me.slice];
-  const b265_sao& s = sao[ctb];
-  int type = s.type[c];
-  if (!(c ? sl.sao_chroma : sl.sao_luma)) type = 0;
-  // plane widths and heights are multiples of 4 (the coded size is a multiple of the 8x8 minimum coding block), so
-  // every word is complete and a thread has 4 or 8 rows
-  const int rows = min(SAO_ROWS, H - y0);
+  const uint2 rec = __ldg(f.sao_rec + (size_t)c * (ctbs_w * f.ctbs_h) + ctb);
+  const int type = rec.x & 3;
   if (type == 0) {
-    uint32_t v[SAO_ROWS];
 #pragma unroll
-    for (int r = 0; r < SAO_ROWS; r++) if (r < rows) v[r] = __ldg(reinterpret_cast<const uint32_t*>(in + (size_t)r * pitch));
-#pragma unroll
-    for (int r = 0; r < SAO_ROWS; r++) if (r < rows) *reinterpret_cast<uint32_t*>(out + (size_t)r * pitch) = v[r];
+    for (int r = 0; r < SAO_ROWS; r++) if (r < 4 || rows > 4) *reinterpret_cast<uint32_t*>(out + (ptrdiff_t)r * pitch) = v[r];
     return;
   }
-  const uint32_t o4 = (uint32_t)(uint8_t)s.offset[c][0] | ((uint32_t)(uint8_t)s.offset[c][1] << 8) |
-                      ((uint32_t)(uint8_t)s.offset[c][2] << 16) | ((uint32_t)(uint8_t)s.offset[c][3] << 24);
-  const int cls = s.band_eo[c];   // band position (type 1) or edge class (type 2)
+  const uint32_t o4 = rec.y;
+  const int cls = (rec.x >> 2) & 31;   // band position (type 1) or edge class (type 2)
   // pcm (with pcm_loop_filter_disabled) / transquant-bypass samples are not filtered (sao.cc:112-117): the unit flags
   // under this thread's samples, fetched once.  nf[q] covers rows [q*SAO_ROWS/4, (q+1)*SAO_ROWS/4) for chroma (one luma
   // unit row = 2 chroma rows) and rows [4*(q&1), ..) for luma (nf[0], nf[1]).
@@ -279,42 +273,24 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
   }
   if (type == 1) {
     const uint32_t negpos4 = 0x01010101u * (uint32_t)((32 - cls) & 31);
-    uint32_t v[SAO_ROWS];
-#pragma unroll
-    for (int r = 0; r < SAO_ROWS; r++) if (r < rows) v[r] = __ldg(reinterpret_cast<const uint32_t*>(in + (size_t)r * pitch));
 #pragma unroll
     for (int r = 0; r < SAO_ROWS; r++) {
-      if (r >= rows) break;
+      if (r == 4 && rows == 4) break;
       uint32_t res = sao_band_word(v[r], negpos4, o4);
       if (any_nf) {
         const uint32_t m = sh ? nf[r >> 1] : nf[r >> 2];
         res = (res & ~m) | (v[r] & m);
       }
-      *reinterpret_cast<uint32_t*>(out + (size_t)r * pitch) = res;
+      *reinterpret_cast<uint32_t*>(out + (ptrdiff_t)r * pitch) = res;
     }
     return;
   }
   const int cx = x0 - (xCtb << lc), cy0 = y0 - (yCtb << lc);
   const int cw_ = min(1 << lc, W - (xCtb << lc)), ch_ = min(1 << lc, H - (yCtb << lc));
-  // Edge offset next to a CTB of another slice or tile follows the reference's boundary rules sample by sample.
-  // `foreign`: some CTB around this one (or, for chroma, the CTB the reference takes this one's slice from,
-  // sao.cc:50-56) differs in slice or tile; only words on the CTB rim can be affected.
-  bool foreign = false;
+  // Edge offset next to a CTB of another slice or tile follows the reference's boundary rules sample by sample
+  // (record flag, sao_records()); only words on the CTB rim can be affected.
   const bool rim_lr = cx == 0 || cx + 4 >= cw_;
-  if (ctbs && (rim_lr || cy0 == 0 || cy0 + SAO_ROWS >= ch_)) {
-    const int ctbs_h = f.ctbs_h;
-    for (int dy = -1; dy <= 1; dy++)
-      for (int dx = -1; dx <= 1; dx++) {
-        const int nx = xCtb + dx, ny = yCtb + dy;
-        if ((dx | dy) == 0 || nx < 0 || ny < 0 || nx >= ctbs_w || ny >= ctbs_h) continue;
-        const b265_ctb o = ctbs[ny * ctbs_w + nx];
-        foreign |= o.slice != me.slice || o.tile != me.tile;
-      }
-    if (sh) {
-      const int qx = (xCtb << lc) >> f.log2_ctb, qy = (yCtb << lc) >> f.log2_ctb;
-      foreign |= ctbs[qy * ctbs_w + qx].slice != me.slice;
-    }
-  }
+  const bool foreign = (rec.x & B265_SAOREC_FOREIGN) && (rim_lr || cy0 == 0 || cy0 + SAO_ROWS >= ch_);
   const uint32_t tab_lo = (o4 & 0xffffu) | ((o4 & 0x00ff0000u) << 8);   // edgeIdx + 2 -> {o0, o1, 0, o2 | o3}
   const uint32_t tab_hi = o4 >> 24;
   uint32_t keep_x = 0;   // bytes whose horizontal neighbour lies outside the picture stay unfiltered
@@ -322,17 +298,19 @@ __global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ fra
     if (x0 == 0) keep_x |= 0x000000ffu;
     if (x0 + 4 >= W) keep_x |= 0xff000000u;
   }
-  SaoEdgeArgs e;
-  e.f = &f; e.s = &s; e.sl = &sl; e.in = in; e.out = out; e.pitch = pitch; e.c = c; e.x0 = x0; e.y0 = y0; e.H = H;
-  e.rows = rows; e.has_l = x0 > 0; e.has_r = x0 + 4 < W; e.keep_x = keep_x; e.tab_lo = tab_lo;
-  e.tab_hi = tab_hi; e.any_nf = any_nf; e.foreign = foreign; e.rim_lr = rim_lr; e.cy0 = cy0; e.ch_ = ch_;
-#pragma unroll
-  for (int q = 0; q < 4; q++) e.nf[q] = nf[q];
   if (foreign) {
+    const b265_ctb* ctbs = f.ctbs;
+    SaoEdgeArgs e;
+    e.f = &f; e.s = &f.sao[ctb]; e.sl = &f.slices[ctbs ? ctbs[ctb].slice : 0];
+    e.in = in; e.out = out; e.pitch = pitch; e.c = c; e.x0 = x0; e.y0 = y0; e.H = H;
+    e.rows = rows; e.has_l = x0 > 0; e.has_r = x0 + 4 < W; e.keep_x = keep_x; e.tab_lo = tab_lo;
+    e.tab_hi = tab_hi; e.any_nf = any_nf; e.foreign = foreign; e.rim_lr = rim_lr; e.cy0 = cy0; e.ch_ = ch_;
+#pragma unroll
+    for (int q = 0; q < 4; q++) e.nf[q] = nf[q];
     sao_edge_rows_foreign(e, cls);
     return;
   }
-  sao_edge_rows(e, cls);
+  sao_edge_rows(in, out, pitch, v, cls, rows, y0, H, x0 > 0, x0 + 4 < W, keep_x, tab_lo, tab_hi, any_nf, nf, sh);
 }
 
 void launch_sao(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h) {

@@ -34,3 +34,36 @@ int launch_postfilters(b265_ctx* ctx, const FrameDev* d_frames, const FrameDev* 
 void launch_deblock(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h,
                     const uint32_t* mc_items, int n_mc, bool chroma);
 void launch_sao(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h);
+
+// Per-plane, per-CTB SAO control records for k_sao (host side, at batch build): resolves the slice's sao_luma / sao_chroma
+// switches, packs the offsets, and flags CTBs that touch another slice or tile.  out has 3 * ctbs_w * ctbs_h entries.
+inline void sao_records(const b265_frame_job& J, int ctbs_w, int ctbs_h, bool default_on, uint2* out) {
+  const int n = ctbs_w * ctbs_h;
+  for (int y = 0; y < ctbs_h; y++)
+    for (int x = 0; x < ctbs_w; x++) {
+      const int i = y * ctbs_w + x;
+      const b265_sao& s = J.sao[i];
+      const int my_slice = J.ctbs ? J.ctbs[i].slice : 0, my_tile = J.ctbs ? J.ctbs[i].tile : 0;
+      const b265_slice* sl = (J.n_slices > 0 && J.slices) ? &J.slices[my_slice] : nullptr;
+      bool foreign = false;
+      if (J.ctbs)
+        for (int dy = -1; dy <= 1; dy++)
+          for (int dx = -1; dx <= 1; dx++) {
+            const int nx = x + dx, ny = y + dy;
+            if ((dx | dy) == 0 || nx < 0 || ny < 0 || nx >= ctbs_w || ny >= ctbs_h) continue;
+            const b265_ctb& o = J.ctbs[ny * ctbs_w + nx];
+            foreign |= o.slice != my_slice || o.tile != my_tile;
+          }
+      for (int c = 0; c < 3; c++) {
+        int type = s.type[c];
+        const bool on = sl ? (c ? sl->sao_chroma : sl->sao_luma) != 0 : default_on;   // no slice list: the caller's default slice
+        if (!on) type = 0;
+        bool fgn = foreign;
+        // chroma: the reference looks this CTB's slice up with component coordinates (sao.cc:50-56)
+        if (c && J.ctbs) fgn |= J.ctbs[(y >> 1) * ctbs_w + (x >> 1)].slice != my_slice;
+        const uint32_t o4 = (uint32_t)(uint8_t)s.offset[c][0] | ((uint32_t)(uint8_t)s.offset[c][1] << 8) |
+                            ((uint32_t)(uint8_t)s.offset[c][2] << 16) | ((uint32_t)(uint8_t)s.offset[c][3] << 24);
+        out[c * n + i] = make_uint2((uint32_t)(type & 3) | ((uint32_t)(s.band_eo[c] & 31) << 2) | (fgn ? B265_SAOREC_FOREIGN : 0u), o4);
+      }
+    }
+}
