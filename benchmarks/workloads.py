@@ -22,7 +22,7 @@ REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 SWEEP = [("DST4", 1, 2), ("DCT4", 0, 2), ("DCT8", 0, 3), ("DCT16", 0, 4), ("DCT32", 0, 5)]
 STREAM_WL = {
     # name: (golden stream, deblocking patched on, loops of the stream per step, kernel batch, description)
-    "stream_4k": ("c4_2160p_q32", True, 8, 32, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
+    "stream_4k": ("c4_2160p_q32", True, 32, 32, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
                   "deblocking enabled by PPS re-write (SAO cannot be enabled in an enc265 stream)"),
     "stream_1080p": ("c1_1080p_q32", False, 16, 64, "1920x1080 8-bit 4:2:0 enc265 intra stream (16 unique frames, qp 32)"),
 }
@@ -383,7 +383,10 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) / a.steps),
                 "mpixel_per_s": e2e_fps * W * H / 1e6,
-                "host_parse_core_seconds_per_step": (s1["parse_s"] - s0["parse_s"]) / a.steps},
+                "host_parse_core_seconds_per_step": (s1["parse_s"] - s0["parse_s"]) / a.steps,
+                "recon_thread_seconds_per_step": (s1["gpu_s"] - s0["gpu_s"]) / a.steps,
+                "submit_seconds_per_step": (s1["submit_s"] - s0["submit_s"]) / a.steps,
+                "wall_seconds_per_step": e2e_s / a.steps},
         "gpu_launches": int(launches), "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": "k_intra_wavefront", "achieved": intra_gbs, "peak": peak, "unit": "GB/s",
                      "frac": intra_gbs / peak,

@@ -35,7 +35,6 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   const size_t o_ui = off; off += J.unit_info ? al256(n_units) : 0;
   const size_t o_qp = off; off += J.qp_y ? al256(n_qp) : 0;
   const size_t o_scal = off; off += J.scaling ? al256(sizeof(b265_scaling)) : 0;
-  const size_t o_bs = off; off += al256(((size_t)(J.width + 3) >> 2) * ((J.height + 3) >> 2));
   S.extra_off = off;
   off += extra;
   int r = devbuf_reserve(ctx, &ctx->d_stage, off, false);
@@ -62,7 +61,6 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   CK(up(o_ui, J.unit_info, n_units));
   CK(up(o_qp, J.qp_y, n_qp));
   CK(up(o_scal, J.scaling, sizeof(b265_scaling)));
-  CK(cudaMemsetAsync(D + o_bs, 0, al256(((size_t)(J.width + 3) >> 2) * ((J.height + 3) >> 2)), st));
   FrameDev& f = S.f;
   f.width = J.width; f.height = J.height;
   f.cw = J.chroma_format_idc ? (J.width + 1) >> 1 : 0;
@@ -80,7 +78,7 @@ int stage_meta(b265_ctx* ctx, const b265_frame_job& J, size_t extra, bool need_m
   f.unit_info = J.unit_info ? D + o_ui : nullptr;
   f.qp_y = J.qp_y ? (const int8_t*)(D + o_qp) : nullptr;
   f.scaling = J.scaling ? (const b265_scaling*)(D + o_scal) : nullptr;
-  f.bs = D + o_bs;
+  f.bs = nullptr;
   if (need_maps && (!f.unit_info || !f.qp_y)) return B265_ERR_INVALID_ARG;
   return B265_OK;
 }
@@ -173,7 +171,7 @@ int b265_deblock_planes(b265_ctx* ctx, int mem, const b265_frame_job* meta, uint
   r = push_framedev(ctx, S);
   if (r) return r;
   launch_deblock(ctx->stream, (const FrameDev*)S.base, 1, J.width, J.height, nullptr, 0, np == 3);
-  ctx->launches += 3 + (np == 3 ? 2 : 0);
+  ctx->launches += 2 + (np == 3 ? 2 : 0);
   CK_LAUNCH("deblock");
   if (mem == B265_MEM_HOST)
     for (int c = 0; c < np; c++)

@@ -25,7 +25,7 @@ struct b265_batch {
   uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
   IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
   unsigned* d_ticket = nullptr;
-  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // bs maps + border mailboxes, cleared per run
+  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // border mailboxes, cleared per run
   uint8_t* d_done_init = nullptr;     size_t done_bytes = 0;   // per CTB plane: 1 = no intra ticket (read-only)
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
   int max_wave = 0;
@@ -179,7 +179,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   // device-only scratch after the uploaded part
   const size_t o_ticket = P.take(256);
   const size_t o_zero = P.off;
-  struct SOff { size_t done[3], bs, tmp[3], motion, resid[3], tb_mask, mbox[3]; int dp[3]; };
+  struct SOff { size_t done[3], tmp[3], motion, resid[3], tb_mask, mbox[3]; int dp[3]; };
   std::vector<SOff> so(n_jobs);
   {
     size_t acc = 0;
@@ -194,7 +194,6 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
         const int S = (1 << J.log2_ctb) >> ((c && J.chroma_format_idc) ? 1 : 0);
         so[j].mbox[c] = (c == 0 || J.chroma_format_idc) ? P.take((size_t)cw_ * ch_ * 4 * S) : 0;
       }
-      so[j].bs = P.take((size_t)((J.width + 3) >> 2) * ((J.height + 3) >> 2));
     }
   }
   b->zero_bytes = P.off - o_zero;
@@ -321,7 +320,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.tb_mask = (uint64_t*)(D + so[j].tb_mask);
     b->max_tus = std::max(b->max_tus, J.n_tus);
     b->max_pcms = std::max(b->max_pcms, J.n_pcms);
-    f.bs = D + so[j].bs;
+    f.bs = nullptr;   // boundary strengths are derived inside the deblocking kernels
     f.motion = so[j].motion ? (uint32_t*)(D + so[j].motion) : nullptr;
     f.n_refs = std::min(J.n_refs, 16);
     for (int r = 0; r < f.n_refs; r++) {

@@ -1,4 +1,4 @@
-// k_deblock.cu — in-loop deblocking filter: boundary strength, luma and chroma edge filters.
+// k_deblock.cu — in-loop deblocking filter: boundary strength (derived inside the edge kernels), luma and chroma edge filters.
 //
 // Restates libde265/deblock.cc: derive_boundaryStrength (:241-375), edge_filtering_luma_internal
 // (:405-699), edge_filtering_chroma_internal (:730-871), tables :389-399.  The edge flags themselves
@@ -64,20 +64,6 @@ __device__ __forceinline__ int edge_bs(const FrameDev& f, int up, int uq, bool t
   return ((far4(p0, q0) || far4(p1, q1)) && (far4(p0, q1) || far4(p1, q0))) ? 1 : 0;
 }
 
-__global__ void k_boundary_strength(const FrameDev* __restrict__ frames) {
-  const FrameDev& f = frames[blockIdx.y];
-  if (!(f.flags & B265_FRAME_DEBLOCK) || !f.unit_info) return;
-  const int uw = f.width >> 2, uh = f.height >> 2;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= uw * uh) return;
-  const int ux = i % uw, uy = i / uw;
-  const uint8_t info = f.unit_info[i];
-  int bs = 0;
-  if (!(ux & 1) && ux > 0 && (info & B265_UNIT_EDGE_V)) bs |= edge_bs(f, i - 1, i, info & B265_UNIT_TU_EDGE_V);
-  if (!(uy & 1) && uy > 0 && (info & B265_UNIT_EDGE_H)) bs |= edge_bs(f, i - uw, i, info & B265_UNIT_TU_EDGE_H) << 2;
-  f.bs[uy * ((f.width + 3) >> 2) + ux] = (uint8_t)bs;
-}
-
 __device__ __forceinline__ int qp_at(const FrameDev& f, int x, int y) {
   return f.qp_y[(y >> f.log2_min_cb) * (f.width >> f.log2_min_cb) + (x >> f.log2_min_cb)];
 }
@@ -96,7 +82,12 @@ __global__ void k_deblock_luma(const FrameDev* __restrict__ frames) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ew * eh) return;
   const int ux = VERT ? 2 * (i % ew) : i % ew, uy = VERT ? i / ew : 2 * (i / ew);
-  const int bs = (f.bs[uy * ((f.width + 3) >> 2) + ux] >> (VERT ? 0 : 2)) & 3;
+  // boundary strength of this segment, derived here from the unit flags (no bS map round trip through memory)
+  if ((VERT ? ux : uy) == 0) return;
+  const int uq = uy * uw + ux;
+  const uint8_t info = f.unit_info[uq];
+  if (!(info & (VERT ? B265_UNIT_EDGE_V : B265_UNIT_EDGE_H))) return;
+  const int bs = edge_bs(f, VERT ? uq - 1 : uq - uw, uq, info & (VERT ? B265_UNIT_TU_EDGE_V : B265_UNIT_TU_EDGE_H));
   if (!bs) return;
   const int x = ux << 2, y = uy << 2, pitch = f.pitch[0];
   uint8_t* ptr = f.plane[0] + (size_t)y * pitch + x;
@@ -133,8 +124,8 @@ __global__ void k_deblock_luma(const FrameDev* __restrict__ frames) {
                   abs(p[3][0] - q[3][0]) < ((5 * tc + 1) >> 1);
   const bool strong = s0 && s3;
   const bool dEp = dp < ((beta + (beta >> 1)) >> 3), dEq = dq < ((beta + (beta >> 1)) >> 3);
-  const int up = VERT ? uy * uw + ux - 1 : (uy - 1) * uw + ux;
-  const bool filterP = !(f.unit_info[up] & B265_UNIT_NOFILT), filterQ = !(f.unit_info[uy * uw + ux] & B265_UNIT_NOFILT);
+  const int up = VERT ? uq - 1 : uq - uw;
+  const bool filterP = !(f.unit_info[up] & B265_UNIT_NOFILT), filterQ = !(info & B265_UNIT_NOFILT);
 #pragma unroll
   for (int k = 0; k < 4; k++) {
     const int p0 = p[k][0], p1 = p[k][1], p2 = p[k][2], p3 = p[k][3];
@@ -189,14 +180,17 @@ __global__ void k_deblock_chroma(const FrameDev* __restrict__ frames) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= ew * eh) return;
   const int ux = (VERT ? 4 : 2) * (i % ew), uy = (VERT ? 2 : 4) * (i / ew);
-  const int bs = (f.bs[uy * ((f.width + 3) >> 2) + ux] >> (VERT ? 0 : 2)) & 3;
-  if (bs < 2) return;
+  // chroma is filtered where bS == 2 only: a flagged edge with an intra unit on either side (deblock.cc:283-290)
+  if ((VERT ? ux : uy) == 0) return;
+  const int uq = uy * uw + ux, up = VERT ? uq - 1 : uq - uw;
+  const uint8_t iq = f.unit_info[uq], ip = f.unit_info[up];
+  if (!(iq & (VERT ? B265_UNIT_EDGE_V : B265_UNIT_EDGE_H)) || !((ip | iq) & B265_UNIT_INTRA)) return;
+  const int bs = 2;
   const int xl = ux << 2, yl = uy << 2;          // luma position
   const int xc = xl >> 1, yc = yl >> 1;          // chroma position
   const int qpi = (qp_at(f, xl, yl) + qp_at(f, VERT ? xl - 1 : xl, VERT ? yl : yl - 1) + 1) >> 1;
   const int tc_offset = slice_at(f, xl, yl).tc_offset;
-  const int up = VERT ? uy * uw + ux - 1 : (uy - 1) * uw + ux;
-  const bool filterP = !(f.unit_info[up] & B265_UNIT_NOFILT), filterQ = !(f.unit_info[uy * uw + ux] & B265_UNIT_NOFILT);
+  const bool filterP = !(ip & B265_UNIT_NOFILT), filterQ = !(iq & B265_UNIT_NOFILT);
   // rows/columns of the segment that lie inside the plane (picture sizes are multiples of 8 luma)
   for (int c = 1; c <= 2; c++) {
     const int qi = qpi + (c == 1 ? f.cb_qp_offset : f.cr_qp_offset);
@@ -222,8 +216,6 @@ void launch_deblock(cudaStream_t st, const FrameDev* d_frames, int n_frames, int
                     const uint32_t* mc_items, int n_mc, bool chroma) {
   const int uw = max_w >> 2, uh = max_h >> 2;
   if (n_mc > 0) k_motion_raster<<<(n_mc * 32 + 255) / 256, 256, 0, st>>>(d_frames, mc_items, n_mc);
-  dim3 g((uw * uh + 255) / 256, n_frames);
-  k_boundary_strength<<<g, 256, 0, st>>>(d_frames);
   dim3 gv((((uw + 1) >> 1) * uh + 127) / 128, n_frames), gh((uw * ((uh + 1) >> 1) + 127) / 128, n_frames);
   dim3 cv((((uw + 3) >> 2) * ((uh + 1) >> 1) + 127) / 128, n_frames), chh((((uw + 1) >> 1) * ((uh + 3) >> 2) + 127) / 128, n_frames);
   k_deblock_luma<true><<<gv, 128, 0, st>>>(d_frames);

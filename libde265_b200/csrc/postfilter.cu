@@ -1,5 +1,5 @@
 // postfilter.cu — host-side sequencing of the in-loop filters of a batch (S5: decctx.cc:757-766,
-// run_postprocessing_filters_sequential decctx.cc:1859): bS -> deblock V -> deblock H -> SAO.
+// run_postprocessing_filters_sequential decctx.cc:1859): deblock V -> deblock H -> SAO (boundary strengths are derived inside the edge kernels).
 #include <algorithm>
 #include "backend.h"
 #include "kernels.h"
@@ -20,7 +20,7 @@ int launch_postfilters(b265_ctx* ctx, const FrameDev* d_frames, const FrameDev* 
   }
   if (any_dbk) {
     launch_deblock(ctx->stream, d_frames, n, mw, mh, mc_items, n_mc, chroma);
-    ctx->launches += 3 + (chroma ? 2 : 0) + (n_mc > 0 ? 1 : 0);
+    ctx->launches += 2 + (chroma ? 2 : 0) + (n_mc > 0 ? 1 : 0);
     CK_LAUNCH("deblock");
   }
   if (ev) cudaEventRecord(ev, ctx->stream);
