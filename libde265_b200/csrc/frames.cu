@@ -23,6 +23,7 @@ struct b265_batch {
   uint32_t* d_mc_items = nullptr;     int n_mc = 0;
   uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};     // inter TUs (residual added in place)
   uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
+  int n_res_plain[4] = {0, 0, 0, 0}, n_ires_plain[4] = {0, 0, 0, 0};   // leading part of each list: plain DCT TUs (sizes 16, 32)
   IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
   unsigned* d_ticket = nullptr;
   uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // border mailboxes, cleared per run
@@ -143,7 +144,17 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   }
   b->n_tickets = (int)tickets.size();
   b->n_mc = (int)mc.size();
-  for (int s = 0; s < 4; s++) { b->n_res[s] = (int)res[s].size(); b->n_ires[s] = (int)ires[s].size(); }
+  // 16x16 / 32x32 lists: plain DCT TUs first (packed dp2a kernels), transform-skip / bypass TUs after them (generic kernel)
+  for (int s = 0; s < 4; s++) {
+    auto plain = [&](uint32_t o) { return !(jobs[o >> 24].tus[o & 0xffffff].flags & (B265_TU_SKIP | B265_TU_BYPASS)); };
+    b->n_res_plain[s] = b->n_ires_plain[s] = 0;
+    if (s >= 2) {
+      b->n_res_plain[s] = (int)(std::stable_partition(res[s].begin(), res[s].end(), plain) - res[s].begin());
+      b->n_ires_plain[s] = (int)(std::stable_partition(ires[s].begin(), ires[s].end(), plain) - ires[s].begin());
+    }
+    b->n_res[s] = (int)res[s].size();
+    b->n_ires[s] = (int)ires[s].size();
+  }
 
   // ---- layout ----
   Packer P;
@@ -357,18 +368,23 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
     CK_LAUNCH("k_mc");
   }
   if (tm) cudaEventRecord(ctx->stage_ev[1], st);
-  for (int s = 0; s < 4; s++)
-    if (b->n_res[s]) {
-      launch_residual_sparse(st, 2 + s, b->d_frames, b->d_res_order[s], b->n_res[s], ctx->sm_count);
-      ctx->launches++;
-      CK_LAUNCH("k_residual_sparse");
+  for (int pass = 0; pass < 2; pass++) {   // inter TUs in place, then intra TBs to the int16 scratch planes
+    const bool scratch = pass == 1;
+    for (int s = 0; s < 4; s++) {
+      const uint32_t* order = scratch ? b->d_ires_order[s] : b->d_res_order[s];
+      const int n = scratch ? b->n_ires[s] : b->n_res[s], n_plain = scratch ? b->n_ires_plain[s] : b->n_res_plain[s];
+      if (n_plain) {
+        launch_residual_sparse_fast(st, 2 + s, b->d_frames, order, n_plain, ctx->sm_count, scratch);
+        ctx->launches++;
+        CK_LAUNCH("k_residual_sparse_fast");
+      }
+      if (n > n_plain) {
+        launch_residual_sparse(st, 2 + s, b->d_frames, order + n_plain, n - n_plain, ctx->sm_count, scratch);
+        ctx->launches++;
+        CK_LAUNCH("k_residual_sparse");
+      }
     }
-  for (int s = 0; s < 4; s++)
-    if (b->n_ires[s]) {
-      launch_residual_sparse(st, 2 + s, b->d_frames, b->d_ires_order[s], b->n_ires[s], ctx->sm_count, true);
-      ctx->launches++;
-      CK_LAUNCH("k_residual_sparse(scratch)");
-    }
+  }
   if (b->n_tickets) {
     launch_intra_prep(st, b->d_frames, b->n_frames, b->max_tus);
     ctx->launches++;

@@ -316,3 +316,141 @@ bool launch_residual_dense_dct(cudaStream_t st, int log2, int kind, int n_blocks
   }
   return true;
 }
+
+// ------------------------------------------------------------------------------------------------------
+// Sparse work-list form of the same arithmetic for 16x16 and 32x32 transform blocks (frame path, S2 =
+// scale_coefficients, transform.cc:353-625): the non-zero levels {int16 level, uint16 pos} of a TU are dequantised
+// and scattered straight into the vertical-pair plane, then the two passes of k_dense run on it.  Only plain DCT
+// TUs come here (frames.cu puts transform-skip / bypass TUs and the 4x4 / 8x8 sizes on the generic kernel's list).
+// SCRATCH: residual rows go to the picture's int16 plane (intra TBs, added by the wavefront) clamped to +-1024,
+// stored transposed for the column-wise predicted modes 2..17; otherwise they are added to the prediction in place.
+// ------------------------------------------------------------------------------------------------------
+template <int LOG2, int L>
+__device__ __forceinline__ void sparse_rows(const uint32_t* blk, int sub, int (&out)[1 << LOG2]) {
+  constexpr int N = 1 << LOG2, GSW = DenseCfg<LOG2>::GSW;
+  uint32_t P[N / 2];
+  const uint4* row = reinterpret_cast<const uint4*>(blk + sub * GSW);
+#pragma unroll
+  for (int q = 0; q < N / 8; q++) {
+    uint4 w = row[q];
+    P[4 * q] = w.x; P[4 * q + 1] = w.y; P[4 * q + 2] = w.z; P[4 * q + 3] = w.w;
+  }
+  IdctP<N, L>::run(P, out, 2048);
+}
+
+template <int LOG2, bool SCRATCH>
+__global__ void __launch_bounds__(DENSE_WARPS * 32)
+k_residual_sparse_fast(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ order, int n) {
+  using Cfg = DenseCfg<LOG2>;
+  constexpr int N = Cfg::N, G = Cfg::G;
+  __shared__ __align__(16) uint32_t smem[DENSE_WARPS][Cfg::WARPW];
+  __shared__ uint8_t slot_lut[32];   // row -> int16 slot of the column pass' pair order
+  if (threadIdx.x < N) slot_lut[threadIdx.x] = (uint8_t)pair_slot(N, threadIdx.x);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int grp = lane / N, sub = lane % N;
+  uint32_t* blk = smem[warp] + grp * Cfg::BLKW;
+  const int slot = pair_slot(N, sub);
+  const int warps_total = gridDim.x * DENSE_WARPS;
+  for (int base = (blockIdx.x * DENSE_WARPS + warp) * G; base < n; base += warps_total * G) {
+    const int i = base + grp;
+    const bool active = i < n;
+    b265_tu tu = {};
+    const FrameDev* f = frames;
+    if (active) {
+      const uint32_t o = order[i];
+      f = frames + (o >> 24);
+      tu = f->tus[o & 0xffffff];
+    }
+    const int cidx = tu.cidx_log2 & 3;
+    __syncwarp();   // the previous iteration's row pass has read the result plane
+#pragma unroll
+    for (int q = 0; q < N / 8; q++) reinterpret_cast<uint4*>(blk)[sub * (N / 8) + q] = make_uint4(0, 0, 0, 0);
+    __syncwarp();
+    // ---- scatter + dequantise ----
+    int mx = -1, my = -1;
+    {
+      const b265_coeff* __restrict__ c = f->coeffs + tu.coeff_off;
+      const int ncoeff = active ? tu.ncoeff : 0;
+      const b265_scaling* sl = (f->flags & B265_FRAME_SCALING_LIST) ? f->scaling : nullptr;
+      const DequantK k = dequant_consts(tu.qp, LOG2);
+      const int mid = cidx + ((tu.flags & B265_TU_INTRA_CU) ? 0 : (N < 32 ? 3 : 1));
+      int16_t* plane = reinterpret_cast<int16_t*>(blk);
+      for (int e = sub; e < ncoeff; e += N) {
+        const b265_coeff kc = c[e];
+        const int x = kc.pos & (N - 1), y = kc.pos >> LOG2;
+        int v;
+        if (sl) v = dequant_list(kc.level, tu.qp, LOG2, (LOG2 == 4) ? sl->s16[mid][kc.pos] : sl->s32[mid][kc.pos]);
+        else v = clip16((kc.level * (int)k.sel_lo * k.m + k.rnd) >> k.sh);
+        const int s = slot_lut[y];
+        plane[((((s >> 1) * N) + x) << 1) | (s & 1)] = (int16_t)v;
+        mx = max(mx, x);
+        my = max(my, y);
+      }
+    }
+    const int nrows = __reduce_max_sync(B265_FULL_MASK, my + 1);
+    const int ncols = __reduce_max_sync(B265_FULL_MASK, mx + 1);
+    __syncwarp();
+    // ---- first pass down the columns ----
+    if (N >= 32 && nrows > 16) dense_cols<LOG2, (N >= 32 ? 32 : N)>(blk, sub, slot);
+    else if (nrows > 8) dense_cols<LOG2, 16>(blk, sub, slot);
+    else if (nrows > 4) dense_cols<LOG2, 8>(blk, sub, slot);
+    else dense_cols<LOG2, 4>(blk, sub, slot);
+    __syncwarp();
+    // ---- second pass along the rows ----
+    int out[N];
+    if (N >= 32 && ncols > 16) sparse_rows<LOG2, (N >= 32 ? 32 : N)>(blk, sub, out);
+    else if (ncols > 8) sparse_rows<LOG2, 16>(blk, sub, out);
+    else if (ncols > 4) sparse_rows<LOG2, 8>(blk, sub, out);
+    else sparse_rows<LOG2, 4>(blk, sub, out);
+    if (!active) continue;
+    const int pitch = f->pitch[cidx];
+    if (SCRATCH) {
+      int16_t* d = f->resid[cidx] + (size_t)tu.y * pitch + tu.x;
+      const bool transposed = tu.intra_mode >= 2 && tu.intra_mode < 18;
+      if (transposed) {
+#pragma unroll
+        for (int x = 0; x < N; x++) d[(size_t)x * pitch + sub] = (int16_t)min(max(out[x] >> 12, -1024), 1023);
+      } else {
+        uint4* dr = reinterpret_cast<uint4*>(d + (size_t)sub * pitch);
+#pragma unroll
+        for (int q = 0; q < N / 8; q++) {
+          uint32_t w[4];
+#pragma unroll
+          for (int j = 0; j < 4; j++) {
+            const uint32_t p2 = pack_sat16(out[8 * q + 2 * j] >> 12, out[8 * q + 2 * j + 1] >> 12);
+            w[j] = __vmaxs2(__vmins2(p2, 0x03ff03ffu), 0xfc00fc00u);
+          }
+          dr[q] = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+      }
+    } else {
+      uint8_t* drow = f->plane[cidx] + (size_t)(tu.y + sub) * pitch + tu.x;
+#pragma unroll
+      for (int q = 0; q < N / 16; q++) {
+        const uint4 pw = reinterpret_cast<const uint4*>(drow)[q];
+        reinterpret_cast<uint4*>(drow)[q] = make_uint4(add_pack4(out + 16 * q, pw.x), add_pack4(out + 16 * q + 4, pw.y),
+                                                       add_pack4(out + 16 * q + 8, pw.z), add_pack4(out + 16 * q + 12, pw.w));
+      }
+    }
+  }
+}
+
+// plain DCT TUs of 16x16 / 32x32; returns false for the other sizes (generic kernel)
+bool launch_residual_sparse_fast(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order, int n,
+                                 int sm_count, bool to_scratch) {
+  if (log2 < 4) return false;
+  if (n <= 0) return true;
+  const int G = 32 >> log2;
+  const int warps = (n + G - 1) / G, ctas = (warps + DENSE_WARPS - 1) / DENSE_WARPS;
+  const int grid = min(ctas, sm_count * 16);
+  dim3 b(DENSE_WARPS * 32);
+  if (log2 == 4) {
+    if (to_scratch) k_residual_sparse_fast<4, true><<<grid, b, 0, st>>>(frames, order, n);
+    else k_residual_sparse_fast<4, false><<<grid, b, 0, st>>>(frames, order, n);
+  } else {
+    if (to_scratch) k_residual_sparse_fast<5, true><<<grid, b, 0, st>>>(frames, order, n);
+    else k_residual_sparse_fast<5, false><<<grid, b, 0, st>>>(frames, order, n);
+  }
+  return true;
+}

@@ -13,6 +13,9 @@ bool launch_residual_dense_dct(cudaStream_t st, int log2, int kind, int n_blocks
 // wavefront) instead of adding them to the prediction already in the plane (inter TBs)
 void launch_residual_sparse(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order,
                             int n, int sm_count, bool to_scratch = false);
+// plain DCT TUs of 16x16 / 32x32 on the packed dp2a kernels (k_residual_dense.cu); false = size not covered
+bool launch_residual_sparse_fast(cudaStream_t st, int log2, const FrameDev* frames, const uint32_t* order, int n,
+                                 int sm_count, bool to_scratch);
 void launch_mc(cudaStream_t st, const FrameDev* frames, const uint32_t* items, int n, int sm_count);
 // PCM sample store (k_blocks.cu): grid (max_pcms, n_frames)
 void launch_pcm(cudaStream_t st, const FrameDev* frames, int n_frames, int max_pcms);
