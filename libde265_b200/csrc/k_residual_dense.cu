@@ -216,7 +216,7 @@ k_dense(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint
   for (long long base = (long long)(blockIdx.x * DENSE_WARPS + warp) * G; base < n_blocks; base += (long long)warps_total * G) {
     const long long i = base + grp;
     const bool active = i < n_blocks;
-    const long long ib = active ? i : 0;
+    const long long ib = active ? i : n_blocks - 1;   // idle groups of the last iteration redo the last block (no store)
     // prediction row `sub` (needed last, requested first)
     uint32_t pred[N / 4];
     uint8_t* drow = dst + ib * (N * N) + sub * N;
@@ -257,11 +257,17 @@ k_dense(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint
       uint32_t v[CH];
 #pragma unroll
       for (int h = 0; h < CH / 2; h++) {
-        const uint32_t a = active ? wa[r][h] : 0u, b = active ? wb[r][h] : 0u;
+        const uint32_t a = wa[r][h], b = wb[r][h];
         ora |= a; orb |= b;
-        if (a | b) ncols = max(ncols, t_c0[r] + 2 * h + 2);
         v[2 * h] = pack_sat16(dq_lo(a, k), dq_lo(b, k));
         v[2 * h + 1] = pack_sat16(dq_hi(a, k), dq_hi(b, k));
+      }
+      {  // column bound in steps of CH/2 columns (the pass variants are selected at 4 / 8 / 16)
+        uint32_t hi = 0;
+#pragma unroll
+        for (int h = CH / 4; h < CH / 2; h++) hi |= wa[r][h] | wb[r][h];
+        if (hi) ncols = max(ncols, t_c0[r] + CH);
+        else if (ora | orb) ncols = max(ncols, t_c0[r] + CH / 2);
       }
       if (ora) nrows = max(nrows, ra + 1);
       if (orb) nrows = max(nrows, rb + 1);
