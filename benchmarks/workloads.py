@@ -237,7 +237,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
     W, H, nuniq = gold["width"], gold["height"], gold["frames"]
     cores = host_cores()
-    threads = max(1, cores // world - 1)
+    threads = int(os.environ.get("B265_BENCH_THREADS", 0)) or max(1, cores // world - 1)   # override: developer sweeps
 
     # ---------------- kernels with work lists resident in HBM ----------------
     ctx = L.Context(local)

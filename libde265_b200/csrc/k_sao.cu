@@ -198,7 +198,7 @@ __device__ __forceinline__ void sao_edge_rows(const uint8_t* in, uint8_t* out, i
   }
 }
 
-__global__ void __launch_bounds__(256, 4) k_sao(const FrameDev* __restrict__ frames) {
+__global__ void __launch_bounds__(256, 5) k_sao(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.z / 3];
   const uint32_t fflags = f.flags;
   if (!(fflags & B265_FRAME_SAO) || !f.sao_rec) return;
