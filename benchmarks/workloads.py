@@ -370,7 +370,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
         "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": kbatch,
                    "mpixel_per_s": value * W * H / 1e6,
-                   "value_is": "reconstruction kernels (residual pre-pass, intra wavefront, deblock bS+V+H) on a batch of %d pictures "
+                   "value_is": "reconstruction kernels (residual pre-pass, intra wavefront, deblock V+H) on a batch of %d pictures "
                                "whose work lists are resident in HBM" % kbatch,
                    "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
                          % (kbatch * W * H * 3 // 2 >> 20),
@@ -398,7 +398,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                              "sample of a coded TB read; time = CUDA events around this launch only",
                      "per_kernel_gbs": {"k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1),
                                         "k_intra_wavefront": round(intra_gbs, 1),
-                                        "deblock(bs+V+H luma/chroma, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None,
+                                        "deblock(V+H luma/chroma, bS derived in-kernel, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None,
                                         "sao(synthetic per-CTB parameters on the same pictures, 2P per picture)": round(sao_gbs, 1) if sao_gbs else None}},
     }
     if rank == 0 and world == 1:
