@@ -198,7 +198,11 @@ __device__ __forceinline__ void sao_edge_rows(const uint8_t* in, uint8_t* out, i
   }
 }
 
-__global__ void __launch_bounds__(256, 5) k_sao(const FrameDev* __restrict__ frames) {
+#ifndef SAO_WARPS
+#define SAO_WARPS 8   // warps per block: 8 = two rows of four 32x32 regions, 4 = one row
+#endif
+#define SAO_WY (SAO_WARPS / 4)
+__global__ void __launch_bounds__(SAO_WARPS * 32, 1280 / (SAO_WARPS * 32)) k_sao(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.z / 3];
   const uint32_t fflags = f.flags;
   if (!(fflags & B265_FRAME_SAO) || !f.sao_rec) return;
@@ -215,11 +219,11 @@ __global__ void __launch_bounds__(256, 5) k_sao(const FrameDev* __restrict__ fra
   if (cz == 0) {
     c = 0;
     xw = (wrp & 3) * 8 + (lane & 7);
-    yrow = (blockIdx.y * 8 + (wrp >> 2) * 4 + (lane >> 3)) * SAO_ROWS;
+    yrow = (blockIdx.y * (4 * SAO_WY) + (wrp >> 2) * 4 + (lane >> 3)) * SAO_ROWS;
   } else {
     c = 1 + (lane >> 4);
     xw = (wrp & 3) * 8 + (lane & 7);
-    yrow = ((blockIdx.y * 2 + (cz - 1)) * 4 + (wrp >> 2) * 2 + ((lane >> 3) & 1)) * SAO_ROWS;
+    yrow = ((blockIdx.y * 2 + (cz - 1)) * (2 * SAO_WY) + (wrp >> 2) * 2 + ((lane >> 3) & 1)) * SAO_ROWS;
   }
   const int sh = c ? 1 : 0;
   const int W = c ? fcw : f.width, H = c ? f.ch : f.height;
@@ -314,6 +318,6 @@ __global__ void __launch_bounds__(256, 5) k_sao(const FrameDev* __restrict__ fra
 }
 
 void launch_sao(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h) {
-  dim3 g((((max_w + 3) >> 2) + 31) / 32, (max_h + 8 * SAO_ROWS - 1) / (8 * SAO_ROWS), 3 * n_frames);
-  k_sao<<<g, dim3(32, 8), 0, st>>>(d_frames);
+  dim3 g((((max_w + 3) >> 2) + 31) / 32, (max_h + 4 * SAO_WY * SAO_ROWS - 1) / (4 * SAO_WY * SAO_ROWS), 3 * n_frames);
+  k_sao<<<g, dim3(32, SAO_WARPS), 0, st>>>(d_frames);
 }
