@@ -92,6 +92,20 @@ class B265Error(RuntimeError):
     pass
 
 
+def _check_host_isa():
+    """The host parser is built for x86-64-v3 (build.py HOST_ISA): say so instead of dying with SIGILL."""
+    if os.environ.get("B265_HOST_ISA") == "baseline":
+        return
+    try:
+        flags = next(l for l in open("/proc/cpuinfo") if l.startswith("flags")).split()
+    except (OSError, StopIteration):
+        return
+    missing = [f for f in ("avx2", "bmi2") if f not in flags]
+    if missing:
+        raise B265Error("this CPU lacks %s: rebuild with B265_HOST_ISA=baseline python -m libde265_b200.build --force"
+                        % ", ".join(missing))
+
+
 def load():
     """Load libb265.so (raises if it has not been built: python -m libde265_b200.build)."""
     global _lib
@@ -100,6 +114,7 @@ def load():
     if not os.path.exists(LIB_PATH):
         raise B265Error("libb265.so not built (run `python -m libde265_b200.build`); "
                         "there is no CPU fallback for the b265 pixel path")
+    _check_host_isa()
     lib = C.CDLL(LIB_PATH)
     vp, i32, u8p, i16p = C.c_void_p, C.c_int, C.POINTER(C.c_uint8), C.POINTER(C.c_int16)
     lib.b265_version.restype = C.c_char_p
