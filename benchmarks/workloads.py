@@ -340,7 +340,8 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     # ---------------- end to end through the libde265 C API (host bitstream -> host pictures) ----------------
     step_data = data * loops
     frames_step = nuniq * loops
-    dec = Decoder(device=local, threads=threads, batch=16)
+    dbatch = int(os.environ.get("B265_BENCH_BATCH", 16))   # override: developer sweeps
+    dec = Decoder(device=local, threads=threads, batch=dbatch)
     count = [0]
     cb = lambda img: count.__setitem__(0, count[0] + 1)
     dec.decode_stream(step_data, chunk=1 << 20, on_picture=cb)      # warm-up: allocations, clocks
@@ -375,7 +376,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
                    "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
                          % (kbatch * W * H * 3 // 2 >> 20),
                    "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
-                             "2 CUDA contexts, batch 16; %d frames per step" % (threads, frames_step),
+                             "%s CUDA contexts, batch %d; %d frames per step" % (threads, os.environ.get("B265_RECON_CONTEXTS", "3"), dbatch, frames_step),
                    "host_cores": cores,
                    "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage],
                    "sao_leg_ms": round(sao_ms, 3) if sao_ms else None},
