@@ -61,7 +61,12 @@ static int reject(int line, int code) {
   return code;
 }
 
+#include <chrono>
+static double t_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+static const bool g_build_timing = getenv("B265_BUILD_TIMING") != nullptr;   // developer aid: host time of build_batch by section
+
 static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b265_batch* b) {
+  const double tb0 = t_now();
   if (n_jobs > 255) return reject(__LINE__, B265_ERR_INVALID_ARG);
   b->n_frames = n_jobs;
   b->frames.assign(n_jobs, FrameDev());
@@ -132,6 +137,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       n_pieces[j] = n;
     }
   }
+  const double tb1 = t_now();
   b->max_wave = max_wave;
   // ---- counting sort of the tickets by wave (stable) ----
   std::vector<IntraTicket> tickets(intra.size());
@@ -156,6 +162,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     b->n_ires[s] = (int)ires[s].size();
   }
 
+  const double tb2 = t_now();
   // ---- layout ----
   Packer P;
   const size_t o_frames = P.take(sizeof(FrameDev) * n_jobs);
@@ -253,6 +260,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     CK(cudaMalloc((void**)&b->dev, b->dev_bytes));
     CK(cudaMallocHost((void**)&b->host, b->upload_bytes));
   }
+  const double tb3 = t_now();
   uint8_t* H = b->host;
   uint8_t* D = b->dev;
   auto cp = [&](size_t off, const void* src, size_t bytes) { if (bytes && src) memcpy(H + off, src, bytes); };
@@ -342,15 +350,19 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
   }
   memcpy(H + o_frames, b->frames.data(), sizeof(FrameDev) * n_jobs);
+  const double tb4 = t_now();
   CK(cudaMemcpyAsync(D, H, b->upload_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (g_build_timing)
+    fprintf(stderr, "b265 build_batch n=%d: classify %.2f ms, ticket sort %.2f, layout+staging %.2f, copy %.2f, memcpyAsync call %.2f (%.1f MB)\n",
+            n_jobs, (tb1 - tb0) * 1e3, (tb2 - tb1) * 1e3, (tb3 - tb2) * 1e3, (tb4 - tb3) * 1e3, (t_now() - tb4) * 1e3, b->upload_bytes / 1e6);
   return B265_OK;
 }
 
 // ------------------------------------------------------------------------------------------
 // Device work for one batch, all on ctx->stream:
-//   clear done/bs maps -> [pcm store] -> MC (all PUs) -> inter residual (4 sizes, in place)
+//   clear border mailboxes -> [pcm store] -> MC (all PUs) -> inter residual (4 sizes, in place)
 //   -> intra residual (4 sizes, to the int16 scratch planes) -> intra wavefront
-//   -> boundary strength -> deblock V -> deblock H -> SAO
+//   -> deblock V -> deblock H -> SAO
 // ------------------------------------------------------------------------------------------
 static int run_batch(b265_ctx* ctx, b265_batch* b) {
   cudaStream_t st = ctx->stream;
