@@ -71,7 +71,10 @@ k_dense4(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uin
 // 8x8: one lane per block as well (64 levels = 32 registers).  Columns are transformed in the pair order of the
 // row pass, two at a time, so the clipped first-pass results are packed straight into the row pass' pair words.
 // ------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+#ifndef DENSE8_MIN_CTAS
+#define DENSE8_MIN_CTAS 7   // 72 registers, 28 warps/SM (the kernel is latency-bound)
+#endif
+__global__ void __launch_bounds__(128, DENSE8_MIN_CTAS)
 k_dense8(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uint8_t* __restrict__ dst, int n_blocks) {
   constexpr int KA[4] = {1, 5, 2, 0}, KB[4] = {3, 7, 6, 4};   // pair order of the 8-point transform
   const long long stride = (long long)gridDim.x * blockDim.x;
@@ -84,12 +87,7 @@ k_dense8(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uin
       x[r][0] = w.x; x[r][1] = w.y; x[r][2] = w.z; x[r][3] = w.w;
     }
     uint4* dp = reinterpret_cast<uint4*>(dst + i * 64);
-    uint32_t pw[16];   // row y = words 2y, 2y+1
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const uint4 w = dp[q];
-      pw[4 * q] = w.x; pw[4 * q + 1] = w.y; pw[4 * q + 2] = w.z; pw[4 * q + 3] = w.w;
-    }
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(dp));   // the prediction is loaded after the first pass (16 registers less)
     const DequantK k = dequant_consts(qp ? (int)qp[i] : -1, 3);
     uint32_t Q[4][8];
 #pragma unroll
@@ -108,6 +106,12 @@ k_dense8(const int16_t* __restrict__ coeffs, const uint8_t* __restrict__ qp, uin
       }
 #pragma unroll
       for (int y = 0; y < 8; y++) Q[p][y] = pack_sat16(sra<7>(o[0][y]), sra<7>(o[1][y]));
+    }
+    uint32_t pw[16];   // row y = words 2y, 2y+1
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const uint4 w = dp[q];
+      pw[4 * q] = w.x; pw[4 * q + 1] = w.y; pw[4 * q + 2] = w.z; pw[4 * q + 3] = w.w;
     }
     uint32_t out[16];
 #pragma unroll
