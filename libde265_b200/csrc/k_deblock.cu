@@ -72,23 +72,12 @@ __device__ __forceinline__ const b265_slice& slice_at(const FrameDev& f, int x, 
   return f.slices[f.ctbs ? f.ctbs[ctb].slice : 0];
 }
 
-// one 4-sample luma edge segment; p[k][i] / q[k][i]: line k, distance i from the edge
+// one 4-sample luma edge segment with boundary strength bs > 0; p[k][i] / q[k][i]: line k, distance i from the edge
 template <bool VERT>
-__global__ void k_deblock_luma(const FrameDev* __restrict__ frames) {
-  const FrameDev& f = frames[blockIdx.y];
-  if (!(f.flags & B265_FRAME_DEBLOCK) || !f.unit_info) return;
-  const int uw = f.width >> 2, uh = f.height >> 2;
-  const int ew = VERT ? (uw + 1) >> 1 : uw, eh = VERT ? uh : (uh + 1) >> 1;
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= ew * eh) return;
-  const int ux = VERT ? 2 * (i % ew) : i % ew, uy = VERT ? i / ew : 2 * (i / ew);
-  // boundary strength of this segment, derived here from the unit flags (no bS map round trip through memory)
-  if ((VERT ? ux : uy) == 0) return;
+__device__ __forceinline__ void deblock_luma_segment(const FrameDev& f, int ux, int uy, int bs) {
+  const int uw = f.width >> 2;
   const int uq = uy * uw + ux;
   const uint8_t info = f.unit_info[uq];
-  if (!(info & (VERT ? B265_UNIT_EDGE_V : B265_UNIT_EDGE_H))) return;
-  const int bs = edge_bs(f, VERT ? uq - 1 : uq - uw, uq, info & (VERT ? B265_UNIT_TU_EDGE_V : B265_UNIT_TU_EDGE_H));
-  if (!bs) return;
   const int x = ux << 2, y = uy << 2, pitch = f.pitch[0];
   uint8_t* ptr = f.plane[0] + (size_t)y * pitch + x;
   int p[4][4], q[4][4];
@@ -167,6 +156,50 @@ __global__ void k_deblock_luma(const FrameDev* __restrict__ frames) {
   }
 }
 
+// Candidate segments are all positions of the 8-sample edge grid, but only those on a TU / PU edge with bS > 0 are
+// filtered (one in four for 32x32 TUs), and a warp pays for the filter as soon as ONE lane needs it.  So a warp first
+// tests DBK_ROUNDS x 32 candidates (unit flag + boundary strength, derived here from the unit flags: no bS map round
+// trip through memory), compacts the hits into a shared-memory queue with ballot / popc, then filters them with
+// all lanes busy.
+#define DBK_WARPS 4
+#define DBK_ROUNDS 4
+template <bool VERT>
+__global__ void __launch_bounds__(DBK_WARPS * 32) k_deblock_luma(const FrameDev* __restrict__ frames) {
+  const FrameDev& f = frames[blockIdx.y];
+  if (!(f.flags & B265_FRAME_DEBLOCK) || !f.unit_info) return;
+  __shared__ uint32_t queue[DBK_WARPS][DBK_ROUNDS * 32];
+  const int uw = f.width >> 2, uh = f.height >> 2;
+  const int ew = VERT ? (uw + 1) >> 1 : uw, eh = VERT ? uh : (uh + 1) >> 1;
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int base = (blockIdx.x * DBK_WARPS + warp) * (DBK_ROUNDS * 32);
+  if (base >= ew * eh) return;
+  uint32_t* q = queue[warp];
+  int n = 0;
+#pragma unroll
+  for (int r = 0; r < DBK_ROUNDS; r++) {
+    const int i = base + r * 32 + lane;
+    int bs = 0, ux = 0, uy = 0;
+    if (i < ew * eh) {
+      ux = VERT ? 2 * (i % ew) : i % ew;
+      uy = VERT ? i / ew : 2 * (i / ew);
+      if ((VERT ? ux : uy) != 0) {
+        const int uq = uy * uw + ux;
+        const uint8_t info = f.unit_info[uq];
+        if (info & (VERT ? B265_UNIT_EDGE_V : B265_UNIT_EDGE_H))
+          bs = edge_bs(f, VERT ? uq - 1 : uq - uw, uq, info & (VERT ? B265_UNIT_TU_EDGE_V : B265_UNIT_TU_EDGE_H));
+      }
+    }
+    const unsigned hit = __ballot_sync(B265_FULL_MASK, bs != 0);
+    if (bs) q[n + __popc(hit & ((1u << lane) - 1))] = (uint32_t)ux | ((uint32_t)uy << 14) | ((uint32_t)bs << 28);
+    n += __popc(hit);
+  }
+  __syncwarp();
+  for (int k = lane; k < n; k += 32) {
+    const uint32_t e = q[k];
+    deblock_luma_segment<VERT>(f, (int)(e & 0x3fff), (int)((e >> 14) & 0x3fff), (int)(e >> 28));
+  }
+}
+
 // chroma (4:2:0): edges on an 8-chroma-sample grid, only bS == 2, one sample each side; the bS of a
 // 4-row chroma segment is the one of the FIRST luma unit of the corresponding 8 luma rows
 // (deblock.cc:741-763)
@@ -216,10 +249,11 @@ void launch_deblock(cudaStream_t st, const FrameDev* d_frames, int n_frames, int
                     const uint32_t* mc_items, int n_mc, bool chroma) {
   const int uw = max_w >> 2, uh = max_h >> 2;
   if (n_mc > 0) k_motion_raster<<<(n_mc * 32 + 255) / 256, 256, 0, st>>>(d_frames, mc_items, n_mc);
-  dim3 gv((((uw + 1) >> 1) * uh + 127) / 128, n_frames), gh((uw * ((uh + 1) >> 1) + 127) / 128, n_frames);
+  const int per_cta = DBK_WARPS * DBK_ROUNDS * 32;   // candidate segments per block
+  dim3 gv((((uw + 1) >> 1) * uh + per_cta - 1) / per_cta, n_frames), gh((uw * ((uh + 1) >> 1) + per_cta - 1) / per_cta, n_frames);
   dim3 cv((((uw + 3) >> 2) * ((uh + 1) >> 1) + 127) / 128, n_frames), chh((((uw + 1) >> 1) * ((uh + 3) >> 2) + 127) / 128, n_frames);
-  k_deblock_luma<true><<<gv, 128, 0, st>>>(d_frames);
+  k_deblock_luma<true><<<gv, DBK_WARPS * 32, 0, st>>>(d_frames);
   if (chroma) k_deblock_chroma<true><<<cv, 128, 0, st>>>(d_frames);
-  k_deblock_luma<false><<<gh, 128, 0, st>>>(d_frames);
+  k_deblock_luma<false><<<gh, DBK_WARPS * 32, 0, st>>>(d_frames);
   if (chroma) k_deblock_chroma<false><<<chh, 128, 0, st>>>(d_frames);
 }
