@@ -161,8 +161,12 @@ __device__ __forceinline__ void deblock_luma_segment(const FrameDev& f, int ux, 
 // tests DBK_ROUNDS x 32 candidates (unit flag + boundary strength, derived here from the unit flags: no bS map round
 // trip through memory), compacts the hits into a shared-memory queue with ballot / popc, then filters them with
 // all lanes busy.
+#ifndef DBK_WARPS
 #define DBK_WARPS 4
+#endif
+#ifndef DBK_ROUNDS
 #define DBK_ROUNDS 4
+#endif
 template <bool VERT>
 __global__ void __launch_bounds__(DBK_WARPS * 32) k_deblock_luma(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.y];
