@@ -3,6 +3,7 @@
 // frame path (k_residual.cu, k_deblock.cu, k_sao.cu) on caller-supplied host or device planes; they
 // exist so each stage can be parity-tested and timed in isolation (SURVEY §8c function-level oracle).
 #include <string.h>
+#include <algorithm>
 #include <vector>
 #include "backend.h"
 #include "kernels.h"
@@ -121,14 +122,29 @@ int b265_residual_sparse(b265_ctx* ctx, int mem, const b265_tu* tus, int n_tus, 
   for (int c = 0; c < 3; c++) { S.f.plane[c] = d_plane; S.f.pitch[c] = pitch; }  // every TU addresses `dst`
   r = push_framedev(ctx, S);
   if (r) return r;
+  // the packed kernels add to the prediction with 128-bit accesses: 16-byte aligned plane, pitch and TU column
+  int n_plain[4] = {0, 0, 0, 0};
+  if (pitch % 16 == 0 && (reinterpret_cast<uintptr_t>(d_plane) & 15) == 0)
+    for (int s = 2; s < 4; s++) {
+      auto plain = [&](uint32_t i) { return !(tus[i].flags & (B265_TU_SKIP | B265_TU_BYPASS)) && (tus[i].x & 15) == 0; };
+      n_plain[s] = (int)(std::stable_partition(items[s].begin(), items[s].end(), plain) - items[s].begin());
+    }
   for (int s = 0; s < 4; s++) {
     if (items[s].empty()) continue;
     uint32_t* d = (uint32_t*)(d_items + (size_t)s * al256(4 * (size_t)n_tus));
     CK(cudaMemcpyAsync(d, items[s].data(), 4 * items[s].size(), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    launch_residual_sparse(ctx->stream, 2 + s, (const FrameDev*)S.base, d, (int)items[s].size(), ctx->sm_count);
-    ctx->launches++;
-    CK_LAUNCH("k_residual_sparse");
+    const int n = (int)items[s].size(), np = n_plain[s];
+    if (np) {   // plain DCT TUs of 16x16 / 32x32: packed dp2a kernels (as in the frame path)
+      launch_residual_sparse_fast(ctx->stream, 2 + s, (const FrameDev*)S.base, d, np, ctx->sm_count, false);
+      ctx->launches++;
+      CK_LAUNCH("k_residual_sparse_fast");
+    }
+    if (n > np) {
+      launch_residual_sparse(ctx->stream, 2 + s, (const FrameDev*)S.base, d + np, n - np, ctx->sm_count);
+      ctx->launches++;
+      CK_LAUNCH("k_residual_sparse");
+    }
   }
   if (mem == B265_MEM_HOST) CK(cudaMemcpyAsync(dst, d_plane, (size_t)pitch * height, cudaMemcpyDeviceToHost, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
