@@ -502,14 +502,36 @@ def run_sweep(a, rank, world, local, ClockSampler, measured_peaks):
     clk = clocks.stop()
     launches = ctx.launches - launches0
     ms_step = ms_total / a.steps
-    e2e_px = 0
-    t0 = time.perf_counter()
+    # end to end through the C ABI with HOST buffers: levels, QPs and prediction in pinned host memory (b265_host_alloc),
+    # H2D + kernel + D2H of the reconstruction inside the timed region; 2^24 px per transform kind
+    def pinned_copy(arr):
+        p = C.c_void_p()
+        if ctx.lib.b265_host_alloc(ctx.h, arr.nbytes, C.byref(p)) != 0:
+            return arr.copy(), None
+        view = np.frombuffer((C.c_uint8 * arr.nbytes).from_address(p.value), dtype=arr.dtype).reshape(arr.shape)
+        view[...] = arr
+        return view, p
+    e2e_in, pins = [], []
     for k in kinds:
         c, q, d = k["host"]
         m = min(k["n"], (1 << 24) >> (2 * k["log2"]))
-        ctx.residual_batch(k["kind"], k["log2"], c[:m], d[:m].copy(), q[:m])
+        trio = []
+        for arr in (c[:m], q[:m], d[:m]):
+            v, p = pinned_copy(arr)
+            trio.append(v)
+            if p is not None:
+                pins.append(p)
+        e2e_in.append((k, m, trio))
+    e2e_px = 0
+    for k, m, (pc, pq, pd) in e2e_in[:1]:   # untimed warm-up of the staging buffers
+        ctx.residual_batch(k["kind"], k["log2"], pc, pd.copy(), pq)
+    t0 = time.perf_counter()
+    for k, m, (pc, pq, pd) in e2e_in:
+        ctx.residual_batch(k["kind"], k["log2"], pc, pd, pq)
         e2e_px += m << (2 * k["log2"])
     e2e_s = _barrier_max(world, time.perf_counter() - t0)
+    for p in pins:
+        ctx.lib.b265_host_free(ctx.h, p)
     peak, peak_src = measured_peaks()
     dom = max(per_kind.items(), key=lambda kv: kv[1]["ms"])
     res = {
