@@ -657,6 +657,15 @@ def run_mc(a, rank, world, local, ClockSampler, measured_peaks):
     launches = ctx.launches - launches0
     ms_step = _barrier_max(world, float(np.mean(ms)))
     ctx.free_batch(batch)
+    # end to end through b265_mc_batch with HOST buffers: reference planes, PU and slice lists up, prediction planes down
+    dst = [np.zeros((H, W), np.uint8), np.zeros((H // 2, W // 2), np.uint8), np.zeros((H // 2, W // 2), np.uint8)]
+    ctx.mc_batch(keep[0], keep[1], refs, dst, W, H)   # untimed: staging buffers
+    t0 = time.perf_counter()
+    for i in range(layers):
+        ctx.mc_batch(keep[2 * i], keep[2 * i + 1], refs, dst, W, H)
+    e2e_s = _barrier_max(world, time.perf_counter() - t0)
+    e2e = {"value": world * layers * W * H / e2e_s / 1e6, "unit": "Mpixel/s",
+           "h2d_bytes_per_step": int(layers * len(refs) * W * H * 3 // 2 + 24 * n_pus), "d2h_bytes_per_step": int(layers * W * H * 3 // 2)}
     for s_ in sids + ref_sids:
         ctx.surface_release(s_)
     ctx.close()
@@ -668,7 +677,7 @@ def run_mc(a, rank, world, local, ClockSampler, measured_peaks):
             "vs_baseline": None, "dtype": "u8 pixels / int16 intermediates / int32 accumulators", "data": "synthetic",
             "config": {"workload": "mc_pus: SURVEY 8d config 3, 1920x1080, 3 references, %d PUs in %d pictures" % (n_pus, layers),
                        "l2": "L2 flushed before every timed step"},
-            "e2e": None, "gpu_launches": int(launches), "clocks": clk,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "roofline": {"bound": "hbm", "kernel": "k_mc", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                          "traffic": None, "peak_source": peak_src,
                          "note": "algorithmic bytes = 3*w*h per uni-predicted PU (1.5 read + 1.5 written), 4.5*w*h per bi-predicted PU"}}
