@@ -8,7 +8,7 @@ stream_1080p  (configs[0]) the 1080p intra stream, same measurement.
 idct_sweep    (configs[1]) synthetic TU coefficient sweep, dense-input form (4*nT^2 B per block).
 
 The reference arm / cpu_baseline is the unmodified reference decoder `oracle/_ref/dec265` (SSE path) run as
-min(cores, 16) concurrent processes on the same stream (enc265 streams have no WPP/tiles, so the
+one process per host core on the same stream (enc265 streams have no WPP/tiles, so the
 reference parallelises only across streams).
 """
 import ctypes as C
@@ -177,7 +177,7 @@ def cpu_baseline_stream(wl, budget_s=20.0):
     name, patched, loops, _, desc = STREAM_WL[wl]
     data = _stream_bytes(name, patched)
     gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
-    procs = min(host_cores(), 16)
+    procs = host_cores()   # every core the box has: both arms see the same machine
     one = run_dec265(data, 1, 1)
     if one is None:
         return cpu_port_stream(wl)
@@ -411,7 +411,7 @@ def run_reference_stream(a, wl):
     name, patched, loops, _, desc = STREAM_WL[wl]
     data = _stream_bytes(name, patched)
     gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
-    procs = min(host_cores(), 16)
+    procs = host_cores()   # every core the box has: both arms see the same machine
     one = run_dec265(data, 1, 1)
     if one is None:
         cb = cpu_port_stream(wl)

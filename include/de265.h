@@ -134,6 +134,9 @@ LIBDE265_API int de265_get_number_of_NAL_units_pending(de265_decoder_context*);
  * IMAGE_BUFFER_FULL); err == OK && !more: finished; err != OK && !more: fatal (de265.h:263-276) */
 LIBDE265_API de265_error de265_decode(de265_decoder_context*, int* more);
 LIBDE265_API void de265_reset(de265_decoder_context*);
+/* deprecated one-call form (de265.h:206-219, de265.cc:262-300): push `length` bytes (0 = flush) and decode
+ * everything that is complete; WAITING_FOR_INPUT_DATA is not reported as an error */
+LIBDE265_API de265_error de265_decode_data(de265_decoder_context*, const void* data, int length);
 
 LIBDE265_API const struct de265_image* de265_peek_next_picture(de265_decoder_context*);
 LIBDE265_API const struct de265_image* de265_get_next_picture(de265_decoder_context*);
@@ -192,9 +195,16 @@ enum de265_acceleration {
   de265_acceleration_ARM = 70,
   de265_acceleration_NEON = 80,
   de265_acceleration_AUTO = 10000,
-  /* extension: the only code path this library has; every other value is accepted and maps here */
+  /* extension: the only pixel path this library has.  de265_set_parameter_int(ACCELERATION_CODE, v) accepts
+   * AUTO and CUDA; any CPU code (SCALAR .. NEON) cannot be honoured (there is no CPU pixel path) and is
+   * reported through de265_get_warning() as DE265_WARNING_B265_ACCELERATION_UNAVAILABLE */
+  de265_acceleration_CUDA = 20000,
   de265_acceleration_CUDA_SM100 = 20000
 };
+/* b265 warnings (>= 1000 like every libde265 warning; outside the reference's range 1000-1026) */
+#define DE265_WARNING_B265_ACCELERATION_UNAVAILABLE ((de265_error)1100)
+/* current ACCELERATION_CODE (always de265_acceleration_CUDA) */
+LIBDE265_API int b265_de265_get_acceleration(de265_decoder_context*);
 LIBDE265_API void de265_set_parameter_bool(de265_decoder_context*, enum de265_param param, int value);
 LIBDE265_API void de265_set_parameter_int(de265_decoder_context*, enum de265_param param, int value);
 LIBDE265_API int de265_get_parameter_bool(de265_decoder_context*, enum de265_param param);
@@ -219,6 +229,8 @@ LIBDE265_API void b265_de265_set_parse_only(int on);
 /* `out` is a b265_frame_job (b265.h); void* here so that de265.h stays free of b265.h types */
 LIBDE265_API int b265_de265_image_job(de265_decoder_context*, const struct de265_image*, void* out_b265_frame_job);
 LIBDE265_API int b265_de265_image_poc(const struct de265_image*);
+/* 1 = IRAP picture with NoRaslOutputFlag (first of a coded video sequence: POCs restart, earlier pictures are output first) */
+LIBDE265_API int b265_de265_image_starts_cvs(const struct de265_image*);
 
 #ifdef __cplusplus
 }

@@ -92,11 +92,14 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     ctb_area.assign((size_t)3 * nctb, 0);
     b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
     if (J.log2_ctb < 4 || J.log2_ctb > 6) return reject(__LINE__, B265_ERR_INVALID_ARG);
+    // FrameDev holds 16 reference slots (a DPB of 16 pictures is the HEVC maximum, A.4.2); slice indices travel in 8 bits
+    if (J.n_refs < 0 || J.n_refs > 16 || J.n_slices > 256) return reject(__LINE__, B265_ERR_INVALID_ARG);
     int cur = -1;
     for (int i = 0; i < J.n_tus; i++) {
       const b265_tu& t = J.tus[i];
       const int c = t.cidx_log2 & 3, lg = (t.cidx_log2 >> 2) & 7;
       if (lg < 2 || lg > 5 || c > 2) return reject(__LINE__, B265_ERR_INVALID_ARG);
+      if ((uint64_t)t.coeff_off + t.ncoeff > (uint64_t)J.n_coeffs) return reject(__LINE__, B265_ERR_INVALID_ARG);
       const int sh = (c && J.chroma_format_idc) ? 1 : 0;
       const int bx = (t.x << sh) >> J.log2_ctb, by = (t.y << sh) >> J.log2_ctb;
       if (bx >= cw_ || by >= ch_) return reject(__LINE__, B265_ERR_INVALID_ARG);
@@ -131,8 +134,16 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
     {  // one MC item per 16x16 piece of a prediction block (pu_expand)
       uint32_t n = 0;
-      for (int i = 0; i < J.n_pus; i++)
-        for (int k = pu_pieces(J.pus[i]); k > 0; k--) mc.push_back(((uint32_t)j << 24) | n++);
+      const int n_sl = std::max(1, J.n_slices);
+      for (int i = 0; i < J.n_pus; i++) {
+        const b265_pu& pu = J.pus[i];
+        // a slot or slice index outside the job's tables would become a wild device pointer in k_mc
+        if (pu.slice >= n_sl || !(pu.flags & (B265_PU_L0 | B265_PU_L1)) || pu.w == 0 || pu.h == 0 || pu.w > 64 || pu.h > 64 ||
+            ((pu.flags & B265_PU_L0) && (pu.ref_slot[0] >= J.n_refs || (uint8_t)pu.ref_idx[0] >= 16)) ||
+            ((pu.flags & B265_PU_L1) && (pu.ref_slot[1] >= J.n_refs || (uint8_t)pu.ref_idx[1] >= 16)))
+          return reject(__LINE__, B265_ERR_INVALID_ARG);
+        for (int k = pu_pieces(pu); k > 0; k--) mc.push_back(((uint32_t)j << 24) | n++);
+      }
       if (n >= (1u << 24)) return reject(__LINE__, B265_ERR_UNSUPPORTED);
       n_pieces[j] = n;
     }
@@ -341,7 +352,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     b->max_pcms = std::max(b->max_pcms, J.n_pcms);
     f.bs = nullptr;   // boundary strengths are derived inside the deblocking kernels
     f.motion = so[j].motion ? (uint32_t*)(D + so[j].motion) : nullptr;
-    f.n_refs = std::min(J.n_refs, 16);
+    f.n_refs = J.n_refs;
     for (int r = 0; r < f.n_refs; r++) {
       const int sid = J.ref_surfaces[r];
       if (sid < 0 || sid >= (int)ctx->surfaces.size() || !ctx->surfaces[sid].used) return reject(__LINE__, B265_ERR_INVALID_ARG);

@@ -135,6 +135,18 @@ struct Decoder {
       gpus.push_back(c);
     }
     gpu = gpus[0];
+    dpb.make_unavailable = [this](int poc, bool lt) {
+      auto r = std::make_shared<RefPic>();
+      r->poc = poc;
+      r->is_lt = lt;
+      r->unavailable = true;
+      r->uid = next_uid++;
+      r->owner = this;
+      r->recycle = &Decoder::recycle_cb;
+      if (cur) { r->u_w = cur->pic.u_w; r->u_h = cur->pic.u_h; r->ctbs_w = cur->pic.sps->ctbs_w; r->log2_ctb = cur->pic.sps->log2_ctb; }
+      r->parsed.store(1, std::memory_order_release);   // empty motion field = all intra (fill_pred_mode(MODE_INTRA))
+      return r;
+    };
     for (int i = 0; i < n_ctx; i++) recon_threads.emplace_back([this, i] { recon_loop(i); });
   }
   ~Decoder() {
@@ -416,7 +428,17 @@ struct Decoder {
         }
         // a reference that failed (or was never reconstructed) cannot be read
         bool refs_ok = true;
-        for (const auto& r : p.ref_pics) refs_ok &= r && r->surface >= 0 && r->ctx == ci;
+        for (const auto& r : p.ref_pics) {
+          if (r && r->unavailable && r->surface < 0) {   // generate_unavailable_reference_picture: 1 << (bit depth - 1) everywhere
+            int sid = -1;
+            if (b265_surface_alloc(gpu, p.width, p.height, p.sps->chroma_array_type ? 1 : 0, &sid) == B265_OK &&
+                b265_surface_fill(gpu, sid, 128, 128) == B265_OK) {
+              r->ctx = ci;
+              r->surface = sid;
+            } else if (sid >= 0) b265_surface_release(gpu, sid);
+          }
+          refs_ok &= r && r->surface >= 0 && r->ctx == ci;
+        }
         if (!refs_ok) {
           b265_surface_release(gpu, p.surface);
           p.surface = -1;
@@ -475,7 +497,12 @@ struct Decoder {
           inflight.pop_front();
           stat_pictures++;
           if (up->pic.error && up->pic.error < 1000 && !fatal_error) fatal_error = up->pic.error;
+          const uint64_t gop_done = up->pic.gop;
           push_reorder(std::move(up));
+          // context pinning of GOPs nobody can belong to any more (pictures retire in decoding order, GOP ids grow)
+          const uint64_t oldest = inflight.empty() ? gop_done : inflight.front()->pic.gop;
+          for (auto it = gop_ctx.begin(); it != gop_ctx.end();)
+            if (it->first < oldest) it = gop_ctx.erase(it); else ++it;
         }
       }
       cv_done.notify_all();
@@ -485,8 +512,7 @@ struct Decoder {
 
   // output order (C.5.2.2 "bumping"): called with mu held
   void push_reorder(std::unique_ptr<de265_image> img) {
-    const bool irap = img->pic.nal_type >= NAL_BLA_W_LP && img->pic.nal_type <= NAL_RSV_IRAP_VCL23;
-    if (irap && (img->pic.nal_type != NAL_CRA)) flush_reorder();
+    if (img->pic.irap_no_rasl) flush_reorder();   // every IRAP picture with NoRaslOutputFlag (decctx.cc:1357-1365), CRA included
     const int max_reorder = img->pic.sps->max_num_reorder[img->pic.sps->max_sub_layers - 1];
     if (!img->pic.pic_output || (img->pic.error && suppress_faulty)) {
       release_locked(*img);
@@ -639,6 +665,12 @@ struct Decoder {
     std::shared_ptr<const Pps> pps;
     int r = parse_slice_header(br, type, ps, have_prev_indep ? &prev_indep : nullptr, removed, sh, pps);
     if (r) { warn(r >= 1000 ? r : DE265_WARNING_SLICEHEADER_INVALID); return DE265_OK; }
+    // RASL pictures that follow an IRAP picture with NoRaslOutputFlag are not decoded at all (decctx.cc:2038-2045, :2069):
+    // no picture, no POC / reference-picture-set processing, no DPB entry, no error
+    if ((type == NAL_RASL_N || type == NAL_RASL_R) && skip_rasl) {
+      if (sh.first_slice_segment_in_pic) dispatch_current();
+      return DE265_OK;
+    }
     if (sh.first_slice_segment_in_pic) {
       dispatch_current();
       cur.reset(new de265_image());
@@ -652,8 +684,10 @@ struct Decoder {
       p.pic_output = sh.pic_output;
       p.init_maps();
       p.poc = compute_poc(sh, *pps->sps, type, tid);
-      if ((type == NAL_RASL_N || type == NAL_RASL_R) && skip_rasl) p.pic_output = 0;   // leading pictures of a random access point
-      if (type >= NAL_BLA_W_LP && type <= NAL_RSV_IRAP_VCL23) skip_rasl = last_no_rasl_output;
+      if (type >= NAL_BLA_W_LP && type <= NAL_RSV_IRAP_VCL23) {
+        skip_rasl = last_no_rasl_output;
+        p.irap_no_rasl = last_no_rasl_output;
+      }
       dpb.apply_rps(sh, *pps->sps, p.poc, last_no_rasl_output);
       if (last_no_rasl_output) gop_id++;
       p.gop = gop_id;
@@ -815,6 +849,7 @@ LIBDE265_API const char* de265_get_error_text(de265_error err) {
     case DE265_WARNING_NONEXISTING_PPS_REFERENCED: return "non-existing PPS referenced";
     case DE265_WARNING_NONEXISTING_SPS_REFERENCED: return "non-existing SPS referenced";
     case DE265_WARNING_EOSS_BIT_NOT_SET: return "end-of-sub-stream-one-bit not set to 1 when it should be";
+    case DE265_WARNING_B265_ACCELERATION_UNAVAILABLE: return "requested CPU acceleration code is not available: this library only has the CUDA pixel path";
     default: return err >= 1000 ? "warning" : "unknown error";
   }
 }
@@ -884,6 +919,18 @@ LIBDE265_API int de265_get_number_of_input_bytes_pending(de265_decoder_context* 
 LIBDE265_API int de265_get_number_of_NAL_units_pending(de265_decoder_context* c) { return (int)DEC(c)->nals.size(); }
 
 LIBDE265_API de265_error de265_decode(de265_decoder_context* c, int* more) { return DEC(c)->decode(more); }
+
+LIBDE265_API de265_error de265_decode_data(de265_decoder_context* c, const void* data, int len) {
+  de265_error err = len > 0 ? de265_push_data(c, data, len, 0, nullptr) : de265_flush_data(c);
+  if (err != DE265_OK) return err;
+  int more = 0;
+  do {
+    err = de265_decode(c, &more);
+    if (err != DE265_OK) more = 0;
+    if (err == DE265_ERROR_WAITING_FOR_INPUT_DATA) err = DE265_OK;   // not an error for this call (de265.cc:283-288)
+  } while (more);
+  return err;
+}
 
 LIBDE265_API void de265_reset(de265_decoder_context* c) {
   Decoder* d = DEC(c);
@@ -997,9 +1044,13 @@ LIBDE265_API void de265_set_parameter_bool(de265_decoder_context* c, enum de265_
     default: break;
   }
 }
-LIBDE265_API void de265_set_parameter_int(de265_decoder_context*, enum de265_param, int) {
-  // DUMP_*_HEADERS are debugging aids; ACCELERATION_CODE has a single implementation (CUDA sm_100a)
+LIBDE265_API void de265_set_parameter_int(de265_decoder_context* c, enum de265_param p, int v) {
+  // DUMP_*_HEADERS are debugging aids.  ACCELERATION_CODE (de265.cc:603-612 -> decctx.cc:430-449): the only
+  // table this library can install is the CUDA one; a request for a CPU table is refused with a warning
+  if (p == DE265_DECODER_PARAM_ACCELERATION_CODE && v != de265_acceleration_AUTO && v != de265_acceleration_CUDA)
+    DEC(c)->warn(DE265_WARNING_B265_ACCELERATION_UNAVAILABLE);
 }
+LIBDE265_API int b265_de265_get_acceleration(de265_decoder_context*) { return de265_acceleration_CUDA; }
 LIBDE265_API int de265_get_parameter_bool(de265_decoder_context* c, enum de265_param p) {
   Decoder* d = DEC(c);
   switch (p) {
@@ -1018,6 +1069,7 @@ LIBDE265_API int b265_de265_image_job(de265_decoder_context* c, const struct de2
   return img->pic.error;
 }
 LIBDE265_API int b265_de265_image_poc(const struct de265_image* img) { return img->pic.poc; }
+LIBDE265_API int b265_de265_image_starts_cvs(const struct de265_image* img) { return img->pic.irap_no_rasl ? 1 : 0; }
 LIBDE265_API void b265_de265_set_batch(de265_decoder_context* c, int n) {
   Decoder* d = DEC(c);
   std::lock_guard<std::mutex> l(d->mu);

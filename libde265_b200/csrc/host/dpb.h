@@ -3,6 +3,7 @@
 // (process_reference_picture_set, construct_reference_picture_lists).  The pictures themselves live in HBM
 // (RefPic::surface); this is only the bookkeeping, shared by the decoder and the test-stream generator.
 #pragma once
+#include <functional>
 #include <memory>
 #include <vector>
 #include "picture.h"
@@ -13,7 +14,16 @@ struct Dpb {
   std::vector<std::shared_ptr<RefPic>> pics;   // pictures marked "used for reference"
   // reference picture set of the current picture
   std::vector<std::shared_ptr<RefPic>> st_before, st_after, lt_curr;
-  bool missing = false;                        // a picture of the set is not in the buffer
+  bool missing = false;                        // a picture of the set is not in the buffer (and could not be substituted)
+  // Substitute for a picture of the set that is not in the buffer (8.3.3.2, decctx.cc:1408-1434: a mid-grey picture
+  // whose motion field reads "all intra", never output).  Unset: such a picture makes the lists fail.
+  std::function<std::shared_ptr<RefPic>(int poc, bool long_term)> make_unavailable;
+  std::shared_ptr<RefPic> substitute(int poc, bool lt) {
+    if (!make_unavailable) { missing = true; return nullptr; }
+    std::shared_ptr<RefPic> r = make_unavailable(poc, lt);
+    if (!r) missing = true;
+    return r;
+  }
 
   void clear() { pics.clear(); st_before.clear(); st_after.clear(); lt_curr.clear(); missing = false; }
 
@@ -45,22 +55,24 @@ struct Dpb {
       } else {
         r = find_any(p, max_lsb - 1);
       }
+      // a missing long-term picture is generated whether the current picture uses it or not (decctx.cc:1572-1612),
+      // with the POC the header gives (LSB only when the MSB is not signalled)
+      if (!r) r = substitute(p, true);
       if (r) { r->is_lt = true; keep.push_back(r); }
-      if (sh.used_by_curr_lt[i]) {
-        if (!r) missing = true;
-        lt_curr.push_back(r);
-      }
+      if (sh.used_by_curr_lt[i]) lt_curr.push_back(r);
     }
     const ShortTermRps& rps = sh.st_rps;
     for (int i = 0; i < rps.num_negative; i++) {
       std::shared_ptr<RefPic> r = find_st(poc + rps.delta_poc_s0[i]);
+      if (!r && rps.used_s0[i]) r = substitute(poc + rps.delta_poc_s0[i], false);   // only pictures of the Curr sets (decctx.cc:1627-1667)
       if (r) keep.push_back(r);
-      if (rps.used_s0[i]) { if (!r) missing = true; st_before.push_back(r); }
+      if (rps.used_s0[i]) st_before.push_back(r);
     }
     for (int i = 0; i < rps.num_positive; i++) {
       std::shared_ptr<RefPic> r = find_st(poc + rps.delta_poc_s1[i]);
+      if (!r && rps.used_s1[i]) r = substitute(poc + rps.delta_poc_s1[i], false);
       if (r) keep.push_back(r);
-      if (rps.used_s1[i]) { if (!r) missing = true; st_after.push_back(r); }
+      if (rps.used_s1[i]) st_after.push_back(r);
     }
     pics.swap(keep);   // everything else is no longer used for reference
   }
@@ -94,7 +106,7 @@ struct Dpb {
         size_t slot = 0;
         while (slot < pic.ref_pics.size() && pic.ref_pics[slot] != r) slot++;
         if (slot == pic.ref_pics.size()) {
-          if (slot >= 32) return false;
+          if (slot >= 16) return false;   // the back end holds 16 reference slots per picture (FrameDev::ref_plane)
           pic.ref_pics.push_back(r);
         }
         out.slot[X][i] = (uint8_t)slot;

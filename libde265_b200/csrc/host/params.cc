@@ -259,6 +259,14 @@ int parse_sps(BitReader& br, std::shared_ptr<Sps>& out) {
       s->log2_max_tb > s->log2_ctb || s->width <= 0 || s->height <= 0 || s->width > 16384 || s->height > 16384)
     return E_RANGE;
   if ((s->width & ((1 << s->log2_min_cb) - 1)) || (s->height & ((1 << s->log2_min_cb) - 1))) return E_RANGE;
+  {  // the conformance window must leave at least one sample (7.4.3.2.1), in chroma units of the format
+    const int sub_w = (s->chroma_format_idc == 1 || s->chroma_format_idc == 2) ? 2 : 1, sub_h = s->chroma_format_idc == 1 ? 2 : 1;
+    for (int i = 0; i < 4; i++) if (s->conf_win[i] < 0 || s->conf_win[i] > 16384) return E_RANGE;
+    if (sub_w * (s->conf_win[0] + s->conf_win[1]) >= s->width || sub_h * (s->conf_win[2] + s->conf_win[3]) >= s->height) return E_RANGE;
+  }
+  for (int i = 0; i <= msl1; i++)   // A.4.2: the DPB holds at most 16 pictures
+    if (s->max_dec_pic_buffering[i] < 1 || s->max_dec_pic_buffering[i] > 16 || s->max_num_reorder[i] < 0 ||
+        s->max_num_reorder[i] > s->max_dec_pic_buffering[i] - 1) return E_RANGE;
   s->scaling_list_enabled = br.u1();
   if (s->scaling_list_enabled) {
     default_scaling(s->scaling);
@@ -277,6 +285,9 @@ int parse_sps(BitReader& br, std::shared_ptr<Sps>& out) {
     s->log2_min_pcm = br.ue() + 3;
     s->log2_max_pcm = s->log2_min_pcm + br.ue();
     s->pcm_lf_disabled = br.u1();
+    if (br.err || s->pcm_bits_luma > s->bit_depth_luma || s->pcm_bits_chroma > s->bit_depth_chroma ||
+        s->log2_min_pcm > 5 || s->log2_max_pcm > 5 || s->log2_max_pcm > s->log2_ctb || s->log2_min_pcm < (s->log2_min_cb < 5 ? s->log2_min_cb : 5))
+      return E_RANGE;
   }
   const uint32_t n_rps = br.ue();
   if (br.err || n_rps > 64) return E_RANGE;
@@ -353,7 +364,9 @@ int parse_pps(BitReader& br, const ParamSets& ps, std::shared_ptr<Pps>& out) {
   p->tiles_enabled = br.u1();
   p->entropy_coding_sync = br.u1();
   if (br.err || p->num_ref_idx_default[0] > 16 || p->num_ref_idx_default[1] > 16 ||
-      p->diff_cu_qp_delta_depth > sps->log2_ctb - sps->log2_min_cb)
+      p->diff_cu_qp_delta_depth > sps->log2_ctb - sps->log2_min_cb || p->diff_cu_qp_delta_depth < 0 ||
+      p->init_qp < -(6 * (sps->bit_depth_luma - 8)) || p->init_qp > 51 ||
+      p->cb_qp_offset < -12 || p->cb_qp_offset > 12 || p->cr_qp_offset < -12 || p->cr_qp_offset > 12)
     return E_RANGE;
   std::vector<int> col_w, row_h;
   if (p->tiles_enabled) {
@@ -398,6 +411,7 @@ int parse_pps(BitReader& br, const ParamSets& ps, std::shared_ptr<Pps>& out) {
   }
   p->lists_modification_present = br.u1();
   p->log2_parallel_merge_level = br.ue() + 2;
+  if (br.err || p->log2_parallel_merge_level > sps->log2_ctb) return E_RANGE;
   p->slice_header_extension_present = br.u1();
   if (br.u1()) {  // pps_extension_present_flag
     const int range_ext = br.u1();
@@ -408,6 +422,7 @@ int parse_pps(BitReader& br, const ParamSets& ps, std::shared_ptr<Pps>& out) {
       p->chroma_qp_offset_list_enabled = br.u1();
       if (p->chroma_qp_offset_list_enabled) {
         p->diff_cu_chroma_qp_offset_depth = br.ue();
+        if (br.err || p->diff_cu_chroma_qp_offset_depth < 0 || p->diff_cu_chroma_qp_offset_depth > sps->log2_ctb - sps->log2_min_cb) return E_RANGE;
         p->chroma_qp_offset_list_len = br.ue() + 1;
         if (p->chroma_qp_offset_list_len > 6) return E_RANGE;
         for (int i = 0; i < p->chroma_qp_offset_list_len; i++) {
@@ -617,6 +632,7 @@ int parse_slice_header(BitReader& br, int nal_type, const ParamSets& ps, const S
     sh.lf_across_slices = pps->lf_across_slices;
     if (pps->lf_across_slices && (sh.sao_luma || sh.sao_chroma || !sh.deblocking_disabled)) sh.lf_across_slices = br.u1();
     sh.slice_qp = pps->init_qp + sh.qp_delta;
+    if (sh.slice_qp < -(6 * (pps->sps->bit_depth_luma - 8)) || sh.slice_qp > 51) return E_SLICEHDR;   // SliceQpY range, 7.4.7.1
     sh.slice_addr_rs = sh.segment_address;
   }
   if (pps->tiles_enabled || pps->entropy_coding_sync) {

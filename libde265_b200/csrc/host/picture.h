@@ -6,6 +6,7 @@
 #pragma once
 #include <stdint.h>
 #include <stdlib.h>
+#include <atomic>
 #include <memory>
 #include <vector>
 #include "../../../include/b265.h"
@@ -78,11 +79,15 @@ struct RefPic {
   uint64_t decode_index = 0;
   uint64_t uid = 0;                // unique per decoder, never 0: identifies the picture to parse-only clients
   bool is_ref = true, is_lt = false, needed_for_output = false;
+  bool unavailable = false;        // generated in place of a missing reference (8.3.3.2): mid-grey samples, intra motion field;
+                                   // its surface is allocated and filled by the reconstruction thread that first needs it
   int ctx = -1, surface = -1;      // reconstruction context / HBM surface (set by the reconstruction thread)
   void* owner = nullptr;           // decoder that recycles the surface when the last reference drops
   void (*recycle)(void* owner, int ctx, int surface) = nullptr;
-  volatile int parsed = 0;         // motion field complete (set by the parse worker)
-  volatile int failed = 0;
+  // motion field complete: release-stored by the parse worker after motion / slice_refs / ctb_slice are final,
+  // acquire-loaded by the workers of later pictures that use this one as their collocated picture
+  std::atomic<int> parsed{0};
+  std::atomic<int> failed{0};
   int u_w = 0, u_h = 0, ctbs_w = 0, log2_ctb = 4;
   std::vector<MotionInfo> motion;  // per 4x4 unit
   std::vector<uint16_t> ctb_slice; // per CTB: index into slice_refs
@@ -102,6 +107,7 @@ struct Picture {
   int width = 0, height = 0;
   int poc = 0, nal_type = 0, temporal_id = 0;
   int pic_output = 1;
+  bool irap_no_rasl = false;       // IRAP picture with NoRaslOutputFlag: pictures waiting for output leave first (C.5.2.2)
   int64_t pts = 0;
   void* user_data = nullptr;
   uint64_t decode_index = 0;       // position in decoding order

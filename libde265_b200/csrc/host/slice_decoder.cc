@@ -1,5 +1,6 @@
 // slice_decoder.cc — the decoder's instantiation of the slice-data syntax walk (slice_syntax.h) with the
 // CABAC decoding engine, one picture at a time.
+#include <stdio.h>
 #include "slice_syntax.h"
 
 namespace b265h {
@@ -22,8 +23,8 @@ int decode_picture_slices(Picture& pic) {
   }
   // what later pictures need for temporal motion vector prediction
   pic.self->slice_refs = pic.slice_refs;
-  if (err) pic.self->failed = 1;
-  pic.self->parsed = 1;
+  if (err) pic.self->failed.store(1, std::memory_order_relaxed);
+  pic.self->parsed.store(1, std::memory_order_release);
   return err;
 }
 

@@ -467,7 +467,7 @@ bool SliceDec<Eng>::temporal_mv(int xPb, int yPb, int nPbW, int nPbH, int ref_id
   const int cl = (sh.slice_type == SLICE_B && !sh.collocated_from_l0) ? 1 : 0;
   if (sh.collocated_ref_idx >= refs->n[cl]) return false;
   const RefPic* col = pic.ref_pics[refs->slot[cl][sh.collocated_ref_idx]].get();
-  if (!col || col->failed || col->motion.empty() || col->u_w != pic.u_w || col->u_h != pic.u_h) return false;
+  if (!col || col->failed.load(std::memory_order_relaxed) || col->motion.empty() || col->u_w != pic.u_w || col->u_h != pic.u_h) return false;
   const int xBr = xPb + nPbW, yBr = yPb + nPbH;
   if ((yPb >> sps.log2_ctb) == (yBr >> sps.log2_ctb) && yBr < sps.height && xBr < sps.width)
     if (col_mv(*col, xBr, yBr, ref_idx, X, mv)) return true;
@@ -1211,7 +1211,7 @@ int decode_slice_unit(Picture& pic, const SliceUnit& unit, PicDecodeState& st, c
       const int cl = (sh.slice_type == SLICE_B && !sh.collocated_from_l0) ? 1 : 0;
       if (sh.collocated_ref_idx < d.refs->n[cl]) {
         const RefPic* col = pic.ref_pics[d.refs->slot[cl][sh.collocated_ref_idx]].get();
-        while (col && !col->parsed && !col->failed) wait_a_little();
+        while (col && !col->parsed.load(std::memory_order_acquire)) wait_a_little();   // `failed` is published with `parsed`
       }
     }
   }

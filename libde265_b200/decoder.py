@@ -62,6 +62,7 @@ def _bind():
     lib.b265_de265_get_stats.restype = None
     lib.b265_de265_image_job.argtypes = [vp, vp, C.POINTER(L.FrameJob)]
     lib.b265_de265_image_poc.argtypes = [vp]
+    lib.b265_de265_image_starts_cvs.argtypes = [vp]
     lib.de265_get_image_NAL_header.argtypes = [vp, C.POINTER(C.c_int), vp, vp, vp]
     lib.de265_get_image_NAL_header.restype = None
     _bound = True

@@ -24,7 +24,10 @@ def oracle_planes(job, dpb=None):
     pitch = (C.c_int * 3)(w, w // 2, w // 2)
     refs = None
     if job.n_refs:
-        refs = (C.c_void_p * (3 * job.n_refs))(*[p.ctypes.data for i in range(job.n_refs) for p in dpb[job.ref_surfaces[i]]])
+        # a reference the stream never delivered is the mid-grey picture of 8.3.3.2 (decctx.cc:1408-1434)
+        grey = [np.full((h, w), 128, np.uint8), np.full((h // 2, w // 2), 128, np.uint8), np.full((h // 2, w // 2), 128, np.uint8)]
+        pics = [dpb.setdefault(job.ref_surfaces[i], grey) for i in range(job.n_refs)]
+        refs = (C.c_void_p * (3 * job.n_refs))(*[p.ctypes.data for pl in pics for p in pl])
     o.orc_reconstruct_frame(C.byref(job), pp, pitch, refs)
     if job.flags & L.FRAME_DEBLOCK:
         o.orc_deblock(C.byref(job), pp, pitch)
@@ -47,9 +50,7 @@ def parse_and_reconstruct(data, threads=0, max_frames=None):
         if max_frames is not None and len(md5s) >= max_frames:
             return
         job = dec.job_of(img)
-        nal = C.c_int(0)
-        dec.lib.de265_get_image_NAL_header(img, C.byref(nal), None, None, None)
-        if 16 <= nal.value <= 20:   # IDR / BLA: a new coded video sequence, output before anything that follows
+        if dec.lib.b265_de265_image_starts_cvs(img):   # a new coded video sequence, output after everything before it
             group[0] += 1
         order.append((group[0], dec.lib.b265_de265_image_poc(img), len(order)))
         md5s.append([hashlib.md5(p.tobytes()).hexdigest() for p in oracle_planes(job, dpb)])

@@ -70,6 +70,16 @@ NAMED = {
                                     lists_modification=1, weighted_pred=1),
     "gen_pb_reorder_longterm_256x192": dict(seed=50, w=256, h=192, frames=13, inter=1, reorder=1, long_term=1, poc_bits=5,
                                             max_refs=3, tmvp=1, amp=1, slice_ctbs=8),
+    # ---- open GOPs, random access and lost pictures (skipped RASL pictures, generated references) ----
+    "gen_pb_opengop_256x192": dict(seed=51, w=256, h=192, frames=17, inter=1, reorder=1, open_gop=1, max_refs=3, tmvp=1, sao=1),
+    "gen_pb_opengop_cut_256x192": dict(seed=51, w=256, h=192, frames=17, inter=1, reorder=1, open_gop=1, max_refs=3, tmvp=1, sao=1,
+                                       post={"cut_at_cra": 1}),
+    "gen_pb_opengop_eos_256x192": dict(seed=57, w=256, h=192, frames=17, inter=1, reorder=1, open_gop=1, p_cra=0.5, max_refs=3, tmvp=1,
+                                       post={"eos_at_cra": 1}),
+    "gen_p_lost_picture_256x192": dict(seed=53, w=256, h=192, frames=8, inter=1, max_refs=2, tmvp=1, p_islice=0.0,
+                                       post={"drop_picture": 2}),
+    "gen_pb_lost_longterm_256x192": dict(seed=54, w=256, h=192, frames=12, inter=1, long_term=1, poc_bits=4, max_refs=2, tmvp=1,
+                                         post={"drop_picture": 1}),
     "gen_pb_720p": dict(seed=47, w=1280, h=720, frames=4, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_bipred=1,
                         slice_ctbs=200, p_skip=0.5),
 }
@@ -153,9 +163,63 @@ def catalogue():
     return c
 
 
+def split_nals(data):
+    """Annex-B stream -> list of NAL units, each with its start code (and leading zero byte) attached"""
+    import re
+    starts = [m.start() for m in re.finditer(b"\x00\x00\x01", data)]
+    out = []
+    for i, s0 in enumerate(starts):
+        b = s0 - 1 if s0 > 0 and data[s0 - 1] == 0 else s0
+        e = starts[i + 1] if i + 1 < len(starts) else len(data)
+        if i + 1 < len(starts) and data[e - 1] == 0:
+            e -= 1
+        out.append(data[b:e])
+    return out
+
+
+def nal_type(nal):
+    i = nal.index(b"\x00\x00\x01") + 3
+    return (nal[i] >> 1) & 0x3f
+
+
+def first_slice(nal):
+    i = nal.index(b"\x00\x00\x01") + 3
+    return nal_type(nal) < 32 and bool(nal[i + 2] & 0x80)
+
+
+def post_process(data, post):
+    """Stream surgery the generator itself does not do (the reference decoder still judges the result):
+    cut_at_cra   drop every picture before the first CRA: random access into an open GOP, its RASL pictures must be
+                 skipped (decctx.cc:2038-2045) and trailing pictures that still name earlier pictures get generated ones
+    eos_at_cra   an end-of-sequence NAL in front of every CRA picture: NoRaslOutputFlag = 1 in mid-stream
+    drop_picture=k  lose the k-th picture (0-based, decoding order): unavailable-reference concealment (decctx.cc:1408-1434)"""
+    nals = split_nals(data)
+    out, pic, seen_cra = [], -1, False
+    for n in nals:
+        t = nal_type(n)
+        if t < 32 and first_slice(n):
+            pic += 1
+        if t == 21:
+            if "eos_at_cra" in post and first_slice(n):
+                out.append(b"\x00\x00\x01\x48\x01")   # EOS_NUT = 36
+            seen_cra = True
+        if "cut_at_cra" in post and t < 32 and not seen_cra:
+            continue
+        if "drop_picture" in post and t < 32 and pic == post["drop_picture"]:
+            continue
+        out.append(n)
+    return b"".join(out)
+
+
 def generate(name, args, out_dir=OUT):
     path = os.path.join(out_dir, name + ".bin")
+    args = dict(args)
+    post = args.pop("post", None)
     subprocess.run([build_generator(), path] + ["%s=%s" % kv for kv in args.items()], check=True)
+    if post:
+        data = post_process(open(path, "rb").read(), post)
+        open(path, "wb").write(data)
+        args["post"] = post
     md5 = ref_md5(path, args["w"], args["h"])
     json.dump({"width": args["w"], "height": args["h"], "frames": len(md5), "generator": "tools/make_gen_streams.py",
                "args": args, "md5": md5}, open(os.path.join(out_dir, name + ".md5.json"), "w"), indent=0)

@@ -654,6 +654,8 @@ int main(int argc, char** argv) {
   int poc = 0;
   size_t total_pus = 0;
   int anchor = 0, mini = 0;
+  const bool open_gop = cfg.geti("open_gop", 0) != 0;
+  bool rasl_group = false;
   Dpb dpb;
   for (int f = 0; f < frames; f++) {
     Picture pic;
@@ -670,7 +672,18 @@ int main(int argc, char** argv) {
     }
     const bool idr = nal_type == NAL_IDR_W_RADL || nal_type == NAL_IDR_N_LP;
     if (p.reorder && !idr && nal_type != NAL_TRAIL_R) nal_type = NAL_TRAIL_R;   // (no CRA inside a reordered group)
-    if (idr) { poc = 0; anchor = 0; mini = 0; }
+    // open GOP: the anchor of a reordered group becomes a CRA picture (intra, but its reference picture set keeps the
+    // earlier pictures) and the three pictures that precede it in output order become its RASL pictures.  Decoded from
+    // the start they are ordinary pictures; a decoder that starts at the CRA (or meets it after an end-of-sequence NAL)
+    // must skip them.
+    if (idr) rasl_group = false;
+    if (open_gop && p.reorder && p.inter && !idr && f > 0) {
+      if (mini == 0) {
+        rasl_group = rng.chance(cfg.get("p_cra", 0.4));
+        if (rasl_group) nal_type = NAL_CRA;
+      } else if (rasl_group) nal_type = NAL_RASL_R;
+    }
+    if (idr) { poc = 0; anchor = 0; mini = 0; rasl_group = false; }
     else if (!p.reorder) poc++;
     else {   // groups of four pictures decoded as anchor+4, +2, +1, +3 (output order differs from decoding order)
       static const int step[4] = {4, 2, 1, 3};
@@ -682,7 +695,8 @@ int main(int argc, char** argv) {
     // ---- reference picture set of the picture (negative pictures only: decoding order = output order) ----
     SegmentParams rps_params;
     bool pic_tmvp = false;
-    if (p.inter && nal_type == NAL_TRAIL_R) {
+    const bool cra = nal_type == NAL_CRA;
+    if (p.inter && (nal_type == NAL_TRAIL_R || nal_type == NAL_RASL_R || (cra && open_gop))) {
       std::vector<int> pocs;
       for (const auto& r : dpb.pics) pocs.push_back(r->poc);
       std::sort(pocs.begin(), pocs.end(), [](int a, int b) { return a > b; });   // closest first
@@ -706,7 +720,7 @@ int main(int argc, char** argv) {
           for (const auto& r : dpb.pics) same_lsb += ((r->poc ^ q) & (max_lsb - 1)) == 0;
           const int cycle = ((poc & ~(max_lsb - 1)) - (q & ~(max_lsb - 1))) / max_lsb;
           rps_params.lt_lsb[i] = q & (max_lsb - 1);
-          rps_params.lt_used[i] = rng.chance(0.8);
+          rps_params.lt_used[i] = !cra && rng.chance(0.8);
           rps_params.lt_msb_present[i] = same_lsb > 1 || rng.chance(0.4);
           rps_params.lt_msb_delta[i] = cycle - acc;
           if (rps_params.lt_msb_present[i]) acc = cycle;
@@ -720,7 +734,7 @@ int main(int argc, char** argv) {
         if (!must_keep && (rps_params.n_neg >= max_refs + 1 || !rng.chance(0.85))) continue;    // dropped from the DPB
         if (rps_params.n_neg + rps_params.n_lt + n_after >= 6) continue;   // sps_max_dec_pic_buffering_minus1
         rps_params.delta_poc_minus1[rps_params.n_neg] = prev - q - 1;
-        rps_params.used[rps_params.n_neg] = rng.chance(0.8);
+        rps_params.used[rps_params.n_neg] = !cra && rng.chance(0.8);
         rps_params.n_neg++;
         prev = q;
       }
@@ -729,11 +743,11 @@ int main(int argc, char** argv) {
         const int q = *it;
         if (q < poc) continue;
         rps_params.delta_pos_minus1[rps_params.n_pos] = q - prev - 1;
-        rps_params.used_pos[rps_params.n_pos] = rng.chance(0.8);
+        rps_params.used_pos[rps_params.n_pos] = !cra && rng.chance(0.8);
         rps_params.n_pos++;
         prev = q;
       }
-      pic_tmvp = p.tmvp && rng.chance(0.8);
+      pic_tmvp = !cra && p.tmvp && rng.chance(0.8);
     }
     int n_curr = 0;
     for (int i = 0; i < rps_params.n_neg; i++) n_curr += rps_params.used[i];
@@ -812,6 +826,11 @@ int main(int argc, char** argv) {
       sp.tmvp = pic_tmvp;
       if (!sp.dependent && n_curr > 0 && !rng.chance(p_islice)) {
         sp.slice_type = rng.chance(p_bslice) ? SLICE_B : SLICE_P;
+        // Reference quirk kept out of the golden set: for a P slice the reference's collocated-MV rule walks
+        // RefPicList[1] (motion.cc:1189-1197), which a P slice never fills - it reads stale DPB indices, and with output
+        // reordering those can name a picture after the current one, flipping the list the collocated vector is taken
+        // from.  The spec (8.5.3.2.9) and this repo's parser only look at the lists the slice has.
+        if (open_gop && pic_tmvp) sp.slice_type = SLICE_B;
         const int nl = sp.slice_type == SLICE_B ? 2 : 1;
         sp.override_num_ref = rng.chance(0.6);
         for (int l = 0; l < 2; l++) sp.num_ref[l] = sp.override_num_ref ? rng.range(1, std::min(4, n_curr + 1)) : pps->num_ref_idx_default[l];
@@ -872,7 +891,7 @@ int main(int argc, char** argv) {
         unit.hdr.slice_index = n_slices++;
         prev_independent = unit.hdr;
         SliceRefs sr;
-        if (!dpb.build_lists(unit.hdr, pic, sr)) { fprintf(stderr, "streamgen: reference picture missing\n"); return 1; }
+        if (!dpb.build_lists(unit.hdr, pic, sr)) { fprintf(stderr, "streamgen: reference picture missing (frame %d poc %d nal %d, %zu+%zu+%zu in the set, missing %d)\n", f, poc, nal_type, dpb.st_before.size(), dpb.st_after.size(), dpb.lt_curr.size(), (int)dpb.missing); return 1; }
         pic.slice_refs.push_back(sr);
       }
       unit.hdr.data_offset = 0;
@@ -901,7 +920,7 @@ int main(int argc, char** argv) {
       put_nal(stream, nal_type, payload);
     }
     pic.self->slice_refs = pic.slice_refs;
-    pic.self->parsed = 1;
+    pic.self->parsed.store(1, std::memory_order_release);
     total_pus += pic.pus.size();
   }
   if (cfg.geti("verbose", 0)) fprintf(stderr, "streamgen: %d pictures, %zu prediction units\n", frames, total_pus);
