@@ -39,6 +39,14 @@ __device__ __forceinline__ uint8_t ld_relaxed_u8(const uint8_t* p) {
   asm volatile("ld.relaxed.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return (uint8_t)v;
 }
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const void* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(void* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const void* p) {
   unsigned long long v;
   asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
@@ -79,10 +87,11 @@ struct FrameDev {
   int n_tus;
   uint64_t* tb_mask;          // per TU: availability mask of the intra TB's neighbouring units (k_intra_prep)
   int16_t* resid[3];          // residuals of the coded intra TBs (same geometry/pitch as plane[], in samples)
-  uint8_t* done[3];           // per CTB of the plane (raster): 1 = no intra ticket, its samples are final before the wavefront
+  const struct CtbRec* ctb_rec; // per CTB (raster): its TU range and which planes hold intra TBs (built on the host)
+  uint32_t* deps;             // intra wavefront, [3][ctbs_w*ctbs_h]: (notify mask << 8) | unfinished predecessor CTBs (k_intra_sched_prep)
+  int slot_base;              // first (plane, CTB) slot of this picture in batch-wide numbering (trace only)
   uint8_t* mbox[3];           // intra wavefront border mailboxes: per CTB [bottom row S][right column S] as 8-byte words
                               // {4 samples, tag}; zero before the launch, written once by the CTB's warp
-  int done_pitch[3];          // = ctbs_w
   uint8_t* bs;                // boundary strength: per 4x4 luma unit, bits 0-1 vertical edge, 2-3 horizontal
   uint32_t* motion;           // per 4x4 luma unit: 4 words {ref ids, mv0, mv1, flags} rasterised from PUs
   const uint8_t* ref_plane[16][3];
@@ -95,14 +104,20 @@ struct FrameDev {
 // boundary rules sample by sample on the CTB rim, sao.cc:119-164)
 #define B265_SAOREC_FOREIGN 0x80
 
-// one ticket of the intra CTB wavefront: plane `plane` of CTB `ctb` (raster) of frame `frame`; the CTB's
-// TUs are tus[tu_first .. tu_first+tu_count) in decoding order (all planes interleaved)
-#define B265_TICKET_MIXED 1  // the CTB plane also holds samples not produced by this ticket (inter / PCM)
-struct IntraTicket {
-  uint16_t frame;
-  uint8_t plane;
-  uint8_t flags;
-  uint32_t ctb;
+// Intra wavefront work unit = one colour plane of one CTB ("ticket").  The host only states, per CTB, where its TUs are
+// (decoding order, all planes interleaved) and which planes hold intra TBs; dependency counters and the ready queue are
+// built and driven on the device (k_intra.cu).
+struct CtbRec {
   uint32_t tu_first;
-  uint32_t tu_count;
+  uint16_t tu_count;
+  uint8_t has;     // bit c: plane c of this CTB holds intra TBs (= a ticket exists)
+  uint8_t mixed;   // bit c: ... and also samples produced by earlier launches (inter / PCM)
 };
+// control block of one launch of the wavefront (device memory, zeroed before k_intra_sched_prep)
+struct IntraSched {
+  unsigned head;   // next queue slot to hand to a warp
+  unsigned tail;   // next queue slot to fill
+  unsigned done;   // finished tickets
+  unsigned pad;
+};
+#define B265_QUEUE_EXIT 0xffffffffu

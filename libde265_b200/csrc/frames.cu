@@ -1,9 +1,9 @@
 // frames.cu — frame-level C ABI: b265_upload_frames / b265_run_batch / b265_submit_frames.
 //
 // Host work per batch (cheap, linear in the number of TUs): split TUs into the inter-residual lists
-// (by size) and the intra CTB tickets (one per picture/CTB/plane holding intra TBs, counting-sorted by
-// the CTB anti-diagonal wave = ctbX + 2*ctbY); pack every list of every frame into ONE pinned staging
-// buffer and ship it with ONE cudaMemcpyAsync.  Device work: see b265_run_batch.
+// (by size) and note, per CTB, its TU range and which planes hold intra TBs (CtbRec; the wavefront's
+// dependency counters and ready queue are built on the device); pack every list of every frame into
+// ONE pinned staging buffer and ship it with ONE cudaMemcpyAsync.  Device work: see b265_run_batch.
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -24,13 +24,12 @@ struct b265_batch {
   uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};     // inter TUs (residual added in place)
   uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
   int n_res_plain[4] = {0, 0, 0, 0}, n_ires_plain[4] = {0, 0, 0, 0};   // leading part of each list: plain DCT TUs (sizes 16, 32)
-  IntraTicket* d_tickets = nullptr;   int n_tickets = 0;
-  unsigned* d_ticket = nullptr;
-  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // border mailboxes, cleared per run
-  uint8_t* d_done_init = nullptr;     size_t done_bytes = 0;   // per CTB plane: 1 = no intra ticket (read-only)
+  int n_tickets = 0;                  // (plane, CTB) units with intra TBs in the whole batch
+  int max_slots = 0;                  // largest planes * CTBs of a picture (grid of the scheduling pre-pass)
+  IntraSched* d_sched = nullptr;      // wavefront control block and ready queue: inside the zeroed region
+  uint32_t* d_queue = nullptr;
+  uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // control block, queue, border mailboxes: cleared per run
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
-  int max_wave = 0;
-  int wave_width = 0;                 // largest number of tickets in one wave
   int max_pcms = 0;                   // largest PCM block count of a picture
   int max_tus = 0;
   int log2_ctb = 4;                   // largest CTB of the batch (sizes the wavefront's shared-memory tiles)
@@ -70,15 +69,11 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   if (n_jobs > 255) return reject(__LINE__, B265_ERR_INVALID_ARG);
   b->n_frames = n_jobs;
   b->frames.assign(n_jobs, FrameDev());
-  struct Key { uint32_t wave; IntraTicket t; };
-  std::vector<Key> intra;
   std::vector<uint32_t> res[4], ires[4], mc;
   std::vector<uint32_t> n_pieces(n_jobs, 0);
-  std::vector<std::vector<uint8_t>> done_init(n_jobs);   // per frame: 3 planes x nctb, 1 = nothing to wait for
-  std::vector<uint32_t> ctb_first, ctb_count;
-  std::vector<uint8_t> ctb_has;
+  std::vector<std::vector<CtbRec>> ctb_recs(n_jobs);   // per frame, raster order
   std::vector<uint32_t> ctb_area;   // samples covered by intra TBs, per plane and CTB
-  int max_wave = 0;
+  int n_tickets = 0, max_slots = 0;
   // ---- pass 1: classify; TUs arrive in decoding order, so the TUs of one CTB are contiguous ----
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
@@ -86,10 +81,11 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       return reject(__LINE__, B265_ERR_UNSUPPORTED);
     const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
     const int nctb = cw_ * ch_;
-    ctb_first.assign(nctb, 0);
-    ctb_count.assign(nctb, 0);
-    ctb_has.assign(nctb, 0);
+    if (nctb >= (1 << 20)) return reject(__LINE__, B265_ERR_UNSUPPORTED);   // queue entries carry the CTB number in 20 bits
+    std::vector<CtbRec>& recs = ctb_recs[j];
+    recs.assign(nctb, CtbRec{0, 0, 0, 0});
     ctb_area.assign((size_t)3 * nctb, 0);
+    max_slots = std::max(max_slots, (J.chroma_format_idc ? 3 : 1) * nctb);
     b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
     if (J.log2_ctb < 4 || J.log2_ctb > 6) return reject(__LINE__, B265_ERR_INVALID_ARG);
     // FrameDev holds 16 reference slots (a DPB of 16 pictures is the HEVC maximum, A.4.2); slice indices travel in 8 bits
@@ -105,31 +101,29 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       if (bx >= cw_ || by >= ch_) return reject(__LINE__, B265_ERR_INVALID_ARG);
       const int ctb = by * cw_ + bx;
       if (ctb != cur) {
-        if (ctb_count[ctb]) return reject(__LINE__, B265_ERR_INVALID_ARG);  // TUs of a CTB must be contiguous (decoding order)
-        ctb_first[ctb] = (uint32_t)i;
+        if (recs[ctb].tu_count) return reject(__LINE__, B265_ERR_INVALID_ARG);  // TUs of a CTB must be contiguous (decoding order)
+        recs[ctb].tu_first = (uint32_t)i;
         cur = ctb;
       }
-      ctb_count[ctb]++;
+      if (recs[ctb].tu_count == 0xffff) return reject(__LINE__, B265_ERR_INVALID_ARG);
+      recs[ctb].tu_count++;
       if (t.intra_mode != B265_INTRA_NONE) {
-        ctb_has[ctb] |= (uint8_t)(1 << c);
+        if (c && !J.chroma_format_idc) return reject(__LINE__, B265_ERR_INVALID_ARG);
+        recs[ctb].has |= (uint8_t)(1 << c);
         ctb_area[(size_t)c * nctb + ctb] += 1u << (2 * lg);
         if (t.ncoeff > 0) ires[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
       } else if (t.ncoeff > 0) res[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
     }
-    done_init[j].assign((size_t)3 * nctb, 1);
     for (int ctb = 0; ctb < nctb; ctb++) {
-      if (!ctb_has[ctb]) continue;
-      const uint32_t wave = (uint32_t)(ctb % cw_ + 2 * (ctb / cw_));
-      max_wave = std::max<int>(max_wave, (int)wave);
+      if (!recs[ctb].has) continue;
       const int S = 1 << J.log2_ctb;
       const int bw = std::min(S, J.width - (ctb % cw_) * S), bh = std::min(S, J.height - (ctb / cw_) * S);
       for (int c = 0; c < 3; c++)
-        if (ctb_has[ctb] & (1 << c)) {
-          done_init[j][(size_t)c * nctb + ctb] = 0;
+        if (recs[ctb].has & (1 << c)) {
+          n_tickets++;
           // a CTB plane not fully covered by intra TBs also holds inter / PCM samples written by earlier launches
           const uint32_t full = (c && J.chroma_format_idc) ? (uint32_t)(((bw + 1) >> 1) * ((bh + 1) >> 1)) : (uint32_t)(bw * bh);
-          const uint8_t fl = ctb_area[(size_t)c * nctb + ctb] != full ? B265_TICKET_MIXED : 0;
-          intra.push_back({wave, {(uint16_t)j, (uint8_t)c, fl, (uint32_t)ctb, ctb_first[ctb], ctb_count[ctb]}});
+          if (ctb_area[(size_t)c * nctb + ctb] != full) recs[ctb].mixed |= (uint8_t)(1 << c);
         }
     }
     {  // one MC item per 16x16 piece of a prediction block (pu_expand)
@@ -149,17 +143,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
   }
   const double tb1 = t_now();
-  b->max_wave = max_wave;
-  // ---- counting sort of the tickets by wave (stable) ----
-  std::vector<IntraTicket> tickets(intra.size());
-  {
-    std::vector<uint32_t> cnt((size_t)max_wave + 2, 0);
-    for (auto& k : intra) cnt[k.wave + 1]++;
-    for (size_t i = 1; i < cnt.size(); i++) b->wave_width = std::max<int>(b->wave_width, (int)cnt[i]);
-    for (size_t i = 1; i < cnt.size(); i++) cnt[i] += cnt[i - 1];
-    for (auto& k : intra) tickets[cnt[k.wave]++] = k.t;
-  }
-  b->n_tickets = (int)tickets.size();
+  b->n_tickets = n_tickets;
+  b->max_slots = max_slots;
   b->n_mc = (int)mc.size();
   // 16x16 / 32x32 lists: plain DCT TUs first (packed dp2a kernels), transform-skip / bypass TUs after them (generic kernel)
   for (int s = 0; s < 4; s++) {
@@ -182,11 +167,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   for (int s = 0; s < 4; s++) o_res[s] = P.take(4 * res[s].size());
   size_t o_ires[4];
   for (int s = 0; s < 4; s++) o_ires[s] = P.take(4 * ires[s].size());
-  const size_t o_tickets = P.take(sizeof(IntraTicket) * tickets.size());
-  size_t done_total = 0;
-  for (int j = 0; j < n_jobs; j++) done_total += done_init[j].size();
-  const size_t o_done_init = P.take(done_total);
-  struct FOff { size_t tus, coeffs, pus, slices, ctbs, sao, sao_rec, unit, qp, scaling, pcms, pcm_samples; };
+  struct FOff { size_t tus, coeffs, pus, slices, ctbs, ctb_rec, sao, sao_rec, unit, qp, scaling, pcms, pcm_samples; };
   std::vector<FOff> fo(n_jobs);
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
@@ -196,6 +177,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     fo[j].pus = P.take(sizeof(b265_pu) * (size_t)n_pieces[j]);
     fo[j].slices = P.take(sizeof(b265_slice) * (size_t)std::max(1, J.n_slices));
     fo[j].ctbs = J.ctbs ? P.take(sizeof(b265_ctb) * (size_t)nctb) : 0;
+    fo[j].ctb_rec = P.take(sizeof(CtbRec) * (size_t)nctb);
     fo[j].sao = J.sao ? P.take(sizeof(b265_sao) * (size_t)nctb) : 0;
     fo[j].sao_rec = (J.sao && (J.flags & B265_FRAME_SAO)) ? P.take(sizeof(uint2) * 3 * (size_t)nctb) : 0;
     fo[j].unit = J.unit_info ? P.take((size_t)(J.width >> 2) * (J.height >> 2)) : 0;
@@ -206,27 +188,33 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   }
   b->upload_bytes = P.off;
   // device-only scratch after the uploaded part
-  const size_t o_ticket = P.take(256);
   const size_t o_zero = P.off;
-  struct SOff { size_t done[3], tmp[3], motion, resid[3], tb_mask, mbox[3]; int dp[3]; };
+  static int queue_slack = 0;
+  if (!queue_slack) queue_slack = intra_queue_slack(ctx->sm_count);
+  const size_t o_sched = P.take(sizeof(IntraSched));
+  const size_t o_queue = P.take(sizeof(uint32_t) * ((size_t)n_tickets + (size_t)queue_slack));
+  struct SOff { size_t deps, tmp[3], motion, resid[3], tb_mask, mbox[3]; int slot_base; };
   std::vector<SOff> so(n_jobs);
   {
-    size_t acc = 0;
+    int slots = 0;
     for (int j = 0; j < n_jobs; j++) {
       const b265_frame_job& J = jobs[j];
       const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
+      so[j].slot_base = slots;
+      slots += 3 * cw_ * ch_;
       for (int c = 0; c < 3; c++) {
-        so[j].dp[c] = cw_;
-        so[j].done[c] = o_done_init + acc;   // read-only during the run: 1 = no ticket for this CTB plane
-        acc += (size_t)cw_ * ch_;
         // border mailbox of the intra wavefront: per CTB 2*S samples in flag-in-data form (8 B = 4 samples + tag)
         const int S = (1 << J.log2_ctb) >> ((c && J.chroma_format_idc) ? 1 : 0);
-        so[j].mbox[c] = (c == 0 || J.chroma_format_idc) ? P.take((size_t)cw_ * ch_ * 4 * S) : 0;
+        so[j].mbox[c] = (n_tickets && (c == 0 || J.chroma_format_idc)) ? P.take((size_t)cw_ * ch_ * 4 * S) : 0;
       }
     }
   }
   b->zero_bytes = P.off - o_zero;
-  b->done_bytes = done_total;
+  for (int j = 0; j < n_jobs; j++) {   // dependency words: written by k_intra_sched_prep, no clearing needed
+    const b265_frame_job& J = jobs[j];
+    const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
+    so[j].deps = P.take(sizeof(uint32_t) * 3 * (size_t)cw_ * ch_);
+  }
   for (int j = 0; j < n_jobs; j++) {  // SAO needs the deblocked picture kept aside
     const b265_frame_job& J = jobs[j];
     so[j].tmp[0] = so[j].tmp[1] = so[j].tmp[2] = 0;
@@ -278,18 +266,12 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   cp(o_mc, mc.data(), 4 * mc.size());
   for (int s = 0; s < 4; s++) cp(o_res[s], res[s].data(), 4 * res[s].size());
   for (int s = 0; s < 4; s++) cp(o_ires[s], ires[s].data(), 4 * ires[s].size());
-  cp(o_tickets, tickets.data(), sizeof(IntraTicket) * tickets.size());
-  {
-    size_t acc = 0;
-    for (int j = 0; j < n_jobs; j++) { cp(o_done_init + acc, done_init[j].data(), done_init[j].size()); acc += done_init[j].size(); }
-  }
   b->d_frames = (FrameDev*)(D + o_frames);
   b->d_mc_items = (uint32_t*)(D + o_mc);
   for (int s = 0; s < 4; s++) b->d_res_order[s] = (uint32_t*)(D + o_res[s]);
   for (int s = 0; s < 4; s++) b->d_ires_order[s] = (uint32_t*)(D + o_ires[s]);
-  b->d_tickets = (IntraTicket*)(D + o_tickets);
-  b->d_done_init = D + o_done_init;
-  b->d_ticket = (unsigned*)(D + o_ticket);
+  b->d_sched = (IntraSched*)(D + o_sched);
+  b->d_queue = (uint32_t*)(D + o_queue);
   b->d_zero_begin = D + o_zero;
   static const b265_slice default_slice = {0, 2, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, {}, {}};
   for (int j = 0; j < n_jobs; j++) {
@@ -305,6 +287,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     if (J.n_slices > 0) cp(fo[j].slices, J.slices, sizeof(b265_slice) * (size_t)J.n_slices);
     else cp(fo[j].slices, &default_slice, sizeof(b265_slice));
     cp(fo[j].ctbs, J.ctbs, sizeof(b265_ctb) * (size_t)nctb);
+    cp(fo[j].ctb_rec, ctb_recs[j].data(), sizeof(CtbRec) * (size_t)nctb);
     cp(fo[j].sao, J.sao, sizeof(b265_sao) * (size_t)nctb);
     if (J.sao && (J.flags & B265_FRAME_SAO)) sao_records(J, nctb_w, nctb_h, false, reinterpret_cast<uint2*>(H + fo[j].sao_rec));
     cp(fo[j].unit, J.unit_info, (size_t)(J.width >> 2) * (J.height >> 2));
@@ -321,10 +304,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       f.out[c] = S.plane[c];
       f.pitch[c] = S.pitch[c];
       f.plane[c] = (so[j].tmp[c] && (J.flags & B265_FRAME_SAO)) ? D + so[j].tmp[c] : S.plane[c];
-      f.done[c] = D + so[j].done[c];
       f.mbox[c] = so[j].mbox[c] ? D + so[j].mbox[c] : nullptr;
       f.resid[c] = so[j].resid[c] ? (int16_t*)(D + so[j].resid[c]) : nullptr;
-      f.done_pitch[c] = so[j].dp[c];
     }
     f.width = J.width; f.height = J.height;
     f.cw = J.chroma_format_idc ? (J.width + 1) >> 1 : 0;
@@ -338,6 +319,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.pus = (const b265_pu*)(D + fo[j].pus);
     f.slices = (const b265_slice*)(D + fo[j].slices);
     f.ctbs = J.ctbs ? (const b265_ctb*)(D + fo[j].ctbs) : nullptr;
+    f.ctb_rec = (const CtbRec*)(D + fo[j].ctb_rec);
+    f.deps = (uint32_t*)(D + so[j].deps);
+    f.slot_base = so[j].slot_base;
     f.sao = J.sao ? (const b265_sao*)(D + fo[j].sao) : nullptr;
     f.sao_rec = (J.sao && (J.flags & B265_FRAME_SAO)) ? (const uint2*)(D + fo[j].sao_rec) : nullptr;
     f.unit_info = J.unit_info ? D + fo[j].unit : nullptr;
@@ -364,7 +348,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const double tb4 = t_now();
   CK(cudaMemcpyAsync(D, H, b->upload_bytes, cudaMemcpyHostToDevice, ctx->stream));
   if (g_build_timing)
-    fprintf(stderr, "b265 build_batch n=%d: classify %.2f ms, ticket sort %.2f, layout+staging %.2f, copy %.2f, memcpyAsync call %.2f (%.1f MB)\n",
+    fprintf(stderr, "b265 build_batch n=%d: classify %.2f ms, list partition %.2f, layout+staging %.2f, copy %.2f, memcpyAsync call %.2f (%.1f MB)\n",
             n_jobs, (tb1 - tb0) * 1e3, (tb2 - tb1) * 1e3, (tb3 - tb2) * 1e3, (tb4 - tb3) * 1e3, (t_now() - tb4) * 1e3, b->upload_bytes / 1e6);
   return B265_OK;
 }
@@ -415,9 +399,9 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   }
   if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
   if (b->n_tickets) {
-    launch_intra(st, b->d_frames, b->d_tickets, b->n_tickets, b->d_ticket, ctx->sm_count, b->wave_width, b->log2_ctb);
-    ctx->launches++;
-    CK_LAUNCH("k_intra_wavefront");
+    launch_intra(st, b->d_frames, b->n_frames, b->max_slots, b->n_tickets, b->d_sched, b->d_queue, ctx->sm_count, b->log2_ctb);
+    ctx->launches += 2;
+    CK_LAUNCH("k_intra_sched_prep + k_intra_wavefront");
   }
   if (tm) cudaEventRecord(ctx->stage_ev[3], st);
   int r = launch_postfilters(ctx, b->d_frames, b->frames.data(), b->n_frames, tm ? ctx->stage_ev[4] : nullptr,

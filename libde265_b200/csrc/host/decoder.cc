@@ -824,7 +824,7 @@ LIBDE265_API int de265_get_version_number_minor(void) { return (LIBDE265_NUMERIC
 LIBDE265_API int de265_get_version_number_maintenance(void) { return (LIBDE265_NUMERIC_VERSION >> 8) & 0xff; }
 
 LIBDE265_API const char* de265_get_error_text(de265_error err) {
-  switch (err) {
+  switch ((int)err) {
     case DE265_OK: return "no error";
     case DE265_ERROR_NO_SUCH_FILE: return "no such file";
     case DE265_ERROR_COEFFICIENT_OUT_OF_IMAGE_BOUNDS: return "coefficient out of image bounds";

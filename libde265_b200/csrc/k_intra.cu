@@ -15,15 +15,21 @@
 //    memory (intra.cuh), so global memory is read once per CTB (bordering row/column of the neighbouring
 //    CTBs, one L2 round trip after the flag wait) and never per TB.
 //
-// Host side (frames.cu) emits one ticket per (picture, CTB, plane) that contains intra TBs, sorted by
-// wave.  Warps draw tickets from an atomic counter; a warp waits for the (at most four) neighbouring
-// CTB flags of its plane, processes the CTB's TBs in decoding order, then publishes its own flag with a
-// release store.  Every dependency has a smaller ticket, tickets are only held by running warps, so
-// spinning cannot deadlock for any grid size.
+// Scheduling is DATAFLOW, on the device.  A work unit ("ticket") is one colour plane of one CTB that holds intra TBs.
+// k_intra_sched_prep gives every ticket a counter of unfinished predecessor tickets (a reduced set: left and upper-right,
+// plus upper / upper-left only where the chain through the others is broken by a CTB without intra TBs) and pushes the
+// tickets that start at zero into a global ready queue.  A warp that finishes a ticket decrements the counters of the
+// (at most four) tickets that wait for it; it CONTINUES with the first one that became ready - the critical chain of a
+// picture never goes through the queue - and pushes the others.  A warp without work takes a queue slot and sleeps on
+// it, so a warp never holds a ticket it cannot run: blocked CTBs behind a textured one cost nothing, the pictures of a
+// batch fill the machine, and two batches on two streams share it.  The last finisher writes an exit marker into the
+// slots the sleeping warps hold.
 //
 // HBM traffic per TB: N*N bytes written (+ 2*N*N bytes of residual read when the TB is coded).
 #include <stdio.h>
 #include <stdlib.h>
+#include <algorithm>
+#include <vector>
 #include "transform.cuh"
 #include "intra.cuh"
 #include "kernels.h"
@@ -173,7 +179,7 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
 // The polling loop is executed by the WHOLE warp with a warp-uniform exit: a per-lane loop leaves the
 // warp split into independently scheduled groups, which then walk the TBs separately and pay the slow
 // path of every warp collective (measured: 3x).
-__device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges& E, const uint8_t* done, const uint8_t* mbox,
+__device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges& E, const CtbRec* recs, int plane, const uint8_t* mbox,
                                               int ctbs_w, bool interior, unsigned sleep_ns) {
   const int lane = lane_id();
   const int S = E.S, q = S / 4, pitch = g.pitch;
@@ -200,7 +206,7 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
     // not usable for prediction (outside the picture, other slice/tile): never read, never waited for
     if (!((g.nb >> (piece == 0 ? 2 : piece == 1 ? 3 : piece == 2 ? 0 : 1)) & 1)) continue;
     const int nctb = ny * ctbs_w + nx;
-    if (__ldg(done + nctb) == 0) {   // the neighbour posts its borders in this launch
+    if ((__ldg(&recs[nctb].has) >> plane) & 1) {   // the neighbour posts its borders in this launch
       kind[k] = 1;
       src[k] = mbox + (size_t)nctb * (4 * S) + (piece == 2 ? 2 * S : 0) + 8 * w;
     } else if (piece == 2) {
@@ -275,42 +281,76 @@ __device__ __forceinline__ void post_borders(const CtbEdges& E, uint8_t* mbox, i
   }
 }
 
-// TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 8 x uint64 {t_ticket, t_deps, t_tile, t_tbs, t_pub,
-// n_tbs, gather, filter} + 4 more {predict, add+store, globaltimer, sm id}: 12 x uint64 per ticket, SM cycles
+
+// ---- scheduling ------------------------------------------------------------------------------------------
+// queue entry = 1 + (frame << 22 | plane << 20 | ctb); 0 = not filled yet, B265_QUEUE_EXIT = nothing left
+__device__ __forceinline__ uint32_t queue_entry(int frame, int plane, int ctb) {
+  return 1u + (((uint32_t)frame << 22) | ((uint32_t)plane << 20) | (uint32_t)ctb);
+}
+__device__ __forceinline__ void queue_push(IntraSched* sched, uint32_t* queue, uint32_t entry) {
+  const unsigned slot = atomicAdd(&sched->tail, 1u);
+  st_relaxed_u32(queue + slot, entry);
+}
+
+// Dependency word of every ticket: (notify << 8) | count.
+//   count  = predecessor tickets this one waits for: left, upper-right, upper if there is no upper-right ticket, upper-left if
+//            there is neither an upper nor a left ticket (the others are implied: a CTB's left neighbour is always in its set).
+//            Waiting ignores slices and tiles - a CTB that may not be USED for prediction is still earlier in raster order, so
+//            the graph stays acyclic and nothing is lost but a little parallelism in multi-tile pictures.
+//   notify = successor tickets that count this one: bit 0 right, 1 lower-left, 2 lower, 3 lower-right.
+__global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __restrict__ frames, IntraSched* sched, uint32_t* queue) {
+  const FrameDev& f = frames[blockIdx.y];
+  const int nctb = f.ctbs_w * f.ctbs_h, planes = f.cw ? 3 : 1;
+  const CtbRec* __restrict__ recs = f.ctb_rec;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < planes * nctb; i += gridDim.x * blockDim.x) {
+    const int c = i / nctb, ctb = i - c * nctb;
+    const int cx = ctb % f.ctbs_w, cy = ctb / f.ctbs_w;
+    auto has = [&](int dx, int dy) -> bool {
+      const int nx = cx + dx, ny = cy + dy;
+      if (nx < 0 || ny < 0 || nx >= f.ctbs_w || ny >= f.ctbs_h) return false;
+      return (recs[ny * f.ctbs_w + nx].has >> c) & 1;
+    };
+    uint32_t word = 0;
+    if (has(0, 0)) {
+      const bool L = has(-1, 0), UL = has(-1, -1), U = has(0, -1), UR = has(1, -1);
+      const bool R = has(1, 0), DL = has(-1, 1), D = has(0, 1), DR = has(1, 1);
+      const uint32_t count = (uint32_t)L + (uint32_t)UR + (uint32_t)(U && !UR) + (uint32_t)(UL && !U && !L);
+      const uint32_t notify = (uint32_t)R | ((uint32_t)DL << 1) | ((uint32_t)(D && !R) << 2) | ((uint32_t)(DR && !R && !D) << 3);
+      word = (notify << 8) | count;
+      if (count == 0) queue_push(sched, queue, queue_entry(blockIdx.y, c, ctb));
+    }
+    f.deps[i] = word;
+  }
+}
+
+// TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 12 x uint64 {t_start, t_deps, t_borders, t_tbs, t_end, n_tbs, gather,
+// filter, predict, add+store, globaltimer, (how << 32) | sm id}; how: 0 = taken from the queue, 1 = continued
 template <bool TRACE>
 __global__ void __launch_bounds__(INTRA_WARPS * 32, INTRA_MIN_CTAS)
-k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __restrict__ tickets, int n_tickets,
-                  unsigned* __restrict__ ticket, unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
+k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, uint32_t* queue, unsigned n_tickets, unsigned total_warps,
+                  unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ __align__(16) uint8_t s_border[INTRA_WARPS][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
   uint8_t* my_edges = dyn_smem + (size_t)warp * tile_bytes;
-  // Software pipeline over tickets: the next ticket number is drawn while the current CTB is walked, its
-  // record is loaded during the TB loop and its picture constants are loaded before the (slow) release
-  // store of the current CTB, so that none of these round trips sits between two dependent CTBs.
-  // Holding a reserved ticket cannot deadlock: the smallest unfinished ticket is always being processed
-  // (a warp reserves ticket B only while processing a smaller ticket A and then processes B next).
-  unsigned t = 0;
-  if (lane == 0) t = atomicAdd(ticket, 1u);
-  t = __shfl_sync(B265_FULL_MASK, t, 0);
-  IntraTicket tk = {0, 0, 0, 0, 0, 0};
-  if (t < (unsigned)n_tickets) tk = tickets[t];
-  // picture constants of the ticket -> registers (independent loads, one round trip)
+  // picture / plane constants of the current ticket, reloaded only when a queue slot names another picture or plane
   IntraGeom g;
-  int ctbs_w = 1;
+  int ctbs_w = 1, ctbs_h = 1, cur_frame = -1, cur_plane = -1, slot_base = 0;
   const b265_ctb* __restrict__ ctbs = nullptr;
-  const uint8_t* done = nullptr;
+  const CtbRec* __restrict__ recs = nullptr;
+  uint32_t* deps = nullptr;
   uint8_t* mbox = nullptr;
   const uint4* tus4 = nullptr;
   const uint2* masks = nullptr;
-  auto load_constants = [&](const IntraTicket& k) {
-    const FrameDev* __restrict__ f = frames + k.frame;
-    const int c = k.plane;
+  auto load_constants = [&](int frame, int c) {
+    const FrameDev* __restrict__ f = frames + frame;
     const uint32_t fflags = f->flags;
-    ctbs_w = f->ctbs_w;
+    ctbs_w = f->ctbs_w; ctbs_h = f->ctbs_h;
     ctbs = f->ctbs;
-    done = f->done[c];
+    recs = f->ctb_rec;
+    deps = f->deps + (size_t)c * ctbs_w * ctbs_h;
     mbox = f->mbox[c];
+    slot_base = f->slot_base + c * ctbs_w * ctbs_h;
     tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
     masks = reinterpret_cast<const uint2*>(f->tb_mask);
     g.sh = (c && f->cw) ? 1 : 0;
@@ -320,29 +360,58 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     g.unit_info = (fflags & B265_FRAME_CONSTRAINED_INTRA) ? f->unit_info : nullptr;
     g.unit_pitch = g.width >> 2;
     g.strong = (fflags & B265_FRAME_STRONG_INTRA_SMOOTHING) != 0;
+    cur_frame = frame; cur_plane = c;
   };
-  if (t < (unsigned)n_tickets) load_constants(tk);
-  while (t < (unsigned)n_tickets) {
+  bool have = false;       // a ticket to continue with (warp-uniform)
+  int ctb = 0;
+  uint32_t word = 0;       // its dependency word (notify mask in bits 8..11)
+  CtbRec rec = {0, 0, 0, 0};
+  for (;;) {
     long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
     unsigned long long gt0 = 0;
-    int n_tbs = 0;
-    long long acc[4] = {0, 0, 0, 0};
-    long long lacc = 0;
     if (TRACE) {
       tr0 = clock64();
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
     }
-    unsigned t_next = 0;
-    if (lane == 0) t_next = atomicAdd(ticket, 1u);   // consumed after fill_edges
-    const int c = tk.plane;
-    g.cx = tk.ctb % ctbs_w; g.cy = tk.ctb / ctbs_w;
+    const bool continued = have;
+    if (!have) {
+      unsigned slot = 0;
+      if (lane == 0) slot = atomicAdd(&sched->head, 1u);
+      slot = __shfl_sync(B265_FULL_MASK, slot, 0);
+      uint32_t e;
+      unsigned ns = 32;
+      for (;;) {   // sleep on the slot: it is filled in push order, so the first ticket that becomes ready wakes the first sleeper
+        e = ld_relaxed_u32(queue + slot);
+        if (e) break;
+        __nanosleep(ns);
+        if (ns < 1024) ns <<= 1;
+      }
+      if (e == B265_QUEUE_EXIT) return;
+      e -= 1;
+      const int frame = (int)(e >> 22), c = (int)((e >> 20) & 3);
+      ctb = (int)(e & 0xfffffu);
+      if (frame != cur_frame || c != cur_plane) load_constants(frame, c);
+      word = ld_cg_u32(deps + ctb);
+      const uint2 rr = __ldg(reinterpret_cast<const uint2*>(recs + ctb));
+      rec.tu_first = rr.x; rec.tu_count = (uint16_t)(rr.y & 0xffff); rec.has = (uint8_t)(rr.y >> 16); rec.mixed = (uint8_t)(rr.y >> 24);
+    }
+    have = false;
+    const int c = cur_plane;
+    g.cx = ctb % ctbs_w; g.cy = ctb / ctbs_w;
     const int cx = g.cx, cy = g.cy;
+    const uint32_t notify = (word >> 8) & 0xfu;
+    // successor lanes: lane 0 right, 1 lower-left, 2 lower, 3 lower-right; their records travel while this CTB is processed
+    const int sx = cx + ((lane == 0 || lane == 3) ? 1 : (lane == 1 ? -1 : 0)), sy = cy + (lane == 0 ? 0 : 1);
+    const int sctb = sy * ctbs_w + sx;
+    const bool succ = lane < 4 && ((notify >> lane) & 1u);
+    uint2 srec = make_uint2(0, 0);
+    if (succ) srec = __ldg(reinterpret_cast<const uint2*>(recs + sctb));
     // prefetch the first 32 TU records of the CTB while waiting for the neighbours
     uint4 mine = make_uint4(0, 0xff000000u, 0, 0);
     uint2 mymask = make_uint2(0, 0);
-    if ((uint32_t)lane < tk.tu_count) {
-      mine = __ldg(tus4 + tk.tu_first + lane);
-      mymask = __ldg(masks + tk.tu_first + lane);
+    if ((uint32_t)lane < rec.tu_count) {
+      mine = __ldg(tus4 + rec.tu_first + lane);
+      mymask = __ldg(masks + rec.tu_first + lane);
     }
     CtbEdges E;
     E.S = (1 << g.log2_ctb) >> g.sh;
@@ -355,35 +424,31 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
     {
       const int nx = cx + (lane == 3 ? 1 : (lane == 2 || lane == 4 ? 0 : -1)), ny = cy - (lane == 0 || lane == 4 ? 0 : 1);
       const bool exists = lane < 5 && nx >= 0 && ny >= 0 && nx < ctbs_w;
-      b265_ctb rec = {0, 0, 0};
-      if (exists && ctbs) rec = ctbs[ny * ctbs_w + nx];
-      const int my_ts = __shfl_sync(B265_FULL_MASK, rec.addr_ts, 4);
-      const int my_slice = __shfl_sync(B265_FULL_MASK, (int)rec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)rec.tile, 4);
-      const bool usable = exists && lane < 4 && (!ctbs || (rec.slice == my_slice && rec.tile == my_tile_id && rec.addr_ts < my_ts));
+      b265_ctb crec = {0, 0, 0};
+      if (exists && ctbs) crec = ctbs[ny * ctbs_w + nx];
+      const int my_ts = __shfl_sync(B265_FULL_MASK, crec.addr_ts, 4);
+      const int my_slice = __shfl_sync(B265_FULL_MASK, (int)crec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)crec.tile, 4);
+      const bool usable = exists && lane < 4 && (!ctbs || (crec.slice == my_slice && crec.tile == my_tile_id && crec.addr_ts < my_ts));
       g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;
     }
     if (TRACE) tr1 = clock64();
-    fetch_borders(g, E, done, mbox, ctbs_w, (tk.flags & B265_TICKET_MIXED) != 0, sleep_ns);
+    fetch_borders(g, E, recs, c, mbox, ctbs_w, ((rec.mixed >> c) & 1) != 0, sleep_ns);
     if (TRACE) tr2 = clock64();
-    // the next ticket's record travels while the TBs are processed
-    t_next = __shfl_sync(B265_FULL_MASK, t_next, 0);
-    IntraTicket tk_next = {0, 0, 0, 0, 0, 0};
-    if (t_next < (unsigned)n_tickets) tk_next = tickets[t_next];
-    for (uint32_t base = 0; base < tk.tu_count; base += 32) {
+    int n_tbs = 0;
+    long long acc[4] = {0, 0, 0, 0};
+    for (uint32_t base = 0; base < rec.tu_count; base += 32) {
       if (base) {
         mine = make_uint4(0, 0xff000000u, 0, 0);
-        if (base + lane < tk.tu_count) {
-          mine = __ldg(tus4 + tk.tu_first + base + lane);
-          mymask = __ldg(masks + tk.tu_first + base + lane);
+        if (base + lane < rec.tu_count) {
+          mine = __ldg(tus4 + rec.tu_first + base + lane);
+          mymask = __ldg(masks + rec.tu_first + base + lane);
         }
       }
-      const int n_here = min(32u, tk.tu_count - base);
+      const int n_here = min(32u, (uint32_t)rec.tu_count - base);
       // lanes whose TU is an intra TB of this plane
       const bool want = lane < n_here && (mine.y >> 24) != B265_INTRA_NONE && (int)(mine.y & 3) == c;
       unsigned todo = __ballot_sync(B265_FULL_MASK, want);
       while (todo) {
-        long long lc0 = 0;
-        if (TRACE) lc0 = clock64();
         const int src = __ffs(todo) - 1;
         todo &= todo - 1;
         const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
@@ -393,7 +458,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
         const bool coded = (r3 & 0xffff) != 0;
         const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
                            ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
-        if (TRACE) { n_tbs++; lacc += clock64() - lc0; }
+        if (TRACE) n_tbs++;
         switch ((r1 >> 2) & 7) {
           case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
           case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
@@ -403,22 +468,36 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, const IntraTicket* __rest
       }
     }
     if (TRACE) tr3 = clock64();
-    // next ticket's picture constants: issued before the release store so that both round trips overlap
-    uint8_t* my_mbox = mbox;
-    const int my_ctb = (int)tk.ctb;
-    const unsigned t_cur = t;
-    t = t_next;
-    tk = tk_next;
-    if (t < (unsigned)n_tickets) load_constants(tk);
-    // post the borders later CTBs read (the picture itself is complete at the end of the launch)
-    post_borders(E, my_mbox, my_ctb);
+    // post the borders later CTBs read (the picture itself is complete at the end of the launch), then release the successors
+    post_borders(E, mbox, ctb);
+    uint32_t old = 0;
+    if (succ) old = atomicSub(deps + sctb, 1u);
+    else if (lane == 4) old = atomicAdd(&sched->done, 1u);
+    const bool ready = succ && (old & 0xffu) == 1u;
+    const unsigned ready_mask = __ballot_sync(B265_FULL_MASK, ready);
+    const bool last = __shfl_sync(B265_FULL_MASK, old, 4) == n_tickets - 1;
+    const int t_ctb = ctb;
+    if (ready_mask) {   // continue with the first one (right neighbour first: same CTB row), hand the others to sleeping warps
+      const int pick = __ffs(ready_mask) - 1;
+      if (ready && lane != pick) queue_push(sched, queue, queue_entry(cur_frame, c, sctb));
+      ctb = __shfl_sync(B265_FULL_MASK, sctb, pick);
+      word = __shfl_sync(B265_FULL_MASK, old, pick);
+      const uint32_t rx = __shfl_sync(B265_FULL_MASK, srec.x, pick), ry = __shfl_sync(B265_FULL_MASK, srec.y, pick);
+      rec.tu_first = rx; rec.tu_count = (uint16_t)(ry & 0xffff); rec.has = (uint8_t)(ry >> 16); rec.mixed = (uint8_t)(ry >> 24);
+      have = true;
+    } else if (last) {
+      // every ticket is finished: at most total_warps warps sleep or are about to, on distinct slots >= tail
+      const unsigned tail = ld_relaxed_u32(&sched->tail);
+      for (unsigned i = lane; i < total_warps; i += 32) st_relaxed_u32(queue + tail + i, B265_QUEUE_EXIT);
+    }
     if (TRACE && lane == 0) {
       unsigned smid;
       asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-      unsigned long long* o = trace + (size_t)t_cur * 12;
+      unsigned long long* o = trace + (size_t)(slot_base + t_ctb) * 12;
       o[0] = tr0; o[1] = tr1; o[2] = tr2; o[3] = tr3; o[4] = clock64(); o[5] = n_tbs; o[6] = acc[0]; o[7] = acc[1];
-      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = ((unsigned long long)lacc << 16) | smid;
+      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = ((unsigned long long)(continued ? 1 : 0) << 32) | smid;
     }
+    if (last && !have) return;
   }
 }
 
@@ -436,38 +515,55 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb) {
   return per_sm * sm_count;
 }
 
-void launch_intra(cudaStream_t st, const FrameDev* frames, const IntraTicket* tickets, int n_tickets, unsigned* ticket,
-                  int sm_count, int wave_width, int log2_ctb) {
+// queue entries beyond the tickets themselves: one per warp that can be resident (exit markers)
+int intra_queue_slack(int sm_count) { return intra_max_resident_ctas(sm_count, 4) * INTRA_WARPS + 64; }
+
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int n_tickets, IntraSched* sched,
+                  uint32_t* queue, int sm_count, int log2_ctb) {
   if (n_tickets <= 0) return;
   static int max_ctas[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (!max_ctas[log2_ctb & 7]) max_ctas[log2_ctb & 7] = intra_max_resident_ctas(sm_count, log2_ctb);
-  // warps beyond ~3 waves' worth would only poll; keep them off the SMs the working warps run on
-  int want = 3 * wave_width;
-  if (want < 2 * sm_count) want = 2 * sm_count;
-  if (want > n_tickets) want = n_tickets;
-  int ctas = (want + INTRA_WARPS - 1) / INTRA_WARPS;
-  if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
-  cudaMemsetAsync(ticket, 0, sizeof(unsigned), st);
-  static int sleep_ns = -1;
-  if (sleep_ns < 0) {
-    const char* e = getenv("B265_INTRA_SLEEP_NS");
-    sleep_ns = e ? atoi(e) : 100;
+  {
+    int gx = (max_slots + 255) / 256;
+    if (gx > 4 * sm_count) gx = 4 * sm_count;
+    k_intra_sched_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched, queue);
   }
+  // Sleeping warps cost next to nothing, but a grid that fills every CTA slot keeps a second batch (another stream of the
+  // same process) off the SMs until it drains: B265_INTRA_CTAS_PER_SM caps the share of one launch.
+  static int cap_per_sm = -1, sleep_ns = -1;
+  if (cap_per_sm < 0) {
+    const char* e = getenv("B265_INTRA_CTAS_PER_SM");
+    cap_per_sm = e ? atoi(e) : 0;
+    const char* s = getenv("B265_INTRA_SLEEP_NS");
+    sleep_ns = s ? atoi(s) : 100;
+  }
+  int ctas = (n_tickets + INTRA_WARPS - 1) / INTRA_WARPS;
+  if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
+  if (cap_per_sm > 0 && ctas > cap_per_sm * sm_count) ctas = cap_per_sm * sm_count;
+  const unsigned total_warps = (unsigned)ctas * INTRA_WARPS;
   const int tb = tile_bytes_for(log2_ctb);
   static const char* trace_path = getenv("B265_INTRA_TRACE");
-  if (trace_path) {  // developer aid: synchronous, one file per process (last launch wins)
+  if (trace_path) {  // developer aid: synchronous, one file per process (last launch wins); one record per (plane, CTB) slot
     unsigned long long* d = nullptr;
-    cudaMalloc((void**)&d, (size_t)n_tickets * 96);
-    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, tickets, n_tickets, ticket,
-                                                                                     (unsigned)sleep_ns, tb, d);
+    size_t n_slots = 0;
+    {
+      std::vector<FrameDev> h(n_frames);
+      cudaStreamSynchronize(st);
+      cudaMemcpy(h.data(), frames, sizeof(FrameDev) * n_frames, cudaMemcpyDeviceToHost);
+      for (const FrameDev& f : h) n_slots = std::max(n_slots, (size_t)f.slot_base + (size_t)3 * f.ctbs_w * f.ctbs_h);
+    }
+    cudaMalloc((void**)&d, n_slots * 96);
+    cudaMemsetAsync(d, 0, n_slots * 96, st);
+    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, (unsigned)n_tickets,
+                                                                                     total_warps, (unsigned)sleep_ns, tb, d);
     cudaStreamSynchronize(st);
-    unsigned long long* h = (unsigned long long*)malloc((size_t)n_tickets * 96);
-    cudaMemcpy(h, d, (size_t)n_tickets * 96, cudaMemcpyDeviceToHost);
-    if (FILE* fp = fopen(trace_path, "wb")) { fwrite(h, 96, (size_t)n_tickets, fp); fclose(fp); }
+    unsigned long long* h = (unsigned long long*)malloc(n_slots * 96);
+    cudaMemcpy(h, d, n_slots * 96, cudaMemcpyDeviceToHost);
+    if (FILE* fp = fopen(trace_path, "wb")) { fwrite(h, 96, n_slots, fp); fclose(fp); }
     free(h);
     cudaFree(d);
     return;
   }
-  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, tickets, n_tickets, ticket,
-                                                                                    (unsigned)sleep_ns, tb, nullptr);
+  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, (unsigned)n_tickets,
+                                                                                    total_warps, (unsigned)sleep_ns, tb, nullptr);
 }

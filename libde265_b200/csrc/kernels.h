@@ -27,8 +27,11 @@ void launch_interp_blocks(cudaStream_t st, int luma, int n_blocks, int w, int h,
 // availability masks of all intra TBs (k_intra.cu), grid (.., n_frames)
 void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus);
 int intra_max_resident_ctas(int sm_count, int log2_ctb);
-void launch_intra(cudaStream_t st, const FrameDev* frames, const IntraTicket* tickets, int n_tickets,
-                  unsigned* ticket, int sm_count, int wave_width, int log2_ctb);
+// dependency counters + initial ready set (grid over the (plane, CTB) slots of every frame), then the wavefront itself;
+// `queue` has n_tickets + intra_max_resident_ctas() * warps + 64 entries and is zero, `sched` is zero
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int n_tickets, IntraSched* sched,
+                  uint32_t* queue, int sm_count, int log2_ctb);
+int intra_queue_slack(int sm_count);
 struct b265_ctx;
 // bS derivation + deblock V/H + SAO for every frame of a batch (k_postfilter.cu); ev (optional) is
 // recorded between deblocking and SAO for stage timing.
