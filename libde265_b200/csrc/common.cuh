@@ -88,7 +88,7 @@ struct FrameDev {
   uint64_t* tb_mask;          // per TU: availability mask of the intra TB's neighbouring units (k_intra_prep)
   int16_t* resid[3];          // residuals of the coded intra TBs (same geometry/pitch as plane[], in samples)
   const struct CtbRec* ctb_rec; // per CTB (raster): its TU range and which planes hold intra TBs (built on the host)
-  uint32_t* deps;             // intra wavefront, [3][ctbs_w*ctbs_h]: (notify mask << 8) | unfinished predecessor CTBs (k_intra_sched_prep)
+  uint8_t* nbinfo;            // intra wavefront, [3][ctbs_w*ctbs_h]: neighbouring CTBs usable for prediction (k_intra_sched_prep)
   int slot_base;              // first (plane, CTB) slot of this picture in batch-wide numbering (trace only)
   uint8_t* mbox[3];           // intra wavefront border mailboxes: per CTB [bottom row S][right column S] as 8-byte words
                               // {4 samples, tag}; zero before the launch, written once by the CTB's warp
@@ -115,9 +115,10 @@ struct CtbRec {
 };
 // control block of one launch of the wavefront (device memory, zeroed before k_intra_sched_prep)
 struct IntraSched {
-  unsigned head;   // next queue slot to hand to a warp
-  unsigned tail;   // next queue slot to fill
-  unsigned done;   // finished tickets
-  unsigned pad;
+  unsigned head;     // next queue index to hand to a warp
+  unsigned tail;     // next queue index to fill
+  unsigned done;     // finished CTB rows
+  unsigned n_rows;   // CTB rows (per plane and picture) that hold intra TBs
 };
-#define B265_QUEUE_EXIT 0xffffffffu
+#define B265_QUEUE_EXIT 0xffffffffu   // queue payload: nothing left, the warp returns
+#define B265_QUEUE_SKIP 0xfffffffeu   // queue payload: a row without intra TBs

@@ -26,8 +26,10 @@ struct b265_batch {
   int n_res_plain[4] = {0, 0, 0, 0}, n_ires_plain[4] = {0, 0, 0, 0};   // leading part of each list: plain DCT TUs (sizes 16, 32)
   int n_tickets = 0;                  // (plane, CTB) units with intra TBs in the whole batch
   int max_slots = 0;                  // largest planes * CTBs of a picture (grid of the scheduling pre-pass)
-  IntraSched* d_sched = nullptr;      // wavefront control block and ready queue: inside the zeroed region
-  uint32_t* d_queue = nullptr;
+  int max_rows = 0;                   // largest CTB row count of a picture
+  IntraSched* d_sched = nullptr;      // wavefront control block and row queue: inside the zeroed region
+  unsigned long long* d_queue = nullptr;
+  unsigned queue_entries = 0;         // power of two
   uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // control block, queue, border mailboxes: cleared per run
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
   int max_pcms = 0;                   // largest PCM block count of a picture
@@ -73,7 +75,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   std::vector<uint32_t> n_pieces(n_jobs, 0);
   std::vector<std::vector<CtbRec>> ctb_recs(n_jobs);   // per frame, raster order
   std::vector<uint32_t> ctb_area;   // samples covered by intra TBs, per plane and CTB
-  int n_tickets = 0, max_slots = 0;
+  int n_tickets = 0, max_slots = 0, max_rows = 0;
   // ---- pass 1: classify; TUs arrive in decoding order, so the TUs of one CTB are contiguous ----
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
@@ -85,7 +87,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     std::vector<CtbRec>& recs = ctb_recs[j];
     recs.assign(nctb, CtbRec{0, 0, 0, 0});
     ctb_area.assign((size_t)3 * nctb, 0);
+    if (cw_ > 1023 || ch_ > 1023) return reject(__LINE__, B265_ERR_UNSUPPORTED);   // queue entries: 10 bits per CTB coordinate
     max_slots = std::max(max_slots, (J.chroma_format_idc ? 3 : 1) * nctb);
+    max_rows = std::max(max_rows, ch_);
     b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
     if (J.log2_ctb < 4 || J.log2_ctb > 6) return reject(__LINE__, B265_ERR_INVALID_ARG);
     // FrameDev holds 16 reference slots (a DPB of 16 pictures is the HEVC maximum, A.4.2); slice indices travel in 8 bits
@@ -145,6 +149,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const double tb1 = t_now();
   b->n_tickets = n_tickets;
   b->max_slots = max_slots;
+  b->max_rows = max_rows;
   b->n_mc = (int)mc.size();
   // 16x16 / 32x32 lists: plain DCT TUs first (packed dp2a kernels), transform-skip / bypass TUs after them (generic kernel)
   for (int s = 0; s < 4; s++) {
@@ -192,8 +197,11 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   static int queue_slack = 0;
   if (!queue_slack) queue_slack = intra_queue_slack(ctx->sm_count);
   const size_t o_sched = P.take(sizeof(IntraSched));
-  const size_t o_queue = P.take(sizeof(uint32_t) * ((size_t)n_tickets + (size_t)queue_slack));
-  struct SOff { size_t deps, tmp[3], motion, resid[3], tb_mask, mbox[3]; int slot_base; };
+  unsigned queue_entries = 1024;
+  while ((size_t)queue_entries < (size_t)3 * n_jobs * max_rows + (size_t)queue_slack) queue_entries <<= 1;
+  b->queue_entries = queue_entries;
+  const size_t o_queue = P.take(sizeof(unsigned long long) * (size_t)queue_entries);
+  struct SOff { size_t nbinfo, tmp[3], motion, resid[3], tb_mask, mbox[3]; int slot_base; };
   std::vector<SOff> so(n_jobs);
   {
     int slots = 0;
@@ -210,10 +218,10 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
   }
   b->zero_bytes = P.off - o_zero;
-  for (int j = 0; j < n_jobs; j++) {   // dependency words: written by k_intra_sched_prep, no clearing needed
+  for (int j = 0; j < n_jobs; j++) {   // usable-neighbour masks: written by k_intra_sched_prep, no clearing needed
     const b265_frame_job& J = jobs[j];
     const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
-    so[j].deps = P.take(sizeof(uint32_t) * 3 * (size_t)cw_ * ch_);
+    so[j].nbinfo = P.take(3 * (size_t)cw_ * ch_);
   }
   for (int j = 0; j < n_jobs; j++) {  // SAO needs the deblocked picture kept aside
     const b265_frame_job& J = jobs[j];
@@ -271,7 +279,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   for (int s = 0; s < 4; s++) b->d_res_order[s] = (uint32_t*)(D + o_res[s]);
   for (int s = 0; s < 4; s++) b->d_ires_order[s] = (uint32_t*)(D + o_ires[s]);
   b->d_sched = (IntraSched*)(D + o_sched);
-  b->d_queue = (uint32_t*)(D + o_queue);
+  b->d_queue = (unsigned long long*)(D + o_queue);
   b->d_zero_begin = D + o_zero;
   static const b265_slice default_slice = {0, 2, 0, 0, 0, 1, 0, 0, 0, 0, 0, 0, 0, {}, {}};
   for (int j = 0; j < n_jobs; j++) {
@@ -320,7 +328,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.slices = (const b265_slice*)(D + fo[j].slices);
     f.ctbs = J.ctbs ? (const b265_ctb*)(D + fo[j].ctbs) : nullptr;
     f.ctb_rec = (const CtbRec*)(D + fo[j].ctb_rec);
-    f.deps = (uint32_t*)(D + so[j].deps);
+    f.nbinfo = D + so[j].nbinfo;
     f.slot_base = so[j].slot_base;
     f.sao = J.sao ? (const b265_sao*)(D + fo[j].sao) : nullptr;
     f.sao_rec = (J.sao && (J.flags & B265_FRAME_SAO)) ? (const uint2*)(D + fo[j].sao_rec) : nullptr;
@@ -399,7 +407,8 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   }
   if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
   if (b->n_tickets) {
-    launch_intra(st, b->d_frames, b->n_frames, b->max_slots, b->n_tickets, b->d_sched, b->d_queue, ctx->sm_count, b->log2_ctb);
+    launch_intra(st, b->d_frames, b->n_frames, b->max_slots, b->max_rows, b->n_tickets, b->d_sched, b->d_queue, b->queue_entries,
+                 ctx->sm_count, b->log2_ctb);
     ctx->launches += 2;
     CK_LAUNCH("k_intra_sched_prep + k_intra_wavefront");
   }

@@ -15,15 +15,17 @@
 //    memory (intra.cuh), so global memory is read once per CTB (bordering row/column of the neighbouring
 //    CTBs, one L2 round trip after the flag wait) and never per TB.
 //
-// Scheduling is DATAFLOW, on the device.  A work unit ("ticket") is one colour plane of one CTB that holds intra TBs.
-// k_intra_sched_prep gives every ticket a counter of unfinished predecessor tickets (a reduced set: left and upper-right,
-// plus upper / upper-left only where the chain through the others is broken by a CTB without intra TBs) and pushes the
-// tickets that start at zero into a global ready queue.  A warp that finishes a ticket decrements the counters of the
-// (at most four) tickets that wait for it; it CONTINUES with the first one that became ready - the critical chain of a
-// picture never goes through the queue - and pushes the others.  A warp without work takes a queue slot and sleeps on
-// it, so a warp never holds a ticket it cannot run: blocked CTBs behind a textured one cost nothing, the pictures of a
-// batch fill the machine, and two batches on two streams share it.  The last finisher writes an exit marker into the
-// slots the sleeping warps hold.
+// Scheduling (all on the device): the unit of work is one CTB ROW of one colour plane of one picture, walked left to right
+// by one warp (the shape of HEVC's own wavefront parallel processing).  Inside a row nothing is exchanged through memory:
+// the right column, the corner and the upper-right row piece of the CTB just finished ARE the left column, the corner and
+// the upper row piece of the next one, so they are moved inside the warp's shared-memory edge store.  Between rows the
+// bottom row of every CTB travels through a flag-in-data mailbox (below); a row needs the CTB above-right of its position,
+// i.e. it trails the row above by two CTBs, and the words it needs next are requested one CTB ahead.
+// Rows sit in a ring-buffer queue (row-major over the pictures of the batch).  A warp takes a row and runs it to the end;
+// when the row above is not far enough AND other rows are waiting in the queue, the warp puts its row (with the column
+// it reached) back at the end of the queue and takes another one, so blocked rows behind a textured CTB do not hold the
+// machine while other pictures have work; with nothing else to do it just keeps polling (lowest latency for a lone
+// picture).  (The give-back threshold is a launch parameter, B265_INTRA_YIELD_POLLS; measured best on B200: never.)  No dependency counters, no atomics and no fences on the path between two dependent CTBs.
 //
 // HBM traffic per TB: N*N bytes written (+ 2*N*N bytes of residual read when the TB is coded).
 #include <stdio.h>
@@ -168,19 +170,54 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
   }
 }
 
-// ---- border exchange between CTBs: flag-in-data mailboxes ---------------------------------------------
+
+// ---- border exchange between CTB rows: flag-in-data mailboxes --------------------------------------------
 // A CTB's warp posts the CTB's bottom row and right column (the only samples later CTBs can read) as
 // 8-byte words {4 samples, tag != 0} written with ONE 64-bit store each: a reader that sees the tag has
 // the samples, so neither side needs a fence (the scheme of low-latency collective protocols).  The
 // mailboxes are zeroed before the launch.  Layout per CTB: S/4 words bottom row, S/4 words right column.
-// Neighbours without a ticket (inter/PCM CTBs, done[] == 1) were finished by earlier launches: their
-// samples are read from the plane.
+// Neighbours without intra TBs (inter/PCM CTBs) were finished by earlier launches: their samples are read
+// from the plane.  The right column is only read back when a row is resumed by another warp.
 //
 // The polling loop is executed by the WHOLE warp with a warp-uniform exit: a per-lane loop leaves the
 // warp split into independently scheduled groups, which then walk the TBs separately and pay the slow
 // path of every warp collective (measured: 3x).
-__device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges& E, const CtbRec* recs, int plane, const uint8_t* mbox,
-                                              int ctbs_w, bool interior, unsigned sleep_ns) {
+
+// mailbox word `lane - q` of the upper-right neighbour's bottom row, requested ahead of time by the lanes that will consume it
+__device__ __forceinline__ unsigned long long prefetch_upper_right(const uint8_t* mbox, int S, int ctbs_w, int cx, int cy) {
+  const int lane = lane_id(), q = S / 4;
+  unsigned long long v = 0;
+  if (cy > 0 && cx + 1 < ctbs_w && lane >= q && lane < 2 * q)
+    v = ld_relaxed_u64(mbox + (size_t)((cy - 1) * ctbs_w + cx + 1) * (4 * S) + 8 * (lane - q));
+  return v;
+}
+
+// Inside a row: the finished CTB's right column, the corner above it and the upper-right row piece become the next CTB's
+// left column, corner and upper row piece (all inside the edge store).
+__device__ __forceinline__ void shift_edges(const CtbEdges& E) {
+  const int lane = lane_id();
+  const int S = E.S, q = S / 4;
+  uint32_t top = 0, left = 0;
+  const uint8_t corner = E.rows[16 + S - 1];
+  if (lane < q) {
+    top = *reinterpret_cast<const uint32_t*>(E.rows + 16 + S + 4 * lane);
+    left = *reinterpret_cast<const uint32_t*>(E.cols + q * S + 4 * lane);
+  }
+  __syncwarp();
+  if (lane < q) {
+    *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * lane) = top;
+    *reinterpret_cast<uint32_t*>(E.cols + 4 * lane) = left;
+    E.rows[(lane + 1) * E.rstride + 15] = (uint8_t)(left >> 24);   // sample (-1, 4w+3) of the inner edge rows
+  }
+  if (lane == 0) E.rows[15] = corner;
+}
+
+// Borders of the CTB at (g.cx, g.cy) into the edge store.  reuse: everything but the upper-right piece is already there
+// (shift_edges).  pre: prefetch_upper_right() of this CTB.  Returns false when the neighbours have not posted after
+// `yield_polls` polls while other rows wait in the queue: the caller gives the row back.
+__device__ __forceinline__ bool fetch_borders(const IntraGeom& g, const CtbEdges& E, const CtbRec* recs, int plane, const uint8_t* mbox,
+                                              int ctbs_w, bool interior, bool reuse, unsigned long long pre, const IntraSched* sched,
+                                              unsigned sleep_ns, unsigned yield_polls) {
   const int lane = lane_id();
   const int S = E.S, q = S / 4, pitch = g.pitch;
   const int W = (g.width + g.sh) >> g.sh, H = (g.height + g.sh) >> g.sh;
@@ -191,7 +228,7 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   int kind[2];   // 0 nothing, 1 mailbox word, 2 plane (row word), 3 plane (column word, 4 strided bytes), 4 plane corner byte
   int slotv[2];
   const int lq = g.log2_ctb - g.sh - 2;   // q = 1 << lq
-  const bool two = 3 * q >= 32;           // more than 32 slots: only for 64-sample CTB planes
+  const bool two = !reuse && 3 * q >= 32; // more than 32 slots: only for 64-sample CTB planes
 #pragma unroll
   for (int k = 0; k < 2; k++) {
     const int slot = lane + 32 * k;
@@ -201,6 +238,7 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
     if (k == 1 && !two) break;   // warp-uniform
     if (slot > 3 * q) continue;
     const int piece = slot >> lq, w = slot == 3 * q ? q - 1 : slot & (q - 1);
+    if (reuse && piece != 1) continue;
     // neighbour CTB of the piece
     const int nx = g.cx + (piece == 1 ? 1 : (piece == 0 ? 0 : -1)), ny = g.cy - (piece == 2 ? 0 : 1);
     // not usable for prediction (outside the picture, other slice/tile): never read, never waited for
@@ -220,6 +258,8 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   }
   uint32_t val[2] = {0, 0};
   bool have[2] = {kind[0] != 1, kind[1] != 1};
+  // the word requested one CTB ahead (same lane, slot [q,2q) is always slot 0 of its lane)
+  if (kind[0] == 1 && lane >= q && lane < 2 * q && (uint32_t)(pre >> 32) != 0) { val[0] = (uint32_t)pre; have[0] = true; }
   // plane reads (rare: mixed pictures)
 #pragma unroll
   for (int k = 0; k < 2; k++) {
@@ -231,15 +271,23 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
   }
   // every lane polls its own word(s): restricting the polling to one lane per neighbour, or pausing longer
   // between polls, was measured slower at every batch size (the wavefront is bound by detection latency)
-  for (;;) {
+  unsigned polls = 0;
+  while (!__all_sync(B265_FULL_MASK, have[0] && have[1])) {
+    if (polls) {
+      if (polls >= yield_polls) {   // warp-uniform: is another row waiting for a warp?
+        const unsigned hd = ld_relaxed_u32(&sched->head), tl = ld_relaxed_u32(&sched->tail);
+        if ((int)(tl - hd) > 0) return false;
+        polls = 1;
+      }
+      if (sleep_ns) __nanosleep(sleep_ns);
+    }
+    polls++;
 #pragma unroll
     for (int k = 0; k < 2; k++)
       if (!have[k] && (k == 0 || two)) {
         const unsigned long long v = ld_relaxed_u64(src[k]);
         if ((uint32_t)(v >> 32) != 0) { val[k] = (uint32_t)v; have[k] = true; }
       }
-    if (__all_sync(B265_FULL_MASK, have[0] && have[1])) break;
-    if (sleep_ns) __nanosleep(sleep_ns);
   }
   // into the edge store
 #pragma unroll
@@ -268,6 +316,7 @@ __device__ __forceinline__ void fetch_borders(const IntraGeom& g, const CtbEdges
     }
   }
   __syncwarp();
+  return true;
 }
 
 // post this CTB's bottom row and right column (edge store rows[S/4], cols[S/4]) to its mailbox
@@ -281,76 +330,93 @@ __device__ __forceinline__ void post_borders(const CtbEdges& E, uint8_t* mbox, i
   }
 }
 
-
 // ---- scheduling ------------------------------------------------------------------------------------------
-// queue entry = 1 + (frame << 22 | plane << 20 | ctb); 0 = not filled yet, B265_QUEUE_EXIT = nothing left
-__device__ __forceinline__ uint32_t queue_entry(int frame, int plane, int ctb) {
-  return 1u + (((uint32_t)frame << 22) | ((uint32_t)plane << 20) | (uint32_t)ctb);
+// Ring-buffer queue of CTB rows.  Entry i lives in queue[i & (entries - 1)] as {payload, i + 1}: a warp that took index i
+// sleeps until the tag is i + 1.  payload = frame << 22 | plane << 20 | row << 10 | first column still to do.
+__device__ __forceinline__ uint32_t row_payload(int frame, int plane, int row, int col) {
+  return ((uint32_t)frame << 22) | ((uint32_t)plane << 20) | ((uint32_t)row << 10) | (uint32_t)col;
 }
-__device__ __forceinline__ void queue_push(IntraSched* sched, uint32_t* queue, uint32_t entry) {
-  const unsigned slot = atomicAdd(&sched->tail, 1u);
-  st_relaxed_u32(queue + slot, entry);
+__device__ __forceinline__ void queue_put(unsigned long long* queue, unsigned mask, unsigned idx, uint32_t payload) {
+  st_relaxed_u64(queue + (idx & mask), ((unsigned long long)(idx + 1u) << 32) | payload);
 }
 
-// Dependency word of every ticket: (notify << 8) | count.
-//   count  = predecessor tickets this one waits for: left, upper-right, upper if there is no upper-right ticket, upper-left if
-//            there is neither an upper nor a left ticket (the others are implied: a CTB's left neighbour is always in its set).
-//            Waiting ignores slices and tiles - a CTB that may not be USED for prediction is still earlier in raster order, so
-//            the graph stays acyclic and nothing is lost but a little parallelism in multi-tile pictures.
-//   notify = successor tickets that count this one: bit 0 right, 1 lower-left, 2 lower, 3 lower-right.
-__global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __restrict__ frames, IntraSched* sched, uint32_t* queue) {
+// Per (plane, CTB) slot: which neighbouring CTBs may be used for prediction (same slice, same tile, earlier in decoding
+// order; intrapred.cc:486-508): bit0 left, bit1 upper-left, bit2 upper, bit3 upper-right.  The thread of a row's first CTB
+// also enters the row into the queue at its row-major position (row, frame, plane): early rows of all pictures first.
+__global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __restrict__ frames, IntraSched* sched, unsigned long long* queue,
+                                                          unsigned qmask, int max_rows) {
   const FrameDev& f = frames[blockIdx.y];
   const int nctb = f.ctbs_w * f.ctbs_h, planes = f.cw ? 3 : 1;
   const CtbRec* __restrict__ recs = f.ctb_rec;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < planes * nctb; i += gridDim.x * blockDim.x) {
-    const int c = i / nctb, ctb = i - c * nctb;
-    const int cx = ctb % f.ctbs_w, cy = ctb / f.ctbs_w;
-    auto has = [&](int dx, int dy) -> bool {
-      const int nx = cx + dx, ny = cy + dy;
-      if (nx < 0 || ny < 0 || nx >= f.ctbs_w || ny >= f.ctbs_h) return false;
-      return (recs[ny * f.ctbs_w + nx].has >> c) & 1;
-    };
-    uint32_t word = 0;
-    if (has(0, 0)) {
-      const bool L = has(-1, 0), UL = has(-1, -1), U = has(0, -1), UR = has(1, -1);
-      const bool R = has(1, 0), DL = has(-1, 1), D = has(0, 1), DR = has(1, 1);
-      const uint32_t count = (uint32_t)L + (uint32_t)UR + (uint32_t)(U && !UR) + (uint32_t)(UL && !U && !L);
-      const uint32_t notify = (uint32_t)R | ((uint32_t)DL << 1) | ((uint32_t)(D && !R) << 2) | ((uint32_t)(DR && !R && !D) << 3);
-      word = (notify << 8) | count;
-      if (count == 0) queue_push(sched, queue, queue_entry(blockIdx.y, c, ctb));
+  const b265_ctb* __restrict__ ctbs = f.ctbs;
+  const int n_frames = gridDim.y;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) sched->tail = (unsigned)(3 * n_frames * max_rows);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * max(nctb, max_rows); i += gridDim.x * blockDim.x) {
+    if (i < planes * nctb) {
+      const int c = i / nctb, ctb = i - c * nctb;
+      const int cx = ctb % f.ctbs_w, cy = ctb / f.ctbs_w;
+      uint32_t nb = 0;
+      if ((recs[ctb].has >> c) & 1) {
+        const b265_ctb me = ctbs ? ctbs[ctb] : b265_ctb{0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {  // left, upper-left, upper, upper-right
+          const int nx = cx + (k == 3 ? 1 : (k == 2 ? 0 : -1)), ny = cy - (k == 0 ? 0 : 1);
+          if (nx < 0 || ny < 0 || nx >= f.ctbs_w) continue;
+          bool ok = true;
+          if (ctbs) {
+            const b265_ctb r = ctbs[ny * f.ctbs_w + nx];
+            ok = r.slice == me.slice && r.tile == me.tile && r.addr_ts < me.addr_ts;
+          }
+          if (ok) nb |= 1u << k;
+        }
+      }
+      f.nbinfo[i] = (uint8_t)nb;
     }
-    f.deps[i] = word;
+    // rows: slot i < 3 * max_rows is (plane, row) = (i / max_rows, i % max_rows)
+    if (i < 3 * max_rows) {
+      const int c = i / max_rows, row = i - c * max_rows;
+      uint32_t payload = B265_QUEUE_SKIP;
+      if (c < planes && row < f.ctbs_h) {
+        for (int cx = 0; cx < f.ctbs_w; cx++)
+          if ((recs[row * f.ctbs_w + cx].has >> c) & 1) {
+            payload = row_payload(blockIdx.y, c, row, cx);
+            atomicAdd(&sched->n_rows, 1u);
+            break;
+          }
+      }
+      queue_put(queue, qmask, (unsigned)((row * n_frames + (int)blockIdx.y) * 3 + c), payload);
+    }
   }
 }
 
-// TRACE (developer aid, B265_INTRA_TRACE=<file>): per ticket 12 x uint64 {t_start, t_deps, t_borders, t_tbs, t_end, n_tbs, gather,
-// filter, predict, add+store, globaltimer, (how << 32) | sm id}; how: 0 = taken from the queue, 1 = continued
+// TRACE (developer aid, B265_INTRA_TRACE=<file>): per (plane, CTB) slot 12 x uint64 {t_start, t_setup, t_borders, t_tbs, t_end,
+// n_tbs, gather, filter, predict, add+store, globaltimer, (how << 32) | sm id}; how: 0 = first CTB after taking the row from the
+// queue, 1 = next CTB of the row with the edge store reused, 2 = next CTB with a full border fetch
 template <bool TRACE>
 __global__ void __launch_bounds__(INTRA_WARPS * 32, INTRA_MIN_CTAS)
-k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, uint32_t* queue, unsigned n_tickets, unsigned total_warps,
-                  unsigned sleep_ns, int tile_bytes, unsigned long long* trace) {
+k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsigned long long* queue, unsigned qmask, unsigned total_warps,
+                  unsigned sleep_ns, unsigned yield_polls, int tile_bytes, unsigned long long* trace) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ __align__(16) uint8_t s_border[INTRA_WARPS][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
   uint8_t* my_edges = dyn_smem + (size_t)warp * tile_bytes;
-  // picture / plane constants of the current ticket, reloaded only when a queue slot names another picture or plane
+  const unsigned n_rows = ld_cg_u32(&sched->n_rows);
+  // picture / plane constants of the current row, reloaded only when a queue entry names another picture or plane
   IntraGeom g;
-  int ctbs_w = 1, ctbs_h = 1, cur_frame = -1, cur_plane = -1, slot_base = 0;
-  const b265_ctb* __restrict__ ctbs = nullptr;
+  int ctbs_w = 1, cur_frame = -1, cur_plane = -1, slot_base = 0;
   const CtbRec* __restrict__ recs = nullptr;
-  uint32_t* deps = nullptr;
+  const uint8_t* __restrict__ nbinfo = nullptr;
   uint8_t* mbox = nullptr;
   const uint4* tus4 = nullptr;
   const uint2* masks = nullptr;
   auto load_constants = [&](int frame, int c) {
     const FrameDev* __restrict__ f = frames + frame;
     const uint32_t fflags = f->flags;
-    ctbs_w = f->ctbs_w; ctbs_h = f->ctbs_h;
-    ctbs = f->ctbs;
+    ctbs_w = f->ctbs_w;
     recs = f->ctb_rec;
-    deps = f->deps + (size_t)c * ctbs_w * ctbs_h;
+    nbinfo = f->nbinfo + (size_t)c * ctbs_w * f->ctbs_h;
     mbox = f->mbox[c];
-    slot_base = f->slot_base + c * ctbs_w * ctbs_h;
+    slot_base = f->slot_base + c * ctbs_w * f->ctbs_h;
     tus4 = reinterpret_cast<const uint4*>(f->tus);  // 16-byte records, 256-byte aligned list
     masks = reinterpret_cast<const uint2*>(f->tb_mask);
     g.sh = (c && f->cw) ? 1 : 0;
@@ -362,142 +428,145 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, uint32
     g.strong = (fflags & B265_FRAME_STRONG_INTRA_SMOOTHING) != 0;
     cur_frame = frame; cur_plane = c;
   };
-  bool have = false;       // a ticket to continue with (warp-uniform)
-  int ctb = 0;
-  uint32_t word = 0;       // its dependency word (notify mask in bits 8..11)
-  CtbRec rec = {0, 0, 0, 0};
   for (;;) {
-    long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
-    unsigned long long gt0 = 0;
-    if (TRACE) {
-      tr0 = clock64();
-      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
-    }
-    const bool continued = have;
-    if (!have) {
-      unsigned slot = 0;
-      if (lane == 0) slot = atomicAdd(&sched->head, 1u);
-      slot = __shfl_sync(B265_FULL_MASK, slot, 0);
-      uint32_t e;
+    // ---- take a row ----
+    unsigned idx = 0;
+    if (lane == 0) idx = atomicAdd(&sched->head, 1u);
+    idx = __shfl_sync(B265_FULL_MASK, idx, 0);
+    uint32_t payload;
+    {
       unsigned ns = 32;
-      for (;;) {   // sleep on the slot: it is filled in push order, so the first ticket that becomes ready wakes the first sleeper
-        e = ld_relaxed_u32(queue + slot);
-        if (e) break;
+      for (;;) {   // sleep on the entry: entries are filled in index order, so the first row that is put back wakes the first sleeper
+        const unsigned long long e = ld_relaxed_u64(queue + (idx & qmask));
+        if ((uint32_t)(e >> 32) == idx + 1u) { payload = (uint32_t)e; break; }
         __nanosleep(ns);
         if (ns < 1024) ns <<= 1;
       }
-      if (e == B265_QUEUE_EXIT) return;
-      e -= 1;
-      const int frame = (int)(e >> 22), c = (int)((e >> 20) & 3);
-      ctb = (int)(e & 0xfffffu);
-      if (frame != cur_frame || c != cur_plane) load_constants(frame, c);
-      word = ld_cg_u32(deps + ctb);
-      const uint2 rr = __ldg(reinterpret_cast<const uint2*>(recs + ctb));
-      rec.tu_first = rr.x; rec.tu_count = (uint16_t)(rr.y & 0xffff); rec.has = (uint8_t)(rr.y >> 16); rec.mixed = (uint8_t)(rr.y >> 24);
     }
-    have = false;
-    const int c = cur_plane;
-    g.cx = ctb % ctbs_w; g.cy = ctb / ctbs_w;
-    const int cx = g.cx, cy = g.cy;
-    const uint32_t notify = (word >> 8) & 0xfu;
-    // successor lanes: lane 0 right, 1 lower-left, 2 lower, 3 lower-right; their records travel while this CTB is processed
-    const int sx = cx + ((lane == 0 || lane == 3) ? 1 : (lane == 1 ? -1 : 0)), sy = cy + (lane == 0 ? 0 : 1);
-    const int sctb = sy * ctbs_w + sx;
-    const bool succ = lane < 4 && ((notify >> lane) & 1u);
-    uint2 srec = make_uint2(0, 0);
-    if (succ) srec = __ldg(reinterpret_cast<const uint2*>(recs + sctb));
-    // prefetch the first 32 TU records of the CTB while waiting for the neighbours
-    uint4 mine = make_uint4(0, 0xff000000u, 0, 0);
-    uint2 mymask = make_uint2(0, 0);
-    if ((uint32_t)lane < rec.tu_count) {
-      mine = __ldg(tus4 + rec.tu_first + lane);
-      mymask = __ldg(masks + rec.tu_first + lane);
-    }
+    if (payload == B265_QUEUE_EXIT) return;
+    if (payload == B265_QUEUE_SKIP) continue;
+    const int frame = (int)(payload >> 22), c = (int)((payload >> 20) & 3), row = (int)((payload >> 10) & 0x3ff);
+    int cx = (int)(payload & 0x3ff);
+    if (frame != cur_frame || c != cur_plane) load_constants(frame, c);
     CtbEdges E;
     E.S = (1 << g.log2_ctb) >> g.sh;
     E.rstride = 2 * E.S + 16;
     E.rows = my_edges;
     E.cols = my_edges + (E.S / 4 + 1) * E.rstride;
-    E.x0 = cx * E.S;
-    E.y0 = cy * E.S;
-    // neighbouring CTBs usable for prediction: lane 0 left, 1 upper-left, 2 upper, 3 upper-right; lane 4 = this CTB
-    {
-      const int nx = cx + (lane == 3 ? 1 : (lane == 2 || lane == 4 ? 0 : -1)), ny = cy - (lane == 0 || lane == 4 ? 0 : 1);
-      const bool exists = lane < 5 && nx >= 0 && ny >= 0 && nx < ctbs_w;
-      b265_ctb crec = {0, 0, 0};
-      if (exists && ctbs) crec = ctbs[ny * ctbs_w + nx];
-      const int my_ts = __shfl_sync(B265_FULL_MASK, crec.addr_ts, 4);
-      const int my_slice = __shfl_sync(B265_FULL_MASK, (int)crec.slice, 4), my_tile_id = __shfl_sync(B265_FULL_MASK, (int)crec.tile, 4);
-      const bool usable = exists && lane < 4 && (!ctbs || (crec.slice == my_slice && crec.tile == my_tile_id && crec.addr_ts < my_ts));
-      g.nb = __ballot_sync(B265_FULL_MASK, usable) & 0xfu;
-    }
-    if (TRACE) tr1 = clock64();
-    fetch_borders(g, E, recs, c, mbox, ctbs_w, ((rec.mixed >> c) & 1) != 0, sleep_ns);
-    if (TRACE) tr2 = clock64();
-    int n_tbs = 0;
-    long long acc[4] = {0, 0, 0, 0};
-    for (uint32_t base = 0; base < rec.tu_count; base += 32) {
-      if (base) {
-        mine = make_uint4(0, 0xff000000u, 0, 0);
-        if (base + lane < rec.tu_count) {
-          mine = __ldg(tus4 + rec.tu_first + base + lane);
-          mymask = __ldg(masks + rec.tu_first + base + lane);
-        }
+    E.y0 = row * E.S;
+    g.cy = row;
+    const CtbRec* __restrict__ row_recs = recs + row * ctbs_w;
+    const uint8_t* __restrict__ row_nb = nbinfo + row * ctbs_w;
+    // record + neighbour mask of the CTB about to be processed (requested one CTB ahead inside the loop)
+    uint2 rr = __ldg(reinterpret_cast<const uint2*>(row_recs + cx));
+    uint32_t nb = __ldg(row_nb + cx);
+    unsigned long long pre = prefetch_upper_right(mbox, E.S, ctbs_w, cx, row);
+    bool chained = false;      // the previous CTB of the row was processed by this warp just now (edge store still holds it)
+    uint32_t nb_prev = 0;
+    bool yielded = false;
+    while (cx < ctbs_w) {
+      const uint32_t has = (rr.y >> 16) & 0xff;
+      // next CTB's record, neighbour mask and upper-right mailbox words travel while this one is processed
+      uint2 rr_next = make_uint2(0, 0);
+      uint32_t nb_next = 0;
+      unsigned long long pre_next = 0;
+      if (cx + 1 < ctbs_w) {
+        rr_next = __ldg(reinterpret_cast<const uint2*>(row_recs + cx + 1));
+        nb_next = __ldg(row_nb + cx + 1);
+        pre_next = prefetch_upper_right(mbox, E.S, ctbs_w, cx + 1, row);
       }
-      const int n_here = min(32u, (uint32_t)rec.tu_count - base);
-      // lanes whose TU is an intra TB of this plane
-      const bool want = lane < n_here && (mine.y >> 24) != B265_INTRA_NONE && (int)(mine.y & 3) == c;
-      unsigned todo = __ballot_sync(B265_FULL_MASK, want);
-      while (todo) {
-        const int src = __ffs(todo) - 1;
-        todo &= todo - 1;
-        const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
-        const uint32_t r3 = __shfl_sync(B265_FULL_MASK, mine.w, src);
-        const int x = (int)(r0 & 0xffff), y = (int)(r0 >> 16);
-        const int flags = (int)((r1 >> 8) & 0xff), mode = (int)(r1 >> 24);
-        const bool coded = (r3 & 0xffff) != 0;
-        const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
-                           ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
-        if (TRACE) n_tbs++;
-        switch ((r1 >> 2) & 7) {
-          case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-          case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-          case 4: intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-          default: intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+      if ((has >> c) & 1) {
+        long long tr0 = 0, tr1 = 0, tr2 = 0, tr3 = 0;
+        unsigned long long gt0 = 0;
+        if (TRACE) {
+          tr0 = clock64();
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt0));
         }
+        const uint32_t tu_first = rr.x, tu_count = rr.y & 0xffff;
+        const bool mixed = ((rr.y >> 24) >> c) & 1;
+        // prefetch the first 32 TU records of the CTB while the borders are fetched
+        uint4 mine = make_uint4(0, 0xff000000u, 0, 0);
+        uint2 mymask = make_uint2(0, 0);
+        if ((uint32_t)lane < tu_count) {
+          mine = __ldg(tus4 + tu_first + lane);
+          mymask = __ldg(masks + tu_first + lane);
+        }
+        g.cx = cx;
+        g.nb = nb;
+        E.x0 = cx * E.S;
+        // the upper row piece and the corner in the edge store were fetched for the previous CTB only if they were usable for it
+        const bool reuse = chained && (!((nb >> 2) & 1) || ((nb_prev >> 3) & 1)) && (!((nb >> 1) & 1) || ((nb_prev >> 2) & 1));
+        if (reuse) shift_edges(E);
+        if (TRACE) tr1 = clock64();
+        if (!fetch_borders(g, E, recs, c, mbox, ctbs_w, mixed, reuse, pre, sched, sleep_ns, yield_polls)) {
+          // blocked while other rows wait: give the row back (its left neighbour's column is in the mailbox)
+          if (lane == 0) queue_put(queue, qmask, atomicAdd(&sched->tail, 1u), row_payload(frame, c, row, cx));
+          yielded = true;
+          break;
+        }
+        if (TRACE) tr2 = clock64();
+        int n_tbs = 0;
+        long long acc[4] = {0, 0, 0, 0};
+        for (uint32_t base = 0; base < tu_count; base += 32) {
+          if (base) {
+            mine = make_uint4(0, 0xff000000u, 0, 0);
+            if (base + lane < tu_count) {
+              mine = __ldg(tus4 + tu_first + base + lane);
+              mymask = __ldg(masks + tu_first + base + lane);
+            }
+          }
+          const int n_here = min(32u, tu_count - base);
+          // lanes whose TU is an intra TB of this plane
+          const bool want = lane < n_here && (mine.y >> 24) != B265_INTRA_NONE && (int)(mine.y & 3) == c;
+          unsigned todo = __ballot_sync(B265_FULL_MASK, want);
+          while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const uint32_t r0 = __shfl_sync(B265_FULL_MASK, mine.x, src), r1 = __shfl_sync(B265_FULL_MASK, mine.y, src);
+            const uint32_t r3 = __shfl_sync(B265_FULL_MASK, mine.w, src);
+            const int x = (int)(r0 & 0xffff), y = (int)(r0 >> 16);
+            const int flags = (int)((r1 >> 8) & 0xff), mode = (int)(r1 >> 24);
+            const bool coded = (r3 & 0xffff) != 0;
+            const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
+                               ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
+            if (TRACE) n_tbs++;
+            switch ((r1 >> 2) & 7) {
+              case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+              case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+              case 4: intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+              default: intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+            }
+          }
+        }
+        if (TRACE) tr3 = clock64();
+        // post the borders the row below (and a warp that resumes this row) reads; the picture itself is complete at the end of the launch
+        post_borders(E, mbox, row * ctbs_w + cx);
+        if (TRACE && lane == 0) {
+          unsigned smid;
+          asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+          unsigned long long* o = trace + (size_t)(slot_base + row * ctbs_w + cx) * 12;
+          o[0] = tr0; o[1] = tr1; o[2] = tr2; o[3] = tr3; o[4] = clock64(); o[5] = n_tbs; o[6] = acc[0]; o[7] = acc[1];
+          o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = ((unsigned long long)(reuse ? 1 : (chained ? 2 : 0)) << 32) | smid;
+        }
+        chained = true;
+        nb_prev = nb;
+      } else {
+        chained = false;
       }
+      cx++;
+      rr = rr_next; nb = nb_next; pre = pre_next;
     }
-    if (TRACE) tr3 = clock64();
-    // post the borders later CTBs read (the picture itself is complete at the end of the launch), then release the successors
-    post_borders(E, mbox, ctb);
-    uint32_t old = 0;
-    if (succ) old = atomicSub(deps + sctb, 1u);
-    else if (lane == 4) old = atomicAdd(&sched->done, 1u);
-    const bool ready = succ && (old & 0xffu) == 1u;
-    const unsigned ready_mask = __ballot_sync(B265_FULL_MASK, ready);
-    const bool last = __shfl_sync(B265_FULL_MASK, old, 4) == n_tickets - 1;
-    const int t_ctb = ctb;
-    if (ready_mask) {   // continue with the first one (right neighbour first: same CTB row), hand the others to sleeping warps
-      const int pick = __ffs(ready_mask) - 1;
-      if (ready && lane != pick) queue_push(sched, queue, queue_entry(cur_frame, c, sctb));
-      ctb = __shfl_sync(B265_FULL_MASK, sctb, pick);
-      word = __shfl_sync(B265_FULL_MASK, old, pick);
-      const uint32_t rx = __shfl_sync(B265_FULL_MASK, srec.x, pick), ry = __shfl_sync(B265_FULL_MASK, srec.y, pick);
-      rec.tu_first = rx; rec.tu_count = (uint16_t)(ry & 0xffff); rec.has = (uint8_t)(ry >> 16); rec.mixed = (uint8_t)(ry >> 24);
-      have = true;
-    } else if (last) {
-      // every ticket is finished: at most total_warps warps sleep or are about to, on distinct slots >= tail
+    if (yielded) continue;
+    // ---- row finished ----
+    unsigned old = 0;
+    if (lane == 0) old = atomicAdd(&sched->done, 1u);
+    old = __shfl_sync(B265_FULL_MASK, old, 0);
+    if (old == n_rows - 1) {
+      // every row is finished: at most total_warps warps sleep or are about to, on consecutive indices >= tail
       const unsigned tail = ld_relaxed_u32(&sched->tail);
-      for (unsigned i = lane; i < total_warps; i += 32) st_relaxed_u32(queue + tail + i, B265_QUEUE_EXIT);
+      for (unsigned i = lane; i < total_warps; i += 32) queue_put(queue, qmask, tail + i, B265_QUEUE_EXIT);
+      return;
     }
-    if (TRACE && lane == 0) {
-      unsigned smid;
-      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-      unsigned long long* o = trace + (size_t)(slot_base + t_ctb) * 12;
-      o[0] = tr0; o[1] = tr1; o[2] = tr2; o[3] = tr3; o[4] = clock64(); o[5] = n_tbs; o[6] = acc[0]; o[7] = acc[1];
-      o[8] = acc[2]; o[9] = acc[3]; o[10] = gt0; o[11] = ((unsigned long long)(continued ? 1 : 0) << 32) | smid;
-    }
-    if (last && !have) return;
   }
 }
 
@@ -515,29 +584,37 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb) {
   return per_sm * sm_count;
 }
 
-// queue entries beyond the tickets themselves: one per warp that can be resident (exit markers)
+// queue entries beyond the rows themselves: one exit marker per warp that can be resident
 int intra_queue_slack(int sm_count) { return intra_max_resident_ctas(sm_count, 4) * INTRA_WARPS + 64; }
 
-void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int n_tickets, IntraSched* sched,
-                  uint32_t* queue, int sm_count, int log2_ctb) {
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_tickets, IntraSched* sched,
+                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb) {
   if (n_tickets <= 0) return;
   static int max_ctas[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (!max_ctas[log2_ctb & 7]) max_ctas[log2_ctb & 7] = intra_max_resident_ctas(sm_count, log2_ctb);
+  const unsigned qmask = queue_entries - 1;
   {
-    int gx = (max_slots + 255) / 256;
+    int gx = (std::max(max_slots, 3 * max_rows) + 255) / 256;
     if (gx > 4 * sm_count) gx = 4 * sm_count;
-    k_intra_sched_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched, queue);
+    k_intra_sched_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched, queue, qmask, max_rows);
   }
   // Sleeping warps cost next to nothing, but a grid that fills every CTA slot keeps a second batch (another stream of the
   // same process) off the SMs until it drains: B265_INTRA_CTAS_PER_SM caps the share of one launch.
-  static int cap_per_sm = -1, sleep_ns = -1;
+  static int cap_per_sm = -1, sleep_ns = -1, yield_polls = -1;
   if (cap_per_sm < 0) {
     const char* e = getenv("B265_INTRA_CTAS_PER_SM");
     cap_per_sm = e ? atoi(e) : 0;
     const char* s = getenv("B265_INTRA_SLEEP_NS");
     sleep_ns = s ? atoi(s) : 100;
+    // measured on B200 (4K, batches of 1..32): giving blocked rows back to the queue costs more (a resumed row pays a full
+    // border fetch and its warp's instruction stream restarts) than it gains, so the default is never; the mechanism stays
+    // for workloads with many more rows than warps
+    const char* y = getenv("B265_INTRA_YIELD_POLLS");
+    yield_polls = y ? atoi(y) : 0x7fffffff;
+    if (yield_polls < 1) yield_polls = 1;
   }
-  int ctas = (n_tickets + INTRA_WARPS - 1) / INTRA_WARPS;
+  // one warp per row is all a launch can use
+  int ctas = (3 * n_frames * max_rows + INTRA_WARPS - 1) / INTRA_WARPS;
   if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
   if (cap_per_sm > 0 && ctas > cap_per_sm * sm_count) ctas = cap_per_sm * sm_count;
   const unsigned total_warps = (unsigned)ctas * INTRA_WARPS;
@@ -554,8 +631,8 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     }
     cudaMalloc((void**)&d, n_slots * 96);
     cudaMemsetAsync(d, 0, n_slots * 96, st);
-    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, (unsigned)n_tickets,
-                                                                                     total_warps, (unsigned)sleep_ns, tb, d);
+    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, qmask, total_warps,
+                                                                                     (unsigned)sleep_ns, (unsigned)yield_polls, tb, d);
     cudaStreamSynchronize(st);
     unsigned long long* h = (unsigned long long*)malloc(n_slots * 96);
     cudaMemcpy(h, d, n_slots * 96, cudaMemcpyDeviceToHost);
@@ -564,6 +641,6 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     cudaFree(d);
     return;
   }
-  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, (unsigned)n_tickets,
-                                                                                    total_warps, (unsigned)sleep_ns, tb, nullptr);
+  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, qmask, total_warps,
+                                                                                    (unsigned)sleep_ns, (unsigned)yield_polls, tb, nullptr);
 }

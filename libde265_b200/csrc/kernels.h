@@ -27,10 +27,10 @@ void launch_interp_blocks(cudaStream_t st, int luma, int n_blocks, int w, int h,
 // availability masks of all intra TBs (k_intra.cu), grid (.., n_frames)
 void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus);
 int intra_max_resident_ctas(int sm_count, int log2_ctb);
-// dependency counters + initial ready set (grid over the (plane, CTB) slots of every frame), then the wavefront itself;
-// `queue` has n_tickets + intra_max_resident_ctas() * warps + 64 entries and is zero, `sched` is zero
-void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int n_tickets, IntraSched* sched,
-                  uint32_t* queue, int sm_count, int log2_ctb);
+// neighbour masks + row queue (grid over the (plane, CTB) slots of every frame), then the wavefront itself; `queue` has
+// `queue_entries` (a power of two >= 3 * n_frames * max_rows + intra_queue_slack()) 8-byte entries and is zero, `sched` is zero
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_tickets, IntraSched* sched,
+                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb);
 int intra_queue_slack(int sm_count);
 struct b265_ctx;
 // bS derivation + deblock V/H + SAO for every frame of a batch (k_postfilter.cu); ev (optional) is

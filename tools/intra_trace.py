@@ -7,9 +7,9 @@ a = a[a[:, 4] != 0]
 t0, t1, t2, t3, t4, ntb, a_g, a_f, a_p, a_s, gt, sm = a.T
 how = sm >> 32
 sm = sm & 0xffff
-print("tickets %d (%.1f %% continued), TBs %d, span %.3f ms (globaltimer)" % (len(a), 100.0 * how.mean(), ntb.sum(), (gt.max() - gt.min()) / 1e6))
-ph = {"take/setup": t1 - t0, "borders": t2 - t1, "tbs": t3 - t2, "post+release": t4 - t3, "total": t4 - t0}
-for sel, name in ((how == 1, "continued"), (how == 0, "from queue")):
+print("tickets %d (%.1f %% with the edge store reused), TBs %d, span %.3f ms (globaltimer)" % (len(a), 100.0 * (how == 1).mean(), ntb.sum(), (gt.max() - gt.min()) / 1e6))
+ph = {"setup/shift": t1 - t0, "borders": t2 - t1, "tbs": t3 - t2, "post+release": t4 - t3, "total": t4 - t0}
+for sel, name in ((how == 1, "next CTB of the row, edge store reused"), (how == 2, "next CTB of the row, full fetch"), (how == 0, "first CTB after taking the row")):
     if not sel.any():
         continue
     print("-- %s: %d tickets" % (name, sel.sum()))
