@@ -83,6 +83,13 @@ B265_API int b265_surface_download(b265_ctx* ctx, int surface_id, int plane, uin
 B265_API int b265_surface_plane(b265_ctx* ctx, int surface_id, int plane, void** dev_ptr,
                                 int* pitch, int* width, int* height);
 
+/* Decoded picture hash (SEI payload 132) of n surfaces, computed on the device from the pictures in HBM the way the
+ * reference computes it from its host planes (sei.cc:160-270; verification :273-354): hash_type 0 = MD5, 1 = CRC,
+ * 2 = checksum.  out receives n * 3 slots of 16 bytes (per colour plane: the MD5 digest, or the CRC / checksum as a
+ * little-endian 32-bit word; absent planes: zeros), copied asynchronously on the context stream - valid after
+ * b265_sync(); `out` should be pinned (b265_host_alloc). */
+B265_API int b265_surface_hash(b265_ctx* ctx, const int* surface_ids, int n, int hash_type, uint8_t* out);
+
 /* ------------------------------------------------------------------------------------------
  * A.2  Work-list records (all little-endian PODs, written by the host parser into pinned memory)
  * ------------------------------------------------------------------------------------------ */

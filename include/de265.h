@@ -229,6 +229,9 @@ LIBDE265_API void b265_de265_set_parse_only(int on);
 /* `out` is a b265_frame_job (b265.h); void* here so that de265.h stays free of b265.h types */
 LIBDE265_API int b265_de265_image_job(de265_decoder_context*, const struct de265_image*, void* out_b265_frame_job);
 LIBDE265_API int b265_de265_image_poc(const struct de265_image*);
+/* pictures whose decoded-picture-hash SEI was verified (on the device) so far; a mismatch makes de265_decode return
+ * DE265_ERROR_CHECKSUM_MISMATCH while the picture is still delivered (decctx.cc:770-779, sei.cc:273-354) */
+LIBDE265_API uint64_t b265_de265_hashes_checked(de265_decoder_context*);
 /* 1 = IRAP picture with NoRaslOutputFlag (first of a coded video sequence: POCs restart, earlier pictures are output first) */
 LIBDE265_API int b265_de265_image_starts_cvs(const struct de265_image*);
 

@@ -88,6 +88,7 @@ void b265_destroy(b265_ctx* ctx) {
     if (s.used && s.base) cudaFree(s.base);
   if (ctx->flush_buf) cudaFree(ctx->flush_buf);
   if (ctx->d_stage.p) cudaFree(ctx->d_stage.p);
+  if (ctx->d_hash.p) cudaFree(ctx->d_hash.p);
   if (ctx->d_submit.p) cudaFree(ctx->d_submit.p);
   if (ctx->h_submit.p) cudaFreeHost(ctx->h_submit.p);
   if (ctx->h_stage.p) cudaFreeHost(ctx->h_stage.p);
@@ -251,6 +252,35 @@ int b265_surface_plane(b265_ctx* ctx, int id, int plane, void** dev_ptr, int* pi
   if (pitch) *pitch = s->pitch[plane];
   if (width) *width = s->pw[plane];
   if (height) *height = s->ph[plane];
+  return B265_OK;
+}
+
+int b265_surface_hash(b265_ctx* ctx, const int* ids, int n, int type, uint8_t* out) {
+  if (!ctx || !ids || n <= 0 || n > 4096 || type < 0 || type > 2 || !out) return B265_ERR_INVALID_ARG;
+  CK(cudaSetDevice(ctx->device));
+  std::vector<HashJob> jobs(n);
+  int max_h = 1;
+  for (int i = 0; i < n; i++) {
+    if (ids[i] < 0 || ids[i] >= (int)ctx->surfaces.size() || !ctx->surfaces[ids[i]].used) return B265_ERR_INVALID_ARG;
+    const Surface& s = ctx->surfaces[ids[i]];
+    if (s.width & 7) return B265_ERR_UNSUPPORTED;   // rows are hashed in 4-byte words (luma and 4:2:0 chroma)
+    for (int c = 0; c < 3; c++) {
+      const bool present = c == 0 || s.chroma;
+      jobs[i].plane[c] = present ? s.plane[c] : nullptr;
+      jobs[i].w[c] = c ? (s.width + 1) / 2 : s.width;
+      jobs[i].h[c] = c ? (s.height + 1) / 2 : s.height;
+      jobs[i].pitch[c] = s.pitch[c];
+      if (jobs[i].h[c] > max_h) max_h = jobs[i].h[c];
+    }
+  }
+  const size_t o_out = (sizeof(HashJob) * (size_t)n + 255) & ~(size_t)255, o_rows = o_out + (((size_t)n * 48 + 255) & ~(size_t)255);
+  int r = devbuf_reserve(ctx, &ctx->d_hash, o_rows + (size_t)n * 3 * max_h * 2 + 256, false);
+  if (r) return r;
+  uint8_t* D = (uint8_t*)ctx->d_hash.p;
+  CK(cudaMemcpyAsync(D, jobs.data(), sizeof(HashJob) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));   // pageable: staged before return
+  ctx->launches += launch_hash(ctx->stream, type, (const HashJob*)D, n, max_h, (uint16_t*)(D + o_rows), D + o_out);
+  CK_LAUNCH("k_hash");
+  CK(cudaMemcpyAsync(out, D + o_out, (size_t)n * 48, cudaMemcpyDeviceToHost, ctx->stream));
   return B265_OK;
 }
 

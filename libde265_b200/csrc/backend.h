@@ -40,6 +40,7 @@ struct b265_ctx {
   // staging for b265_submit_frames (reused between calls)
   DevBuf d_stage, h_stage;
   DevBuf d_submit, h_submit;   // grow-only staging of b265_submit_frames
+  DevBuf d_hash;               // b265_surface_hash: jobs, digests, CRC row scratch
   b265_batch* submit_batch = nullptr;
 };
 

@@ -104,6 +104,12 @@ struct FrameDev {
 // boundary rules sample by sample on the CTB rim, sao.cc:119-164)
 #define B265_SAOREC_FOREIGN 0x80
 
+// one picture to hash (k_hash.cu): planes of an 8-bit surface; plane[c] == NULL: no such plane (4:0:0)
+struct HashJob {
+  const uint8_t* plane[3];
+  int w[3], h[3], pitch[3];
+};
+
 // Intra wavefront work unit = one colour plane of one CTB ("ticket").  The host only states, per CTB, where its TUs are
 // (decoding order, all planes interleaved) and which planes hold intra TBs; dependency counters and the ready queue are
 // built and driven on the device (k_intra.cu).

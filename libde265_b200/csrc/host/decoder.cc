@@ -115,6 +115,9 @@ struct Decoder {
   double stat_parse_s = 0, stat_gpu_s = 0, stat_h2d = 0, stat_d2h = 0;
   uint64_t stat_pictures = 0, stat_batches = 0;
   double stat_submit_s = 0;  // part of stat_gpu_s spent inside b265_submit_frames (host list building + enqueue)
+  uint64_t stat_hashed = 0;  // pictures whose SEI hash was verified on the device
+  uint8_t* hash_host[4] = {nullptr, nullptr, nullptr, nullptr};   // per reconstruction context: pinned digests
+  size_t hash_bytes[4] = {0, 0, 0, 0};
 
   Decoder() {
     int dev = g_device;
@@ -165,6 +168,7 @@ struct Decoder {
     for (auto& i : output) drop(i);
     drop(last_returned);
     for (auto& p : host_pool) { if (gpu) b265_host_free(gpu, p.second); }
+    for (size_t i = 0; i < gpus.size() && i < 4; i++) if (hash_host[i] && gpus[i]) b265_host_free(gpus[i], hash_host[i]);
     for (b265_ctx* c : gpus) if (c) b265_destroy(c);
   }
 
@@ -467,10 +471,48 @@ struct Decoder {
           h2d += (double)(p.tus.size() * sizeof(b265_tu) + p.coeffs.size() * sizeof(b265_coeff) + p.unit_info.size() +
                           p.qp_y.size() + p.sao.size() * sizeof(b265_sao) + p.ctbs.size() * sizeof(b265_ctb));
         }
+        // decoded picture hash (DE265_DECODER_PARAM_BOOL_SEI_CHECK_HASH): computed on the device from the picture in HBM,
+        // 48 bytes per picture come back; pictures that are not output are not checked (sei.cc:277-283)
+        std::vector<de265_image*> hashed[3];
+        if (r == B265_OK && check_hash) {
+          for (de265_image* img : good)
+            if (img->pic.hash_type >= 0 && img->pic.pic_output && !img->pic.error) hashed[img->pic.hash_type].push_back(img);
+          size_t total = hashed[0].size() + hashed[1].size() + hashed[2].size(), at = 0;
+          if (total * 48 > hash_bytes[ci]) {
+            if (hash_host[ci]) b265_host_free(gpu, hash_host[ci]);
+            void* hp = nullptr;
+            hash_bytes[ci] = b265_host_alloc(gpu, total * 48 + 48 * 64, &hp) == B265_OK ? total * 48 + 48 * 64 : 0;
+            hash_host[ci] = (uint8_t*)hp;
+          }
+          for (int t = 0; t < 3 && r == B265_OK && hash_host[ci]; t++) {
+            if (hashed[t].empty()) continue;
+            std::vector<int> ids;
+            for (de265_image* img : hashed[t]) ids.push_back(img->pic.surface);
+            r = b265_surface_hash(gpu, ids.data(), (int)ids.size(), t, hash_host[ci] + at * 48);
+            at += ids.size();
+          }
+        }
         if (r == B265_OK) r = b265_sync(gpu);
+        if (r == B265_OK && check_hash && hash_host[ci]) {
+          size_t at = 0;
+          for (int t = 0; t < 3; t++)
+            for (de265_image* img : hashed[t]) {
+              const uint8_t* got = hash_host[ci] + 48 * at++;
+              const int planes = img->pic.sps->chroma_format_idc == 0 ? 1 : 3, per = t == 0 ? 16 : (t == 1 ? 2 : 4);
+              for (int c = 0; c < planes; c++)
+                if (memcmp(got + 16 * c, img->pic.hash[c], per)) {
+                  fprintf(stderr, "SEI decoded picture hash mismatch (POC=%d, plane %d)\n", img->pic.poc, c);
+                  img->pic.error = DE265_ERROR_CHECKSUM_MISMATCH;
+                  break;
+                }
+              std::lock_guard<std::mutex> l(mu);
+              stat_hashed++;
+            }
+        }
         for (de265_image* img : good) {
           if (r != B265_OK && getenv("B265_DEBUG")) fprintf(stderr, "b265: back end status %d: %s\n", r, b265_last_error(gpu));
           if (r != B265_OK) img->pic.error = r == B265_ERR_OUT_OF_MEMORY ? DE265_ERROR_OUT_OF_MEMORY : DE265_ERROR_UNSPECIFIED_DECODING_ERROR;
+          // (a hash mismatch keeps the picture: it is delivered and the error is reported by de265_decode, like decctx.cc:770-779)
           img->pic.surface = -1;
           img->pic.ref_pics.clear();
           img->pic.self.reset();
@@ -655,6 +697,29 @@ struct Decoder {
     if (type == NAL_AUD || type == NAL_PREFIX_SEI) {
       // a new access unit starts: the previous picture is complete
       if (cur && !cur->pic.slice_units.empty()) dispatch_current();
+      return DE265_OK;
+    }
+    if (type == NAL_SUFFIX_SEI) {
+      // decoded picture hash of the picture being assembled (read_sei_NAL decctx.cc:584-606: the first message of the NAL,
+      // kept for the last image unit; sei.cc:32-61).  Other payloads are ignored like the reference ignores them.
+      if (!cur || cur->pic.slice_units.empty() || rbsp.size() < 3) return DE265_OK;
+      size_t pos = 0;
+      int ptype = 0, psize = 0;
+      while (pos < rbsp.size()) { const int b = rbsp[pos++]; ptype += b; if (b != 0xff) break; }
+      while (pos < rbsp.size()) { const int b = rbsp[pos++]; psize += b; if (b != 0xff) break; }
+      if (ptype != 132 || pos >= rbsp.size()) return DE265_OK;
+      const int htype = rbsp[pos++];
+      const int planes = cur->pic.sps->chroma_format_idc == 0 ? 1 : 3;
+      const int per = htype == 0 ? 16 : (htype == 1 ? 2 : 4);
+      if (htype > 2 || pos + (size_t)planes * per > rbsp.size() || psize < 1 + planes * per) { warn(DE265_ERROR_CANNOT_PROCESS_SEI); return DE265_OK; }
+      Picture& p = cur->pic;
+      memset(p.hash, 0, sizeof(p.hash));
+      for (int c = 0; c < planes; c++) {
+        if (htype == 0) memcpy(p.hash[c], &rbsp[pos], 16);
+        else for (int k = 0; k < per; k++) p.hash[c][per - 1 - k] = rbsp[pos + k];   // big-endian in the stream
+        pos += per;
+      }
+      p.hash_type = htype;
       return DE265_OK;
     }
     if (type > NAL_RSV_IRAP_VCL23 || (type > NAL_RASL_R && type < NAL_BLA_W_LP)) return DE265_OK;  // non-VCL / reserved
@@ -1069,6 +1134,11 @@ LIBDE265_API int b265_de265_image_job(de265_decoder_context* c, const struct de2
   return img->pic.error;
 }
 LIBDE265_API int b265_de265_image_poc(const struct de265_image* img) { return img->pic.poc; }
+LIBDE265_API uint64_t b265_de265_hashes_checked(de265_decoder_context* c) {
+  Decoder* d = DEC(c);
+  std::lock_guard<std::mutex> l(d->mu);
+  return d->stat_hashed;
+}
 LIBDE265_API int b265_de265_image_starts_cvs(const struct de265_image* img) { return img->pic.irap_no_rasl ? 1 : 0; }
 LIBDE265_API void b265_de265_set_batch(de265_decoder_context* c, int n) {
   Decoder* d = DEC(c);

@@ -107,6 +107,9 @@ struct Picture {
   int width = 0, height = 0;
   int poc = 0, nal_type = 0, temporal_id = 0;
   int pic_output = 1;
+  // decoded picture hash of the picture's suffix SEI (sei.cc:32-61): type 0 MD5, 1 CRC, 2 checksum; -1 = none
+  int hash_type = -1;
+  uint8_t hash[3][16] = {};         // per colour plane: MD5 digest bytes, or the CRC / checksum as a little-endian word
   bool irap_no_rasl = false;       // IRAP picture with NoRaslOutputFlag: pictures waiting for output leave first (C.5.2.2)
   int64_t pts = 0;
   void* user_data = nullptr;

@@ -32,6 +32,9 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb);
 void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_tickets, IntraSched* sched,
                   unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb);
 int intra_queue_slack(int sm_count);
+// decoded picture hash of n pictures (k_hash.cu): type 0 MD5, 1 CRC, 2 checksum (sei.h sei_decoded_picture_hash_type);
+// out = n * 3 slots of 16 bytes (MD5 digest / CRC or checksum in the first word); returns the number of launches
+int launch_hash(cudaStream_t st, int type, const HashJob* jobs, int n, int max_h, uint16_t* row_scratch, uint8_t* out);
 struct b265_ctx;
 // bS derivation + deblock V/H + SAO for every frame of a batch (k_postfilter.cu); ev (optional) is
 // recorded between deblocking and SAO for stage timing.

@@ -63,6 +63,8 @@ def _bind():
     lib.b265_de265_image_job.argtypes = [vp, vp, C.POINTER(L.FrameJob)]
     lib.b265_de265_image_poc.argtypes = [vp]
     lib.b265_de265_image_starts_cvs.argtypes = [vp]
+    lib.b265_de265_hashes_checked.argtypes = [vp]
+    lib.b265_de265_hashes_checked.restype = C.c_uint64
     lib.de265_get_image_NAL_header.argtypes = [vp, C.POINTER(C.c_int), vp, vp, vp]
     lib.de265_get_image_NAL_header.restype = None
     _bound = True
@@ -76,7 +78,8 @@ class De265Error(RuntimeError):
 
 
 class Decoder:
-    def __init__(self, device=0, threads=0, batch=8, parse_only=False, disable_deblocking=False, disable_sao=False):
+    def __init__(self, device=0, threads=0, batch=8, parse_only=False, disable_deblocking=False, disable_sao=False,
+                 check_hash=False):
         self.lib = _bind()
         self.lib.b265_de265_set_device(device)
         self.lib.b265_de265_set_parse_only(1 if parse_only else 0)
@@ -91,6 +94,8 @@ class Decoder:
             self.lib.de265_set_parameter_bool(self.h, PARAM_DISABLE_DEBLOCKING, 1)
         if disable_sao:
             self.lib.de265_set_parameter_bool(self.h, PARAM_DISABLE_SAO, 1)
+        if check_hash:   # dec265 -c: verify the decoded-picture-hash SEI of every output picture (on the device)
+            self.lib.de265_set_parameter_bool(self.h, PARAM_SEI_CHECK_HASH, 1)
         self.parse_only = parse_only
 
     def close(self):

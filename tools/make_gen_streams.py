@@ -80,6 +80,13 @@ NAMED = {
                                        post={"drop_picture": 2}),
     "gen_pb_lost_longterm_256x192": dict(seed=54, w=256, h=192, frames=12, inter=1, long_term=1, poc_bits=4, max_refs=2, tmvp=1,
                                          post={"drop_picture": 1}),
+    # ---- decoded picture hash SEI (sei.cc:32-61, 160-354): the three hash types, P/B pictures, and a wrong hash ----
+    "gen_hash_md5_200x136": dict(seed=61, w=200, h=136, frames=3, sao=1, post={"sei_hash": 0}),
+    "gen_hash_crc_416x240": dict(seed=62, w=416, h=240, frames=2, sao=1, pcm=1, post={"sei_hash": 1}),
+    "gen_hash_checksum_320x192": dict(seed=63, w=320, h=192, ctb=6, frames=2, post={"sei_hash": 2}),
+    "gen_hash_pb_mixed_256x192": dict(seed=64, w=256, h=192, frames=6, inter=1, max_refs=2, tmvp=1, sao=1, post={"sei_hash": -1}),
+    "gen_hash_wrong_256x192": dict(seed=64, w=256, h=192, frames=6, inter=1, max_refs=2, tmvp=1, sao=1,
+                                   post={"sei_hash": -1, "corrupt_hash": 3}),
     "gen_pb_720p": dict(seed=47, w=1280, h=720, frames=4, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_bipred=1,
                         slice_ctbs=200, p_skip=0.5),
 }
@@ -211,13 +218,106 @@ def post_process(data, post):
     return b"".join(out)
 
 
+def crc_plane(plane):
+    """the reference's CRC of a plane (sei.cc:216-254): CCITT register 0xFFFF, two zero bytes FIRST, then the rows"""
+    import numpy as np
+    tab = np.zeros(256, np.uint32)
+    for s_ in range(256):
+        t = s_ ^ (s_ >> 4)
+        tab[s_] = (t ^ (t << 5) ^ (t << 12)) & 0xffff
+    crc = 0xffff
+    for b in (0, 0):
+        crc = ((crc << 8) & 0xffff) ^ int(tab[(b ^ (crc >> 8)) & 0xff])
+    for b in plane.tobytes():
+        crc = ((crc << 8) & 0xffff) ^ int(tab[(b ^ (crc >> 8)) & 0xff])
+    return crc
+
+
+def checksum_plane(plane):
+    """sei.cc:160-182"""
+    import numpy as np
+    h, w = plane.shape
+    x, y = np.meshgrid(np.arange(w), np.arange(h))
+    mask = ((x & 0xff) ^ (y & 0xff) ^ (x >> 8) ^ (y >> 8)) & 0xff
+    return int((plane.astype(np.int64) ^ mask).sum() & 0xffffffff)
+
+
+def escape_rbsp(b):
+    out, zeros = bytearray(), 0
+    for v in b:
+        if zeros >= 2 and v <= 3:
+            out.append(3)
+            zeros = 0
+        out.append(v)
+        zeros = zeros + 1 if v == 0 else 0
+    return bytes(out)
+
+
+def add_hash_sei(data, w, h, hash_type, corrupt=None):
+    """append a decoded-picture-hash suffix SEI (payload 132, D.2.19) to every picture: the hash of the REFERENCE decoder's
+    output planes (so `dec265 -c` accepts the stream).  Only for streams whose decoding order is their output order.
+    hash_type 0 MD5, 1 CRC, 2 checksum, -1: cycle through the three.  corrupt = picture index whose hash gets one bit flipped."""
+    import hashlib, tempfile
+    import numpy as np
+    from tools.make_streams import REF
+    with tempfile.TemporaryDirectory() as td:
+        src, yuv = os.path.join(td, "s.bin"), os.path.join(td, "o.yuv")
+        open(src, "wb").write(data)
+        subprocess.run([os.path.join(REF, "dec265"), "-q", "-o", yuv, src], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        raw = np.fromfile(yuv, np.uint8)
+    fs = w * h * 3 // 2
+    n = len(raw) // fs
+    nals = split_nals(data)
+    out, pic = [], -1
+    def sei_for(i):
+        f = raw[i * fs:(i + 1) * fs]
+        planes = [f[:w * h].reshape(h, w), f[w * h:w * h * 5 // 4].reshape(h // 2, w // 2), f[w * h * 5 // 4:].reshape(h // 2, w // 2)]
+        t = hash_type if hash_type >= 0 else i % 3
+        body = bytearray([t])
+        for pl in planes:
+            if t == 0:
+                body += hashlib.md5(pl.tobytes()).digest()
+            elif t == 1:
+                body += crc_plane(pl).to_bytes(2, "big")
+            else:
+                body += checksum_plane(pl).to_bytes(4, "big")
+        if corrupt == i:
+            body[-1] ^= 0x10
+        payload = bytes([132, len(body)]) + bytes(body) + b"\x80"
+        return b"\x00\x00\x01\x50\x01" + escape_rbsp(payload)   # SUFFIX_SEI_NUT = 40, temporal id 0
+    for k, nal in enumerate(nals):
+        t = nal_type(nal)
+        if t < 32 and first_slice(nal):
+            if pic >= 0:
+                out.append(sei_for(pic))
+            pic += 1
+        elif t >= 32 and pic >= 0 and (not out or nal_type(out[-1]) != 40) and t != 40:
+            # a non-VCL NAL (parameter set, EOS ...) ends the picture too
+            out.append(sei_for(pic))
+        out.append(nal)
+    assert pic + 1 == n, "hash SEI needs every picture decoded and output in decoding order (%d coded, %d output)" % (pic + 1, n)
+    if nal_type(out[-1]) != 40:
+        out.append(sei_for(pic))
+    return b"".join(out)
+
+
 def generate(name, args, out_dir=OUT):
     path = os.path.join(out_dir, name + ".bin")
     args = dict(args)
     post = args.pop("post", None)
     subprocess.run([build_generator(), path] + ["%s=%s" % kv for kv in args.items()], check=True)
     if post:
-        data = post_process(open(path, "rb").read(), post)
+        data = open(path, "rb").read()
+        if set(post) - {"sei_hash", "corrupt_hash"}:
+            data = post_process(data, post)
+        if "sei_hash" in post:
+            from tools.make_streams import REF
+            data = add_hash_sei(data, args["w"], args["h"], post["sei_hash"], post.get("corrupt_hash"))
+            open(path, "wb").write(data)
+            # the reference decoder must accept (or, for the corrupted variant, reject) the hashes
+            r = subprocess.run([os.path.join(REF, "dec265"), "-q", "-c", path], capture_output=True, text=True)
+            bad = "mismatch" in r.stderr or "SEI decoded picture hash:" in r.stderr
+            assert bad == ("corrupt_hash" in post), "dec265 -c on %s: %s" % (name, r.stderr[-300:])
         open(path, "wb").write(data)
         args["post"] = post
     md5 = ref_md5(path, args["w"], args["h"])
