@@ -25,7 +25,23 @@ STREAM_WL = {
     "stream_4k": ("c4_2160p_q32", True, 32, 32, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
                   "deblocking enabled by PPS re-write (SAO cannot be enabled in an enc265 stream)"),
     "stream_1080p": ("c1_1080p_q32", False, 16, 64, "1920x1080 8-bit 4:2:0 enc265 intra stream (16 unique frames, qp 32)"),
+    # P/B streams at the metric's sizes.  The reference's encoder cannot produce inter pictures, so these come from
+    # the random-syntax generator (tools/streamgen, golden MD5s from the unmodified reference decoder): merge / AMVP /
+    # temporal MVP, AMP, weighted prediction, SAO and deblocking on; kernel batch = the whole stream in decoding order
+    "stream_inter_1080p": ("gen_pb_1080p_ld32", False, 8, 0, "1920x1080 P/B generator stream, low-delay shape (32 pictures, 3 references, "
+                           "weighted prediction, temporal MVP, AMP, SAO, deblocking)"),
+    "stream_inter_1080p_ra": ("gen_pb_1080p_ra33", False, 8, 0, "1920x1080 P/B generator stream, random-access shape (33 pictures, output "
+                              "reordering, B slices, weighted bi-prediction, temporal MVP, AMP, SAO, deblocking)"),
+    "stream_inter_4k": ("gen_pb_2160p_ld12", False, 16, 0, "3840x2160 P/B generator stream, low-delay shape (12 pictures, 2 references, "
+                        "weighted prediction, temporal MVP, AMP, SAO, deblocking)"),
 }
+# config 5 (BASELINE.json configs[4]): eight independent 4K enc265 streams, seeds 10..17 (tools/make_streams.py), one
+# decoder instance per GPU; rank r of N decodes streams r, r+N, ...
+C5_STREAMS = ["c5_2160p_s%d" % s_ for s_ in range(10, 18)]
+
+
+def c5_available():
+    return all(os.path.exists(os.path.join(STREAMS, n + ".bin")) for n in C5_STREAMS)
 
 
 def _dist_device():
@@ -148,21 +164,26 @@ def host_cores():
 # reference decoder on the host cores
 # =====================================================================================================
 def run_dec265(data, procs, loops, scalar=False):
-    """`procs` concurrent dec265 processes, each decoding `data` repeated `loops` times.
-    Returns (frames_total, seconds) or None when oracle/_ref/dec265 is not available."""
+    """`procs` concurrent dec265 processes, each decoding `data` repeated `loops` times (`data` may be a list of streams:
+    process i takes stream i mod len).  Returns (frames_total, seconds) or None when oracle/_ref/dec265 is not available."""
     exe = os.path.join(REF_DIR, "dec265")
     if not os.path.exists(exe):
         return None
+    datas = data if isinstance(data, (list, tuple)) else [data]
     with tempfile.TemporaryDirectory() as td:
-        f = os.path.join(td, "in.bin")
-        with open(f, "wb") as fh:
-            for _ in range(loops):
-                fh.write(data)
-        cmd = [exe, "-q"] + (["-0"] if scalar else []) + [f]
+        files = []
+        for k, d in enumerate(datas):
+            f = os.path.join(td, "in%d.bin" % k)
+            with open(f, "wb") as fh:
+                for _ in range(loops):
+                    fh.write(d)
+            files.append(f)
+        base = [exe, "-q"] + (["-0"] if scalar else [])
         # warm the page cache / loader
-        subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+        subprocess.run(base + [files[0]], stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
         t0 = time.perf_counter()
-        ps = [subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for _ in range(procs)]
+        ps = [subprocess.Popen(base + [files[i % len(files)]], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+              for i in range(procs)]
         frames = 0
         for p in ps:
             out = p.communicate()[0]
@@ -194,7 +215,7 @@ def cpu_baseline_stream(wl, budget_s=20.0):
 def cpu_port_stream(wl):
     """Fallback when the compiled reference did not travel: host parser + C oracle reconstruction, 1 thread."""
     from benchmarks.jobs import stream_jobs
-    from tests.test_parser_streams import oracle_planes
+    from oracle.frame import oracle_planes
     name, patched, _, _, _ = STREAM_WL[wl]
     jobs = stream_jobs(_stream_bytes(name, patched), threads=1, max_frames=2)
     t0 = time.perf_counter()
@@ -222,10 +243,20 @@ def _job_algorithmic_bytes(J):
     tus = np.ctypeslib.as_array(C.cast(J.tus, C.POINTER(C.c_uint8)), shape=(J.n_tus * 16,)).view(_TU_DT)
     coded = tus[tus['ncoeff'] > 0]
     coded_samples = int((1 << (2 * (coded['cidx_log2'].astype(np.int64) >> 2))).sum())
+    intra_tus = tus[tus['intra_mode'] != 0xff]
+    intra_samples = int((1 << (2 * (intra_tus['cidx_log2'].astype(np.int64) >> 2))).sum())
+    coded_intra = intra_tus[intra_tus['ncoeff'] > 0]
+    coded_intra_samples = int((1 << (2 * (coded_intra['cidx_log2'].astype(np.int64) >> 2))).sum())
     res = 4 * J.n_coeffs + 2 * coded_samples
-    intra = P + 2 * coded_samples
+    intra = intra_samples + 2 * coded_intra_samples      # all-intra picture: intra_samples == P
     dbk = 4 * P if (J.flags & L.FRAME_DEBLOCK) else 0
-    return res, intra, dbk
+    mc = 0
+    if J.n_pus:   # uni-predicted PU 1.5 wh read + 1.5 wh written, bi-predicted 3 wh read + 1.5 wh written
+        pus = np.ctypeslib.as_array(C.cast(J.pus, C.POINTER(C.c_uint8)), shape=(J.n_pus * 24,)).reshape(-1, 24)
+        area = pus[:, 4].astype(np.int64) * pus[:, 5].astype(np.int64)
+        mc = int((area * np.where((pus[:, 6] & 3) == 3, 4.5, 3.0)).sum())
+    sao = 2 * P if (J.flags & L.FRAME_SAO) else 0
+    return res, intra, dbk, mc, sao
 
 
 def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
@@ -236,25 +267,40 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     data = _stream_bytes(name, patched)
     gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
     W, H, nuniq = gold["width"], gold["height"], gold["frames"]
+    if wl == "stream_4k" and world > 1 and c5_available():
+        # config 5: every rank decodes its own stream(s), in the kernel leg and end to end
+        mine = [n for i, n in enumerate(C5_STREAMS) if i % world == rank]
+        data = b"".join(_stream_bytes(n, patched) for n in mine)
+        nuniq = sum(json.load(open(os.path.join(STREAMS, n + ".md5.json")))["frames"] for n in mine)
+        loops = max(1, loops * 8 // nuniq)
+        desc += "; config 5: rank r of %d decodes the independent streams r, r+%d, ... (seeds 10..17)" % (world, world)
     cores = host_cores()
     threads = int(os.environ.get("B265_BENCH_THREADS", 0)) or max(1, cores // world - 1)   # override: developer sweeps
 
     # ---------------- kernels with work lists resident in HBM ----------------
     ctx = L.Context(local)
-    uniq = stream_jobs(data, threads=min(threads, 8))
+    uniq = stream_jobs(data, threads=min(threads, 8))       # decoding order
+    inter = any(oj.job.n_refs for oj in uniq)
+    if not kbatch:
+        kbatch = len(uniq)
     jobs, sids = [], []
+    uid2sid = {}
     for i in range(kbatch):
-        oj = uniq[i % nuniq]
+        oj = uniq[i % len(uniq)]
         J = L.FrameJob()
         C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
         sid = ctx.surface_alloc(W, H)
+        if inter:   # a parse-only decoder names pictures by unique id: map them to surfaces (the whole stream is one batch)
+            uid2sid[oj.job.dst_surface] = sid
+            for r in range(J.n_refs):
+                J.ref_surfaces[r] = uid2sid[oj.job.ref_surfaces[r]]
         J.dst_surface = sid
         sids.append(sid)
         jobs.append(J)
     batch = ctx.upload_frames(jobs)
     ctx.sync()
     ab = [_job_algorithmic_bytes(J) for J in jobs]
-    bytes_res, bytes_intra, bytes_dbk = (sum(x[i] for x in ab) for i in range(3))
+    bytes_res, bytes_intra, bytes_dbk, bytes_mc, bytes_sao = (sum(x[i] for x in ab) for i in range(5))
     for _ in range(a.warmup):
         ctx.run_batch(batch)
     ctx.sync()
@@ -362,44 +408,67 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     e2e_fps = world * frames_step * a.steps / e2e_s
 
     peak, peak_src = measured_peaks()
-    res_gbs = bytes_res / stage[1] / 1e6 if stage[1] > 0 else 0.0
-    intra_gbs = bytes_intra / stage[2] / 1e6 if stage[2] > 0 else 0.0
-    dbk_gbs = bytes_dbk / stage[3] / 1e6 if stage[3] > 0 and bytes_dbk else None
+    gbs = lambda nbytes, ms: (nbytes / ms / 1e6) if (ms and ms > 0 and nbytes) else None
+    mc_gbs, res_gbs, intra_gbs, dbk_gbs = gbs(bytes_mc, stage[0]), gbs(bytes_res, stage[1]), gbs(bytes_intra, stage[2]), gbs(bytes_dbk, stage[3])
+    own_sao_gbs = gbs(bytes_sao, stage[4])
+    # the roofline object describes the stage with the largest share of the step
+    stages = [("k_mc (+k_pcm)", stage[0], mc_gbs,
+               "algorithmic bytes = 3*w*h per uni-predicted PU (1.5 read + 1.5 written), 4.5*w*h per bi-predicted PU"),
+              ("k_residual_sparse* + k_intra_prep", stage[1], res_gbs, "4 B per non-zero level read + 2 B per sample of a coded TB written"),
+              ("k_intra_wavefront", stage[2], intra_gbs,
+               "dependency-latency bound (CTB-row wavefront: one warp walks a CTB row, rows trail each other by two CTBs), not "
+               "bandwidth bound; algorithmic bytes = samples of the intra TBs written + 2 B per sample of a coded intra TB read"),
+              ("k_deblock_* (V+H, bS derived in-kernel)", stage[3], dbk_gbs, "4P per picture: two passes read and write the picture"),
+              ("k_sao", stage[4], own_sao_gbs, "2P per picture")]
+    dom = max(stages, key=lambda t: t[1])
+    traffic = None
+    try:   # dram__bytes_read+write of one launch of the dominant kernel on this workload, from a committed ncu --set full capture
+        tf = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        ent = tf.get(wl, {}).get(dom[0].split(" ")[0])
+        if ent and ent.get("frames_per_launch") == kbatch:
+            traffic = ent["dram_bytes"]
+    except Exception:
+        pass
+    parse_core_s = (s1["parse_s"] - s0["parse_s"]) / a.steps
     res = {
         "metric": "decoded frames/s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
         "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": kbatch,
                    "mpixel_per_s": value * W * H / 1e6,
-                   "value_is": "reconstruction kernels (residual pre-pass, intra wavefront, deblock V+H) on a batch of %d pictures "
-                               "whose work lists are resident in HBM" % kbatch,
+                   "value_is": "all reconstruction kernels (MC, residual, intra wavefront, deblock V+H, SAO where the stream has it) on a batch "
+                               "of %d pictures whose work lists are resident in HBM; the CPU arm is the whole reference decoder "
+                               "(parsing included) and compares with `e2e`, not with `value`" % kbatch,
                    "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
                          % (kbatch * W * H * 3 // 2 >> 20),
                    "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
                              "%s CUDA contexts, batch %d; %d frames per step" % (threads, os.environ.get("B265_RECON_CONTEXTS", "3"), dbatch, frames_step),
-                   "host_cores": cores,
+                   "host_cores": cores, "host_cores_per_rank": cores // world,
                    "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage],
                    "sao_leg_ms": round(sao_ms, 3) if sao_ms else None},
         "e2e": {"value": e2e_fps, "unit": "frames/s",
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
                 "d2h_bytes_per_step": int((s1["d2h_bytes"] - s0["d2h_bytes"]) / a.steps),
                 "mpixel_per_s": e2e_fps * W * H / 1e6,
-                "host_parse_core_seconds_per_step": (s1["parse_s"] - s0["parse_s"]) / a.steps,
+                "per_gpu": e2e_fps / world,
+                "host_parse_core_seconds_per_step": parse_core_s,
                 "recon_thread_seconds_per_step": (s1["gpu_s"] - s0["gpu_s"]) / a.steps,
                 "submit_seconds_per_step": (s1["submit_s"] - s0["submit_s"]) / a.steps,
-                "wall_seconds_per_step": e2e_s / a.steps},
+                "wall_seconds_per_step": e2e_s / a.steps,
+                # what the host cores alone allow: every rank parses its step on `threads` cores
+                "host_parse_ceiling_fps": world * frames_step / max(1e-9, parse_core_s / max(1, threads)),
+                "note": "end to end is bound by CABAC parsing on the host cores (host_parse_ceiling_fps): N GPUs share one host, so e2e does "
+                        "not scale with N on a single node; `value` (kernels) does"},
         "gpu_launches": int(launches), "clocks": clk,
-        "roofline": {"bound": "hbm", "kernel": "k_intra_wavefront", "achieved": intra_gbs, "peak": peak, "unit": "GB/s",
-                     "frac": intra_gbs / peak,
-                     # dram__bytes_read+write of one launch of this kernel on THIS workload, from the ncu --set full
-                     # capture summarised in profiles/r1_summary.md (r1_intra_final); other workloads: not captured
-                     "traffic": 1353.6e6 if wl == "stream_4k" else None, "peak_source": peak_src,
-                     "note": "largest share of the step; dependency-latency bound (CTB anti-diagonal wavefront, one warp "
-                             "walks a CTB), not bandwidth bound; algorithmic bytes per picture = 1.5*W*H written + 2 B per "
-                             "sample of a coded TB read; time = CUDA events around this launch only",
-                     "per_kernel_gbs": {"k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1),
-                                        "k_intra_wavefront": round(intra_gbs, 1),
+        "roofline": {"bound": "hbm", "kernel": dom[0], "achieved": dom[2] or 0.0, "peak": peak, "unit": "GB/s",
+                     "frac": (dom[2] or 0.0) / peak, "traffic": traffic, "peak_source": peak_src,
+                     "share_of_step": dom[1] / stage[5] if stage[5] else None,
+                     "note": "largest share of the step; " + dom[3] + "; time = CUDA events around this stage only",
+                     "per_kernel_gbs": {"k_mc": round(mc_gbs, 1) if mc_gbs else None,
+                                        "k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1) if res_gbs else None,
+                                        "k_intra_wavefront": round(intra_gbs, 1) if intra_gbs else None,
                                         "deblock(V+H luma/chroma, bS derived in-kernel, 4P per picture)": round(dbk_gbs, 1) if dbk_gbs else None,
+                                        "sao(stream's own parameters, 2P per picture)": round(own_sao_gbs, 1) if own_sao_gbs else None,
                                         "sao(synthetic per-CTB parameters on the same pictures, 2P per picture)": round(sao_gbs, 1) if sao_gbs else None}},
     }
     if rank == 0 and world == 1:
@@ -411,8 +480,13 @@ def run_reference_stream(a, wl):
     name, patched, loops, _, desc = STREAM_WL[wl]
     data = _stream_bytes(name, patched)
     gold = json.load(open(os.path.join(STREAMS, name + ".md5.json")))
+    if wl == "stream_4k" and a.gpus > 1 and c5_available():
+        # config 5: the eight independent streams our ranks decode, dealt over the dec265 processes
+        data = [_stream_bytes(n, patched) for n in C5_STREAMS]
+        gold = json.load(open(os.path.join(STREAMS, C5_STREAMS[0] + ".md5.json")))
+        desc += "; config 5: the eight independent streams (seeds 10..17) dealt over the processes"
     procs = host_cores()   # every core the box has: both arms see the same machine
-    one = run_dec265(data, 1, 1)
+    one = run_dec265(data[0] if isinstance(data, list) else data, 1, 1)
     if one is None:
         cb = cpu_port_stream(wl)
         v = cb["value"]

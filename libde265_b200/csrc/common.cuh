@@ -120,11 +120,16 @@ struct CtbRec {
   uint8_t mixed;   // bit c: ... and also samples produced by earlier launches (inter / PCM)
 };
 // control block of one launch of the wavefront (device memory, zeroed before k_intra_sched_prep)
+#define B265_MAX_CTB_ROWS 1024
 struct IntraSched {
   unsigned head;     // next queue index to hand to a warp
   unsigned tail;     // next queue index to fill
-  unsigned done;     // finished CTB rows
-  unsigned n_rows;   // CTB rows (per plane and picture) that hold intra TBs
+  unsigned done;     // finished runs
+  unsigned n_runs;   // runs = maximal sequences of horizontally adjacent CTBs with intra TBs (per plane and picture)
+  // runs per CTB-row level (all pictures and planes of the launch), counted by k_intra_prep; and how many of a level's
+  // queue positions are taken (k_intra_sched_prep): the runs of row r sit after all runs of row r - 1
+  unsigned level_cnt[B265_MAX_CTB_ROWS];
+  unsigned level_fill[B265_MAX_CTB_ROWS];
 };
 #define B265_QUEUE_EXIT 0xffffffffu   // queue payload: nothing left, the warp returns
 #define B265_QUEUE_SKIP 0xfffffffeu   // queue payload: a row without intra TBs

@@ -12,6 +12,22 @@
 #include "backend.h"
 #include "kernels.h"
 
+// A batch may hold pictures that reference earlier pictures of the same batch (P/B pictures in decoding order): it is
+// cut into LAUNCH GROUPS of consecutive pictures that do not reference each other; every kernel stage runs once per
+// group, the groups follow each other on the stream without a host round trip.  All-intra batches are one group.
+struct LaunchGroup {
+  int first = 0, n = 0;               // pictures [first, first + n) of the batch; list items carry frame indices relative to `first`
+  size_t mc0 = 0, mc1 = 0;            // ranges of the batch-wide lists that belong to this group
+  size_t res0[4] = {}, res1[4] = {}, ires0[4] = {}, ires1[4] = {};
+  int n_res_plain[4] = {0, 0, 0, 0}, n_ires_plain[4] = {0, 0, 0, 0};   // leading part of each range: plain DCT TUs (sizes 16, 32)
+  int n_tickets = 0;                  // (plane, CTB) units with intra TBs
+  int n_runs = 0;                     // runs of horizontally adjacent such units: the wavefront's queue entries
+  int max_slots = 0;                  // largest planes * CTBs of a picture (grid of the scheduling pre-pass)
+  int max_rows = 0;                   // largest CTB row count of a picture
+  int max_pcms = 0, max_tus = 0;
+  int log2_ctb = 4;                   // largest CTB (sizes the wavefront's shared-memory tiles)
+};
+
 struct b265_batch {
   int n_frames = 0;
   uint8_t* dev = nullptr;      // one allocation holding everything below
@@ -20,21 +36,17 @@ struct b265_batch {
   size_t upload_bytes = 0;
   // device pointers into dev
   FrameDev* d_frames = nullptr;
-  uint32_t* d_mc_items = nullptr;     int n_mc = 0;
-  uint32_t* d_res_order[4] = {};      int n_res[4] = {0, 0, 0, 0};     // inter TUs (residual added in place)
-  uint32_t* d_ires_order[4] = {};     int n_ires[4] = {0, 0, 0, 0};    // coded intra TUs (residual to scratch)
-  int n_res_plain[4] = {0, 0, 0, 0}, n_ires_plain[4] = {0, 0, 0, 0};   // leading part of each list: plain DCT TUs (sizes 16, 32)
-  int n_tickets = 0;                  // (plane, CTB) units with intra TBs in the whole batch
-  int max_slots = 0;                  // largest planes * CTBs of a picture (grid of the scheduling pre-pass)
-  int max_rows = 0;                   // largest CTB row count of a picture
-  IntraSched* d_sched = nullptr;      // wavefront control block and row queue: inside the zeroed region
+  uint32_t* d_mc_items = nullptr;
+  uint32_t* d_res_order[4] = {};      // inter TUs (residual added in place)
+  uint32_t* d_ires_order[4] = {};     // coded intra TUs (residual to scratch)
+  std::vector<LaunchGroup> groups;
+  int n_tickets = 0;
+  IntraSched* d_sched = nullptr;      // wavefront control block and row queue: start of the zeroed region, re-cleared per group
   unsigned long long* d_queue = nullptr;
   unsigned queue_entries = 0;         // power of two
+  size_t sched_bytes = 0;             // control block + queue
   uint8_t* d_zero_begin = nullptr;    size_t zero_bytes = 0;   // control block, queue, border mailboxes: cleared per run
   std::vector<FrameDev> frames;       // host copy (for post-filter launches)
-  int max_pcms = 0;                   // largest PCM block count of a picture
-  int max_tus = 0;
-  int log2_ctb = 4;                   // largest CTB of the batch (sizes the wavefront's shared-memory tiles)
   bool pooled = false;                // dev/host belong to the context's grow-only staging (b265_submit_frames)
 };
 
@@ -75,25 +87,54 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   std::vector<uint32_t> n_pieces(n_jobs, 0);
   std::vector<std::vector<CtbRec>> ctb_recs(n_jobs);   // per frame, raster order
   std::vector<uint32_t> ctb_area;   // samples covered by intra TBs, per plane and CTB
-  int n_tickets = 0, max_slots = 0, max_rows = 0;
+  std::vector<uint8_t> need_resid(n_jobs, 0);
+  std::vector<LaunchGroup>& groups = b->groups;
+  groups.clear();
+  auto close_group = [&](LaunchGroup& g) {
+    g.mc1 = mc.size();
+    for (int s = 0; s < 4; s++) { g.res1[s] = res[s].size(); g.ires1[s] = ires[s].size(); }
+  };
+  auto open_group = [&](int first) {
+    LaunchGroup g;
+    g.first = first;
+    g.mc0 = mc.size();
+    for (int s = 0; s < 4; s++) { g.res0[s] = res[s].size(); g.ires0[s] = ires[s].size(); }
+    groups.push_back(g);
+  };
   // ---- pass 1: classify; TUs arrive in decoding order, so the TUs of one CTB are contiguous ----
   for (int j = 0; j < n_jobs; j++) {
     const b265_frame_job& J = jobs[j];
     if (J.bit_depth != 8 || J.chroma_format_idc > 1 || J.n_tus >= (1 << 24) || J.n_pus >= (1 << 24))
       return reject(__LINE__, B265_ERR_UNSUPPORTED);
+    if (J.n_refs < 0 || J.n_refs > 16) return reject(__LINE__, B265_ERR_INVALID_ARG);
+    {  // a picture that reads a picture of the current group starts the next group
+      bool dependent = false;
+      if (!groups.empty())
+        for (int r = 0; r < J.n_refs && !dependent; r++)
+          for (int i = groups.back().first; i < j; i++)
+            if (J.ref_surfaces[r] == jobs[i].dst_surface) { dependent = true; break; }
+      if (groups.empty() || dependent) {
+        if (!groups.empty()) close_group(groups.back());
+        open_group(j);
+      }
+    }
+    LaunchGroup& G = groups.back();
+    G.n = j - G.first + 1;
+    const uint32_t jrel = (uint32_t)(j - G.first);
     const int cw_ = (J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb, ch_ = (J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb;
     const int nctb = cw_ * ch_;
-    if (nctb >= (1 << 20)) return reject(__LINE__, B265_ERR_UNSUPPORTED);   // queue entries carry the CTB number in 20 bits
     std::vector<CtbRec>& recs = ctb_recs[j];
     recs.assign(nctb, CtbRec{0, 0, 0, 0});
     ctb_area.assign((size_t)3 * nctb, 0);
     if (cw_ > 1023 || ch_ > 1023) return reject(__LINE__, B265_ERR_UNSUPPORTED);   // queue entries: 10 bits per CTB coordinate
-    max_slots = std::max(max_slots, (J.chroma_format_idc ? 3 : 1) * nctb);
-    max_rows = std::max(max_rows, ch_);
-    b->log2_ctb = std::max(b->log2_ctb, (int)J.log2_ctb);
     if (J.log2_ctb < 4 || J.log2_ctb > 6) return reject(__LINE__, B265_ERR_INVALID_ARG);
+    G.max_slots = std::max(G.max_slots, (J.chroma_format_idc ? 3 : 1) * nctb);
+    G.max_rows = std::max(G.max_rows, ch_);
+    G.log2_ctb = std::max(G.log2_ctb, (int)J.log2_ctb);
+    G.max_tus = std::max(G.max_tus, J.n_tus);
+    G.max_pcms = std::max(G.max_pcms, J.n_pcms);
     // FrameDev holds 16 reference slots (a DPB of 16 pictures is the HEVC maximum, A.4.2); slice indices travel in 8 bits
-    if (J.n_refs < 0 || J.n_refs > 16 || J.n_slices > 256) return reject(__LINE__, B265_ERR_INVALID_ARG);
+    if (J.n_slices > 256) return reject(__LINE__, B265_ERR_INVALID_ARG);
     int cur = -1;
     for (int i = 0; i < J.n_tus; i++) {
       const b265_tu& t = J.tus[i];
@@ -115,8 +156,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
         if (c && !J.chroma_format_idc) return reject(__LINE__, B265_ERR_INVALID_ARG);
         recs[ctb].has |= (uint8_t)(1 << c);
         ctb_area[(size_t)c * nctb + ctb] += 1u << (2 * lg);
-        if (t.ncoeff > 0) ires[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
-      } else if (t.ncoeff > 0) res[lg - 2].push_back(((uint32_t)j << 24) | (uint32_t)i);
+        if (t.ncoeff > 0) { ires[lg - 2].push_back((jrel << 24) | (uint32_t)i); need_resid[j] = 1; }
+      } else if (t.ncoeff > 0) res[lg - 2].push_back((jrel << 24) | (uint32_t)i);
     }
     for (int ctb = 0; ctb < nctb; ctb++) {
       if (!recs[ctb].has) continue;
@@ -124,7 +165,8 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
       const int bw = std::min(S, J.width - (ctb % cw_) * S), bh = std::min(S, J.height - (ctb / cw_) * S);
       for (int c = 0; c < 3; c++)
         if (recs[ctb].has & (1 << c)) {
-          n_tickets++;
+          G.n_tickets++;
+          if (ctb % cw_ == 0 || !(recs[ctb - 1].has & (1 << c))) G.n_runs++;
           // a CTB plane not fully covered by intra TBs also holds inter / PCM samples written by earlier launches
           const uint32_t full = (c && J.chroma_format_idc) ? (uint32_t)(((bw + 1) >> 1) * ((bh + 1) >> 1)) : (uint32_t)(bw * bh);
           if (ctb_area[(size_t)c * nctb + ctb] != full) recs[ctb].mixed |= (uint8_t)(1 << c);
@@ -140,28 +182,26 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
             ((pu.flags & B265_PU_L0) && (pu.ref_slot[0] >= J.n_refs || (uint8_t)pu.ref_idx[0] >= 16)) ||
             ((pu.flags & B265_PU_L1) && (pu.ref_slot[1] >= J.n_refs || (uint8_t)pu.ref_idx[1] >= 16)))
           return reject(__LINE__, B265_ERR_INVALID_ARG);
-        for (int k = pu_pieces(pu); k > 0; k--) mc.push_back(((uint32_t)j << 24) | n++);
+        for (int k = pu_pieces(pu); k > 0; k--) mc.push_back((jrel << 24) | n++);
       }
       if (n >= (1u << 24)) return reject(__LINE__, B265_ERR_UNSUPPORTED);
       n_pieces[j] = n;
     }
   }
   const double tb1 = t_now();
-  b->n_tickets = n_tickets;
-  b->max_slots = max_slots;
-  b->max_rows = max_rows;
-  b->n_mc = (int)mc.size();
-  // 16x16 / 32x32 lists: plain DCT TUs first (packed dp2a kernels), transform-skip / bypass TUs after them (generic kernel)
-  for (int s = 0; s < 4; s++) {
-    auto plain = [&](uint32_t o) { return !(jobs[o >> 24].tus[o & 0xffffff].flags & (B265_TU_SKIP | B265_TU_BYPASS)); };
-    b->n_res_plain[s] = b->n_ires_plain[s] = 0;
-    if (s >= 2) {
-      b->n_res_plain[s] = (int)(std::stable_partition(res[s].begin(), res[s].end(), plain) - res[s].begin());
-      b->n_ires_plain[s] = (int)(std::stable_partition(ires[s].begin(), ires[s].end(), plain) - ires[s].begin());
+  close_group(groups.back());
+  int n_tickets = 0, max_runs = 0;
+  for (LaunchGroup& g : groups) {
+    n_tickets += g.n_tickets;
+    max_runs = std::max(max_runs, g.n_runs);
+    // 16x16 / 32x32 lists: plain DCT TUs first (packed dp2a kernels), transform-skip / bypass TUs after them (generic kernel)
+    auto plain = [&](uint32_t o) { return !(jobs[g.first + (o >> 24)].tus[o & 0xffffff].flags & (B265_TU_SKIP | B265_TU_BYPASS)); };
+    for (int s = 2; s < 4; s++) {
+      g.n_res_plain[s] = (int)(std::stable_partition(res[s].begin() + g.res0[s], res[s].begin() + g.res1[s], plain) - (res[s].begin() + g.res0[s]));
+      g.n_ires_plain[s] = (int)(std::stable_partition(ires[s].begin() + g.ires0[s], ires[s].begin() + g.ires1[s], plain) - (ires[s].begin() + g.ires0[s]));
     }
-    b->n_res[s] = (int)res[s].size();
-    b->n_ires[s] = (int)ires[s].size();
   }
+  b->n_tickets = n_tickets;
 
   const double tb2 = t_now();
   // ---- layout ----
@@ -198,9 +238,10 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   if (!queue_slack) queue_slack = intra_queue_slack(ctx->sm_count);
   const size_t o_sched = P.take(sizeof(IntraSched));
   unsigned queue_entries = 1024;
-  while ((size_t)queue_entries < (size_t)3 * n_jobs * max_rows + (size_t)queue_slack) queue_entries <<= 1;
+  while ((size_t)queue_entries < (size_t)max_runs + (size_t)queue_slack) queue_entries <<= 1;
   b->queue_entries = queue_entries;
   const size_t o_queue = P.take(sizeof(unsigned long long) * (size_t)queue_entries);
+  b->sched_bytes = P.off - o_zero;
   struct SOff { size_t nbinfo, tmp[3], motion, resid[3], tb_mask, mbox[3]; int slot_base; };
   std::vector<SOff> so(n_jobs);
   {
@@ -238,9 +279,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     }
   }
   {  // int16 residual planes of the coded intra TBs (same geometry as the destination surface)
-    std::vector<uint8_t> need(n_jobs, 0);
-    for (int s = 0; s < 4; s++)
-      for (uint32_t o : ires[s]) need[o >> 24] = 1;
+    const std::vector<uint8_t>& need = need_resid;
     for (int j = 0; j < n_jobs; j++) {
       so[j].tb_mask = P.take((size_t)8 * jobs[j].n_tus);
       if (!need[j]) continue;
@@ -340,8 +379,6 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
     f.n_pcms = J.n_pcms;
     f.n_tus = J.n_tus;
     f.tb_mask = (uint64_t*)(D + so[j].tb_mask);
-    b->max_tus = std::max(b->max_tus, J.n_tus);
-    b->max_pcms = std::max(b->max_pcms, J.n_pcms);
     f.bs = nullptr;   // boundary strengths are derived inside the deblocking kernels
     f.motion = so[j].motion ? (uint32_t*)(D + so[j].motion) : nullptr;
     f.n_refs = J.n_refs;
@@ -356,13 +393,13 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
   const double tb4 = t_now();
   CK(cudaMemcpyAsync(D, H, b->upload_bytes, cudaMemcpyHostToDevice, ctx->stream));
   if (g_build_timing)
-    fprintf(stderr, "b265 build_batch n=%d: classify %.2f ms, list partition %.2f, layout+staging %.2f, copy %.2f, memcpyAsync call %.2f (%.1f MB)\n",
-            n_jobs, (tb1 - tb0) * 1e3, (tb2 - tb1) * 1e3, (tb3 - tb2) * 1e3, (tb4 - tb3) * 1e3, (t_now() - tb4) * 1e3, b->upload_bytes / 1e6);
+    fprintf(stderr, "b265 build_batch n=%d (%zu launch groups): classify %.2f ms, list partition %.2f, layout+staging %.2f, copy %.2f, memcpyAsync call %.2f (%.1f MB)\n",
+            n_jobs, groups.size(), (tb1 - tb0) * 1e3, (tb2 - tb1) * 1e3, (tb3 - tb2) * 1e3, (tb4 - tb3) * 1e3, (t_now() - tb4) * 1e3, b->upload_bytes / 1e6);
   return B265_OK;
 }
 
 // ------------------------------------------------------------------------------------------
-// Device work for one batch, all on ctx->stream:
+// Device work for one batch, all on ctx->stream; per launch group (pictures that do not reference each other):
 //   clear border mailboxes -> [pcm store] -> MC (all PUs) -> inter residual (4 sizes, in place)
 //   -> intra residual (4 sizes, to the int16 scratch planes) -> intra wavefront
 //   -> deblock V -> deblock H -> SAO
@@ -370,57 +407,67 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b2
 static int run_batch(b265_ctx* ctx, b265_batch* b) {
   cudaStream_t st = ctx->stream;
   const bool tm = ctx->stage_timing;
-  if (tm) cudaEventRecord(ctx->stage_ev[0], st);
+  if (tm) for (int i = 0; i < 6; i++) ctx->stage_ms[i] = 0;
   if (b->zero_bytes) CK(cudaMemsetAsync(b->d_zero_begin, 0, b->zero_bytes, st));
-  if (b->max_pcms) {
-    launch_pcm(st, b->d_frames, b->n_frames, b->max_pcms);
-    ctx->launches++;
-    CK_LAUNCH("k_pcm");
-  }
-  if (b->n_mc) {
-    launch_mc(st, b->d_frames, b->d_mc_items, b->n_mc, ctx->sm_count);
-    ctx->launches++;
-    CK_LAUNCH("k_mc");
-  }
-  if (tm) cudaEventRecord(ctx->stage_ev[1], st);
-  for (int pass = 0; pass < 2; pass++) {   // inter TUs in place, then intra TBs to the int16 scratch planes
-    const bool scratch = pass == 1;
-    for (int s = 0; s < 4; s++) {
-      const uint32_t* order = scratch ? b->d_ires_order[s] : b->d_res_order[s];
-      const int n = scratch ? b->n_ires[s] : b->n_res[s], n_plain = scratch ? b->n_ires_plain[s] : b->n_res_plain[s];
-      if (n_plain) {
-        launch_residual_sparse_fast(st, 2 + s, b->d_frames, order, n_plain, ctx->sm_count, scratch);
-        ctx->launches++;
-        CK_LAUNCH("k_residual_sparse_fast");
-      }
-      if (n > n_plain) {
-        launch_residual_sparse(st, 2 + s, b->d_frames, order + n_plain, n - n_plain, ctx->sm_count, scratch);
-        ctx->launches++;
-        CK_LAUNCH("k_residual_sparse");
+  for (size_t gi = 0; gi < b->groups.size(); gi++) {
+    const LaunchGroup& g = b->groups[gi];
+    const FrameDev* frames = b->d_frames + g.first;
+    const uint32_t* mc_items = b->d_mc_items + g.mc0;
+    const int n_mc = (int)(g.mc1 - g.mc0);
+    if (tm) cudaEventRecord(ctx->stage_ev[0], st);
+    if (g.max_pcms) {
+      launch_pcm(st, frames, g.n, g.max_pcms);
+      ctx->launches++;
+      CK_LAUNCH("k_pcm");
+    }
+    if (n_mc) {
+      launch_mc(st, frames, mc_items, n_mc, ctx->sm_count);
+      ctx->launches++;
+      CK_LAUNCH("k_mc");
+    }
+    if (tm) cudaEventRecord(ctx->stage_ev[1], st);
+    for (int pass = 0; pass < 2; pass++) {   // inter TUs in place, then intra TBs to the int16 scratch planes
+      const bool scratch = pass == 1;
+      for (int s = 0; s < 4; s++) {
+        const uint32_t* order = scratch ? b->d_ires_order[s] + g.ires0[s] : b->d_res_order[s] + g.res0[s];
+        const int n = (int)(scratch ? g.ires1[s] - g.ires0[s] : g.res1[s] - g.res0[s]);
+        const int n_plain = scratch ? g.n_ires_plain[s] : g.n_res_plain[s];
+        if (n_plain) {
+          launch_residual_sparse_fast(st, 2 + s, frames, order, n_plain, ctx->sm_count, scratch);
+          ctx->launches++;
+          CK_LAUNCH("k_residual_sparse_fast");
+        }
+        if (n > n_plain) {
+          launch_residual_sparse(st, 2 + s, frames, order + n_plain, n - n_plain, ctx->sm_count, scratch);
+          ctx->launches++;
+          CK_LAUNCH("k_residual_sparse");
+        }
       }
     }
-  }
-  if (b->n_tickets) {
-    launch_intra_prep(st, b->d_frames, b->n_frames, b->max_tus);
-    ctx->launches++;
-    CK_LAUNCH("k_intra_prep");
-  }
-  if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
-  if (b->n_tickets) {
-    launch_intra(st, b->d_frames, b->n_frames, b->max_slots, b->max_rows, b->n_tickets, b->d_sched, b->d_queue, b->queue_entries,
-                 ctx->sm_count, b->log2_ctb);
-    ctx->launches += 2;
-    CK_LAUNCH("k_intra_sched_prep + k_intra_wavefront");
-  }
-  if (tm) cudaEventRecord(ctx->stage_ev[3], st);
-  int r = launch_postfilters(ctx, b->d_frames, b->frames.data(), b->n_frames, tm ? ctx->stage_ev[4] : nullptr,
-                             b->d_mc_items, b->n_mc);
-  if (r) return r;
-  if (tm) {
-    cudaEventRecord(ctx->stage_ev[5], st);
-    CK(cudaEventSynchronize(ctx->stage_ev[5]));
-    for (int i = 0; i < 5; i++) cudaEventElapsedTime(&ctx->stage_ms[i], ctx->stage_ev[i], ctx->stage_ev[i + 1]);
-    cudaEventElapsedTime(&ctx->stage_ms[5], ctx->stage_ev[0], ctx->stage_ev[5]);
+    if (g.n_tickets) {
+      if (gi > 0) CK(cudaMemsetAsync(b->d_sched, 0, b->sched_bytes, st));   // control block + queue are shared by the groups
+      launch_intra_prep(st, frames, g.n, g.max_tus, g.max_slots, b->d_sched);
+      ctx->launches++;
+      CK_LAUNCH("k_intra_prep");
+    }
+    if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
+    if (g.n_tickets) {
+      launch_intra(st, frames, g.n, g.max_slots, g.max_rows, g.n_runs, b->d_sched, b->d_queue, b->queue_entries,
+                   ctx->sm_count, g.log2_ctb);
+      ctx->launches += 2;
+      CK_LAUNCH("k_intra_sched_prep + k_intra_wavefront");
+    }
+    if (tm) cudaEventRecord(ctx->stage_ev[3], st);
+    int r = launch_postfilters(ctx, frames, b->frames.data() + g.first, g.n, tm ? ctx->stage_ev[4] : nullptr, mc_items, n_mc);
+    if (r) return r;
+    if (tm) {   // per-stage times are summed over the groups (a host sync per group: timing runs only)
+      cudaEventRecord(ctx->stage_ev[5], st);
+      CK(cudaEventSynchronize(ctx->stage_ev[5]));
+      float ms = 0;
+      for (int i = 0; i < 5; i++) { cudaEventElapsedTime(&ms, ctx->stage_ev[i], ctx->stage_ev[i + 1]); ctx->stage_ms[i] += ms; }
+      cudaEventElapsedTime(&ms, ctx->stage_ev[0], ctx->stage_ev[5]);
+      ctx->stage_ms[5] += ms;
+    }
   }
   return B265_OK;
 }

@@ -364,28 +364,22 @@ struct Decoder {
           while (first < inflight.size() && inflight[first]->state >= de265_image::TAKEN) first++;
           size_t n = 0;
           // Reference pictures live in the surfaces of ONE context: the pictures between two DPB-emptying pictures
-          // (a "GOP") are pinned to the context that takes the first of them.  A batch never holds a picture
-          // together with one of its references (b265_submit_frames runs each stage for all pictures at once).
+          // (a "GOP") are pinned to the context that takes the first of them.  A batch may hold a picture together with
+          // its references: b265_submit_frames cuts it into launch groups that follow each other on the stream, so a
+          // run of P/B pictures costs one list upload and one host synchronisation, not one per picture.
           auto pinned_elsewhere = [&](const de265_image& im) {
             auto it = gop_ctx.find(im.pic.gop);
             return it != gop_ctx.end() && it->second != ci;
           };
-          auto depends_on_batch = [&](const de265_image& im) {
-            if (n == 0) return false;
-            const uint64_t lo = inflight[first]->pic.decode_index;
-            for (const auto& r : im.pic.ref_pics) if (r && r->decode_index >= lo) return true;
-            return false;
-          };
-          bool wrong_ctx = false, dependent = false;
+          bool wrong_ctx = false;
           while (first + n < inflight.size() && (int)n < max_batch && inflight[first + n]->state == de265_image::PARSED &&
                  inflight[first + n]->pic.width == inflight[first]->pic.width &&
                  inflight[first + n]->pic.height == inflight[first]->pic.height) {
             if (pinned_elsewhere(*inflight[first + n])) { wrong_ctx = true; break; }
-            if (depends_on_batch(*inflight[first + n])) { dependent = true; break; }
             n++;
           }
           if (wrong_ctx && n == 0) { cv_recon.wait(l); continue; }   // the other context's pictures come first
-          const bool blocked = dependent || wrong_ctx ||
+          const bool blocked = wrong_ctx ||
                                (first + n < inflight.size() && inflight[first + n]->state == de265_image::PARSED);  // geometry change
           bool take = n > 0 && ((int)n >= max_batch || draining || blocked || parse_only);
           if (!take && n > 0) {

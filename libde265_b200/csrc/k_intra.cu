@@ -15,17 +15,21 @@
 //    memory (intra.cuh), so global memory is read once per CTB (bordering row/column of the neighbouring
 //    CTBs, one L2 round trip after the flag wait) and never per TB.
 //
-// Scheduling (all on the device): the unit of work is one CTB ROW of one colour plane of one picture, walked left to right
-// by one warp (the shape of HEVC's own wavefront parallel processing).  Inside a row nothing is exchanged through memory:
-// the right column, the corner and the upper-right row piece of the CTB just finished ARE the left column, the corner and
-// the upper row piece of the next one, so they are moved inside the warp's shared-memory edge store.  Between rows the
-// bottom row of every CTB travels through a flag-in-data mailbox (below); a row needs the CTB above-right of its position,
-// i.e. it trails the row above by two CTBs, and the words it needs next are requested one CTB ahead.
-// Rows sit in a ring-buffer queue (row-major over the pictures of the batch).  A warp takes a row and runs it to the end;
-// when the row above is not far enough AND other rows are waiting in the queue, the warp puts its row (with the column
-// it reached) back at the end of the queue and takes another one, so blocked rows behind a textured CTB do not hold the
-// machine while other pictures have work; with nothing else to do it just keeps polling (lowest latency for a lone
-// picture).  (The give-back threshold is a launch parameter, B265_INTRA_YIELD_POLLS; measured best on B200: never.)  No dependency counters, no atomics and no fences on the path between two dependent CTBs.
+// Scheduling (all on the device): the unit of work is a RUN - a maximal sequence of horizontally adjacent CTBs that hold
+// intra TBs, in one colour plane of one picture - walked left to right by one warp.  In an all-intra picture a run is a
+// whole CTB row (the shape of HEVC's own wavefront parallel processing); in P/B pictures the scattered intra CTBs become
+// many short, mostly independent runs.  Inside a run nothing is exchanged through memory: the right column, the corner
+// and the upper-right row piece of the CTB just finished ARE the left column, the corner and the upper row piece of the
+// next one, so they are moved inside the warp's shared-memory edge store.  Between rows the bottom row of every CTB
+// travels through a flag-in-data mailbox (below); a run needs the CTB above-right of its position, i.e. it trails the row
+// above by two CTBs, and the words it needs next are requested one CTB ahead.
+// Runs sit in a ring-buffer queue ordered by CTB row (all runs of row r after all runs of row r - 1, over all pictures
+// and planes of the launch): a run only ever waits for runs of the row above, which were taken earlier by warps that are
+// running or done - so polling cannot deadlock for any grid size.  A warp takes a run and walks it to its end; when the
+// row above is not far enough AND other runs are waiting in the queue, the warp may put its run (with the column it
+// reached) back at the end of the queue and take another one; with nothing else to do it just keeps polling (lowest
+// latency for a lone picture).  (The give-back threshold is a launch parameter, B265_INTRA_YIELD_POLLS; measured best on
+// B200: never.)  No dependency counters, no atomics and no fences on the path between two dependent CTBs.
 //
 // HBM traffic per TB: N*N bytes written (+ 2*N*N bytes of residual read when the TB is coded).
 #include <stdio.h>
@@ -43,10 +47,23 @@
 #endif
 
 // ---------------------------------------------------------------------------------------------
-// k_intra_prep: availability mask of every intra TB (one thread per TU), FrameDev::tb_mask[tu]
+// k_intra_prep: availability mask of every intra TB (one thread per TU), FrameDev::tb_mask[tu];
+// and, one thread per (plane, CTB): the CTBs that start a run are counted per CTB-row level
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_intra_prep(const FrameDev* __restrict__ frames) {
+__device__ __forceinline__ bool run_start(const CtbRec* __restrict__ recs, int ctbs_w, int ctb, int c) {
+  if (!((recs[ctb].has >> c) & 1)) return false;
+  return (ctb % ctbs_w) == 0 || !((recs[ctb - 1].has >> c) & 1);
+}
+
+__global__ void __launch_bounds__(256) k_intra_prep(const FrameDev* __restrict__ frames, IntraSched* sched) {
   const FrameDev& f = frames[blockIdx.y];
+  {
+    const int nctb = f.ctbs_w * f.ctbs_h, planes = f.cw ? 3 : 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < planes * nctb; i += gridDim.x * blockDim.x) {
+      const int c = i / nctb, ctb = i - c * nctb;
+      if (run_start(f.ctb_rec, f.ctbs_w, ctb, c)) atomicAdd(&sched->level_cnt[ctb / f.ctbs_w], 1u);
+    }
+  }
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < f.n_tus; i += gridDim.x * blockDim.x) {
     const b265_tu tu = f.tus[i];
     if (tu.intra_mode == B265_INTRA_NONE) continue;
@@ -76,11 +93,11 @@ __global__ void __launch_bounds__(256) k_intra_prep(const FrameDev* __restrict__
   }
 }
 
-void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus) {
-  if (n_frames <= 0 || max_tus <= 0) return;
-  int gx = (max_tus + 255) / 256;
+void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus, int max_slots, IntraSched* sched) {
+  if (n_frames <= 0 || (max_tus <= 0 && max_slots <= 0)) return;
+  int gx = (std::max(max_tus, max_slots) + 255) / 256;
   if (gx > 592) gx = 592;
-  k_intra_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames);
+  k_intra_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -341,51 +358,61 @@ __device__ __forceinline__ void queue_put(unsigned long long* queue, unsigned ma
 }
 
 // Per (plane, CTB) slot: which neighbouring CTBs may be used for prediction (same slice, same tile, earlier in decoding
-// order; intrapred.cc:486-508): bit0 left, bit1 upper-left, bit2 upper, bit3 upper-right.  The thread of a row's first CTB
-// also enters the row into the queue at its row-major position (row, frame, plane): early rows of all pictures first.
+// order; intrapred.cc:486-508): bit0 left, bit1 upper-left, bit2 upper, bit3 upper-right.  The thread of a CTB that starts
+// a run also enters the run into the queue, inside the index range of its CTB-row level: level_base[row] (exclusive scan of
+// the per-level counts of k_intra_prep, recomputed by every block) + the level's fill counter.  A run only waits for runs
+// of the row above, which therefore all have smaller queue indices - whatever the order inside a level.
 __global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __restrict__ frames, IntraSched* sched, unsigned long long* queue,
                                                           unsigned qmask, int max_rows) {
+  __shared__ unsigned s_base[B265_MAX_CTB_ROWS];
+  __shared__ unsigned s_part[256];
+  {  // exclusive scan of level_cnt[0 .. max_rows): 4 levels per thread
+    unsigned v[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const int l = 4 * threadIdx.x + k;
+      v[k] = l < max_rows ? ld_cg_u32(&sched->level_cnt[l]) : 0u;
+      sum += v[k];
+    }
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 256; o <<= 1) {
+      const unsigned add = threadIdx.x >= (unsigned)o ? s_part[threadIdx.x - o] : 0u;
+      __syncthreads();
+      s_part[threadIdx.x] += add;
+      __syncthreads();
+    }
+    unsigned run = s_part[threadIdx.x] - sum;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { s_base[4 * threadIdx.x + k] = run; run += v[k]; }
+    if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 255) { sched->tail = s_part[255]; sched->n_runs = s_part[255]; }
+    __syncthreads();
+  }
   const FrameDev& f = frames[blockIdx.y];
   const int nctb = f.ctbs_w * f.ctbs_h, planes = f.cw ? 3 : 1;
   const CtbRec* __restrict__ recs = f.ctb_rec;
   const b265_ctb* __restrict__ ctbs = f.ctbs;
-  const int n_frames = gridDim.y;
-  if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) sched->tail = (unsigned)(3 * n_frames * max_rows);
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < 3 * max(nctb, max_rows); i += gridDim.x * blockDim.x) {
-    if (i < planes * nctb) {
-      const int c = i / nctb, ctb = i - c * nctb;
-      const int cx = ctb % f.ctbs_w, cy = ctb / f.ctbs_w;
-      uint32_t nb = 0;
-      if ((recs[ctb].has >> c) & 1) {
-        const b265_ctb me = ctbs ? ctbs[ctb] : b265_ctb{0, 0, 0};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < planes * nctb; i += gridDim.x * blockDim.x) {
+    const int c = i / nctb, ctb = i - c * nctb;
+    const int cx = ctb % f.ctbs_w, cy = ctb / f.ctbs_w;
+    uint32_t nb = 0;
+    if ((recs[ctb].has >> c) & 1) {
+      const b265_ctb me = ctbs ? ctbs[ctb] : b265_ctb{0, 0, 0};
 #pragma unroll
-        for (int k = 0; k < 4; k++) {  // left, upper-left, upper, upper-right
-          const int nx = cx + (k == 3 ? 1 : (k == 2 ? 0 : -1)), ny = cy - (k == 0 ? 0 : 1);
-          if (nx < 0 || ny < 0 || nx >= f.ctbs_w) continue;
-          bool ok = true;
-          if (ctbs) {
-            const b265_ctb r = ctbs[ny * f.ctbs_w + nx];
-            ok = r.slice == me.slice && r.tile == me.tile && r.addr_ts < me.addr_ts;
-          }
-          if (ok) nb |= 1u << k;
+      for (int k = 0; k < 4; k++) {  // left, upper-left, upper, upper-right
+        const int nx = cx + (k == 3 ? 1 : (k == 2 ? 0 : -1)), ny = cy - (k == 0 ? 0 : 1);
+        if (nx < 0 || ny < 0 || nx >= f.ctbs_w) continue;
+        bool ok = true;
+        if (ctbs) {
+          const b265_ctb r = ctbs[ny * f.ctbs_w + nx];
+          ok = r.slice == me.slice && r.tile == me.tile && r.addr_ts < me.addr_ts;
         }
+        if (ok) nb |= 1u << k;
       }
-      f.nbinfo[i] = (uint8_t)nb;
+      if (run_start(recs, f.ctbs_w, ctb, c))
+        queue_put(queue, qmask, s_base[cy] + atomicAdd(&sched->level_fill[cy], 1u), row_payload(blockIdx.y, c, cy, cx));
     }
-    // rows: slot i < 3 * max_rows is (plane, row) = (i / max_rows, i % max_rows)
-    if (i < 3 * max_rows) {
-      const int c = i / max_rows, row = i - c * max_rows;
-      uint32_t payload = B265_QUEUE_SKIP;
-      if (c < planes && row < f.ctbs_h) {
-        for (int cx = 0; cx < f.ctbs_w; cx++)
-          if ((recs[row * f.ctbs_w + cx].has >> c) & 1) {
-            payload = row_payload(blockIdx.y, c, row, cx);
-            atomicAdd(&sched->n_rows, 1u);
-            break;
-          }
-      }
-      queue_put(queue, qmask, (unsigned)((row * n_frames + (int)blockIdx.y) * 3 + c), payload);
-    }
+    f.nbinfo[i] = (uint8_t)nb;
   }
 }
 
@@ -400,7 +427,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
   __shared__ __align__(16) uint8_t s_border[INTRA_WARPS][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
   uint8_t* my_edges = dyn_smem + (size_t)warp * tile_bytes;
-  const unsigned n_rows = ld_cg_u32(&sched->n_rows);
+  const unsigned n_runs = ld_cg_u32(&sched->n_runs);
   // picture / plane constants of the current row, reloaded only when a queue entry names another picture or plane
   IntraGeom g;
   int ctbs_w = 1, cur_frame = -1, cur_plane = -1, slot_base = 0;
@@ -551,18 +578,18 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
         chained = true;
         nb_prev = nb;
       } else {
-        chained = false;
+        break;   // a CTB without intra TBs ends the run: the next intra CTB of the row starts a run of its own
       }
       cx++;
       rr = rr_next; nb = nb_next; pre = pre_next;
     }
     if (yielded) continue;
-    // ---- row finished ----
+    // ---- run finished ----
     unsigned old = 0;
     if (lane == 0) old = atomicAdd(&sched->done, 1u);
     old = __shfl_sync(B265_FULL_MASK, old, 0);
-    if (old == n_rows - 1) {
-      // every row is finished: at most total_warps warps sleep or are about to, on consecutive indices >= tail
+    if (old == n_runs - 1) {
+      // every run is finished: at most total_warps warps sleep or are about to, on consecutive indices >= tail
       const unsigned tail = ld_relaxed_u32(&sched->tail);
       for (unsigned i = lane; i < total_warps; i += 32) queue_put(queue, qmask, tail + i, B265_QUEUE_EXIT);
       return;
@@ -587,14 +614,14 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb) {
 // queue entries beyond the rows themselves: one exit marker per warp that can be resident
 int intra_queue_slack(int sm_count) { return intra_max_resident_ctas(sm_count, 4) * INTRA_WARPS + 64; }
 
-void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_tickets, IntraSched* sched,
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_runs, IntraSched* sched,
                   unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb) {
-  if (n_tickets <= 0) return;
+  if (n_runs <= 0) return;
   static int max_ctas[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (!max_ctas[log2_ctb & 7]) max_ctas[log2_ctb & 7] = intra_max_resident_ctas(sm_count, log2_ctb);
   const unsigned qmask = queue_entries - 1;
   {
-    int gx = (std::max(max_slots, 3 * max_rows) + 255) / 256;
+    int gx = (max_slots + 255) / 256;
     if (gx > 4 * sm_count) gx = 4 * sm_count;
     k_intra_sched_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched, queue, qmask, max_rows);
   }
@@ -613,8 +640,8 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     yield_polls = y ? atoi(y) : 0x7fffffff;
     if (yield_polls < 1) yield_polls = 1;
   }
-  // one warp per row is all a launch can use
-  int ctas = (3 * n_frames * max_rows + INTRA_WARPS - 1) / INTRA_WARPS;
+  // one warp per run is all a launch can use
+  int ctas = (n_runs + INTRA_WARPS - 1) / INTRA_WARPS;
   if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
   if (cap_per_sm > 0 && ctas > cap_per_sm * sm_count) ctas = cap_per_sm * sm_count;
   const unsigned total_warps = (unsigned)ctas * INTRA_WARPS;

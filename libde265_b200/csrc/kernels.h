@@ -25,11 +25,13 @@ void launch_intra_blocks(cudaStream_t st, int log2, int cidx, int n_blocks, cons
 void launch_interp_blocks(cudaStream_t st, int luma, int n_blocks, int w, int h, const uint8_t* src, long long src_stride,
                           long long src_block_stride, const uint8_t* frac_xy, int16_t* out);
 // availability masks of all intra TBs (k_intra.cu), grid (.., n_frames)
-void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus);
+// availability masks of all intra TBs + runs per CTB-row level (k_intra.cu), grid (.., n_frames); `sched` is zero
+void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, int max_tus, int max_slots, IntraSched* sched);
 int intra_max_resident_ctas(int sm_count, int log2_ctb);
-// neighbour masks + row queue (grid over the (plane, CTB) slots of every frame), then the wavefront itself; `queue` has
-// `queue_entries` (a power of two >= 3 * n_frames * max_rows + intra_queue_slack()) 8-byte entries and is zero, `sched` is zero
-void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_tickets, IntraSched* sched,
+// neighbour masks + run queue (grid over the (plane, CTB) slots of every frame), then the wavefront itself; after
+// launch_intra_prep on the same frames.  `queue` has `queue_entries` (a power of two >= n_runs + intra_queue_slack())
+// 8-byte entries and is zero
+void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_runs, IntraSched* sched,
                   unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb);
 int intra_queue_slack(int sm_count);
 // decoded picture hash of n pictures (k_hash.cu): type 0 MD5, 1 CRC, 2 checksum (sei.h sei_decoded_picture_hash_type);

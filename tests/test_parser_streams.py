@@ -14,31 +14,7 @@ from libde265_b200.decoder import Decoder
 STREAMS = os.path.join(GOLDEN, "streams")
 
 
-def oracle_planes(job, dpb=None):
-    """reconstruct one picture with the C oracle; `dpb` maps the ids a parse-only decoder puts into
-    ref_surfaces / dst_surface to the finished pictures (inter prediction)"""
-    o = load_oracle()
-    w, h = job.width, job.height
-    planes = [np.zeros((h, w), np.uint8), np.zeros((h // 2, w // 2), np.uint8), np.zeros((h // 2, w // 2), np.uint8)]
-    pp = (C.c_void_p * 3)(*[p.ctypes.data for p in planes])
-    pitch = (C.c_int * 3)(w, w // 2, w // 2)
-    refs = None
-    if job.n_refs:
-        # a reference the stream never delivered is the mid-grey picture of 8.3.3.2 (decctx.cc:1408-1434)
-        grey = [np.full((h, w), 128, np.uint8), np.full((h // 2, w // 2), 128, np.uint8), np.full((h // 2, w // 2), 128, np.uint8)]
-        pics = [dpb.setdefault(job.ref_surfaces[i], grey) for i in range(job.n_refs)]
-        refs = (C.c_void_p * (3 * job.n_refs))(*[p.ctypes.data for pl in pics for p in pl])
-    o.orc_reconstruct_frame(C.byref(job), pp, pitch, refs)
-    if job.flags & L.FRAME_DEBLOCK:
-        o.orc_deblock(C.byref(job), pp, pitch)
-    if job.flags & L.FRAME_SAO:
-        outs = [np.zeros_like(p) for p in planes]
-        op = (C.c_void_p * 3)(*[p.ctypes.data for p in outs])
-        o.orc_sao(C.byref(job), pp, op, pitch)
-        planes = outs
-    if dpb is not None:
-        dpb[job.dst_surface] = planes
-    return planes
+from oracle.frame import oracle_planes  # noqa: E402,F401  (the C oracle on one picture's work lists)
 
 
 def parse_and_reconstruct(data, threads=0, max_frames=None):

@@ -87,6 +87,14 @@ NAMED = {
     "gen_hash_pb_mixed_256x192": dict(seed=64, w=256, h=192, frames=6, inter=1, max_refs=2, tmvp=1, sao=1, post={"sei_hash": -1}),
     "gen_hash_wrong_256x192": dict(seed=64, w=256, h=192, frames=6, inter=1, max_refs=2, tmvp=1, sao=1,
                                    post={"sei_hash": -1, "corrupt_hash": 3}),
+    # ---- P/B streams at the sizes the metric names (BASELINE north_star: 1080p and 4K): low-delay and random-access
+    #      shapes, >= 32 pictures at 1080p, weighted prediction + temporal MVP + SAO on, mostly skipped / merged large blocks ----
+    "gen_pb_1080p_ld32": dict(seed=71, w=1920, h=1080, frames=32, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_pred=1,
+                              weighted_bipred=1, p_skip=0.6, p_split_cu=0.3, p_split_tu=0.25, density=0.5, p_intra_cu=0.1),
+    "gen_pb_1080p_ra33": dict(seed=72, w=1920, h=1080, frames=33, inter=1, reorder=1, max_refs=3, tmvp=1, amp=1, sao=1,
+                              weighted_bipred=1, p_bslice=0.9, p_skip=0.6, p_split_cu=0.3, p_split_tu=0.25, density=0.5, p_intra_cu=0.1),
+    "gen_pb_2160p_ld12": dict(seed=73, w=3840, h=2160, frames=12, inter=1, max_refs=2, tmvp=1, amp=1, sao=1, weighted_pred=1,
+                              p_skip=0.65, p_split_cu=0.25, p_split_tu=0.2, density=0.4, p_intra_cu=0.08),
     "gen_pb_720p": dict(seed=47, w=1280, h=720, frames=4, inter=1, max_refs=3, tmvp=1, amp=1, sao=1, weighted_bipred=1,
                         slice_ctbs=200, p_skip=0.5),
 }

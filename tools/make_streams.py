@@ -95,6 +95,9 @@ STREAMS = {
     "c1_1080p_q22": (1920, 1080, 1, 4, 1, 22, 1.0, []),         # coefficient-heavy variant
     "c4_2160p_q32": (3840, 2160, 4, 8, 1, 32, 2.0, []),         # config 4 base (PPS-patched => deblock on)
 }
+# config 5: eight INDEPENDENT 4K streams (seeds 10..17, 4 frames each), one per GPU / decoder instance
+for _s in range(10, 18):
+    STREAMS["c5_2160p_s%d" % _s] = (3840, 2160, _s, 4, 1, 32, 2.0, [])
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
