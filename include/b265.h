@@ -90,6 +90,19 @@ B265_API int b265_surface_plane(b265_ctx* ctx, int surface_id, int plane, void**
  * b265_sync(); `out` should be pinned (b265_host_alloc). */
 B265_API int b265_surface_hash(b265_ctx* ctx, const int* surface_ids, int n, int hash_type, uint8_t* out);
 
+/* CRC (the hash_type 1 value of b265_surface_hash) of ONE plane, for callers that cannot allocate: code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * The call allocates nothing (no cudaMalloc / cudaFree, no growable context buffer): its per-row
+ * scratch is a static device array of B265_CRC_NOALLOC_MAX_ROWS 16-bit entries (16 KB, held by every GPU that loads the
+ * library until exit).  dev_plane = device pointer to `height` rows of `width` 8-bit samples, `pitch` bytes apart
+ * (address, pitch and width multiples of 4); dev_crc = device pointer to one 32-bit word that receives the CRC.
+ * Asynchronous on the context stream (valid after b265_sync or any later work on that stream).
+ * height > B265_CRC_NOALLOC_MAX_ROWS -> B265_ERR_UNSUPPORTED with the reason in b265_last_error().
+ * All calls share the scratch: calls that overlap on the GPU (other streams, contexts or threads) RACE - serialise them. */
+#define B265_CRC_NOALLOC_MAX_ROWS 8192
+B265_API int b265_plane_crc_noalloc(b265_ctx* ctx, const uint8_t* dev_plane, int pitch, int width, int height,
+                                    uint32_t* dev_crc);
+
 /* ------------------------------------------------------------------------------------------
  * A.2  Work-list records (all little-endian PODs, written by the host parser into pinned memory)
  * ------------------------------------------------------------------------------------------ */

@@ -198,3 +198,95 @@ int launch_hash(cudaStream_t st, int type, const HashJob* jobs, int n, int max_h
   k_hash_checksum<<<dim3(64, 3, n), 256, 0, st>>>(jobs, out);
   return 1;
 }
+
+// ------------------------------------------------------------------------------------------------------------------
+// b265_plane_crc_noalloc: the CRC of one plane for callers that must not allocate (code under CUDA graph capture, tight
+// serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same arithmetic as k_hash_crc_rows / k_hash_crc_fold above, but the per-row scratch lives in a file-scope
+// device array of fixed size instead of the context's growable buffer, and the job description travels as kernel
+// arguments instead of through device memory.  Every GPU that loads the library holds the array until exit (16 KB).
+//   * all calls share the array: calls that overlap on the GPU (different streams / contexts / threads) race;
+//   * the array keeps the last call's contents: a call writes rows [0, height) before the fold reads them, nothing has
+//     to start at zero.
+// ------------------------------------------------------------------------------------------------------------------
+#include <mutex>
+#include <string>
+#include "backend.h"
+
+static __device__ __align__(256) uint16_t g_crc_row_scratch[B265_CRC_NOALLOC_MAX_ROWS];
+
+namespace {
+
+__global__ void __launch_bounds__(128) k_crc_rows_static(const uint8_t* __restrict__ plane, int pitch, int w, int h, uint16_t* __restrict__ rows) {
+  for (int y = blockIdx.x * blockDim.x + threadIdx.x; y < h; y += gridDim.x * blockDim.x) {
+    const uint32_t* p = reinterpret_cast<const uint32_t*>(plane + (size_t)y * pitch);
+    uint32_t crc = 0;
+    for (int i = 0; i < w / 4; i++) {
+      const uint32_t v = p[i];
+      crc = crc_byte(crc, v & 0xff);
+      crc = crc_byte(crc, (v >> 8) & 0xff);
+      crc = crc_byte(crc, (v >> 16) & 0xff);
+      crc = crc_byte(crc, v >> 24);
+    }
+    rows[y] = (uint16_t)crc;
+  }
+}
+
+__global__ void k_crc_fold_static(const uint16_t* __restrict__ rows, int w, int h, uint32_t* __restrict__ out) {
+  if (threadIdx.x || blockIdx.x) return;
+  uint16_t m[16], r[16];
+  for (int k = 0; k < 16; k++) { m[k] = (uint16_t)crc_byte(1u << k, 0); r[k] = (uint16_t)(1u << k); }
+  auto apply = [](const uint16_t* mat, uint32_t v) {
+    uint32_t o = 0;
+    for (int k = 0; k < 16; k++) if ((v >> k) & 1) o ^= mat[k];
+    return o;
+  };
+  for (int e = w; e; e >>= 1) {
+    uint16_t t[16];
+    if (e & 1) { for (int k = 0; k < 16; k++) t[k] = (uint16_t)apply(m, r[k]); for (int k = 0; k < 16; k++) r[k] = t[k]; }
+    for (int k = 0; k < 16; k++) t[k] = (uint16_t)apply(m, m[k]);
+    for (int k = 0; k < 16; k++) m[k] = t[k];
+  }
+  uint32_t crc = 0xffff;
+  crc = crc_byte(crc, 0);
+  crc = crc_byte(crc, 0);
+  for (int y = 0; y < h; y++) crc = apply(r, crc) ^ rows[y];
+  *out = crc;
+}
+
+// In host code `g_crc_row_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+std::mutex g_scratch_mu;
+uint16_t* g_scratch_ptr[64] = {};
+
+}  // namespace
+
+extern "C" int b265_plane_crc_noalloc(b265_ctx* ctx, const uint8_t* dev_plane, int pitch, int width, int height, uint32_t* dev_crc) {
+  if (!ctx || !dev_plane || !dev_crc || width <= 0 || height <= 0 || pitch < width) return B265_ERR_INVALID_ARG;
+  if ((width & 3) || (pitch & 3) || (reinterpret_cast<uintptr_t>(dev_plane) & 3) || (reinterpret_cast<uintptr_t>(dev_crc) & 3)) {
+    ctx->last_error = "b265_plane_crc_noalloc: plane address, pitch and width must be multiples of 4 (rows are read as 32-bit words)";
+    return B265_ERR_INVALID_ARG;
+  }
+  if (height > B265_CRC_NOALLOC_MAX_ROWS) {
+    ctx->last_error = "b265_plane_crc_noalloc: height " + std::to_string(height) + " exceeds the static scratch of " +
+                      std::to_string(B265_CRC_NOALLOC_MAX_ROWS) + " rows (B265_CRC_NOALLOC_MAX_ROWS); use b265_surface_hash";
+    return B265_ERR_UNSUPPORTED;
+  }
+  if (ctx->device < 0 || ctx->device >= 64) return B265_ERR_INVALID_ARG;
+  CK(cudaSetDevice(ctx->device));
+  uint16_t* rows = nullptr;
+  {
+    std::lock_guard<std::mutex> l(g_scratch_mu);
+    if (!g_scratch_ptr[ctx->device]) {
+      void* p = nullptr;
+      CK(cudaGetSymbolAddress(&p, g_crc_row_scratch));
+      g_scratch_ptr[ctx->device] = static_cast<uint16_t*>(p);
+    }
+    rows = g_scratch_ptr[ctx->device];
+  }
+  k_crc_rows_static<<<(height + 127) / 128, 128, 0, ctx->stream>>>(dev_plane, pitch, width, height, rows);
+  k_crc_fold_static<<<1, 32, 0, ctx->stream>>>(rows, width, height, dev_crc);
+  ctx->launches += 2;
+  CK_LAUNCH("k_crc_rows_static + k_crc_fold_static");
+  return B265_OK;
+}
