@@ -78,9 +78,28 @@ static int reject(int line, int code) {
 static double t_now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 static const bool g_build_timing = getenv("B265_BUILD_TIMING") != nullptr;   // developer aid: host time of build_batch by section
 
-static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs, b265_batch* b) {
+static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs_in, int n_jobs, b265_batch* b) {
   const double tb0 = t_now();
   if (n_jobs > 255) return reject(__LINE__, B265_ERR_INVALID_ARG);
+  // Pictures are reordered by DEPENDENCY LEVEL inside the batch (level = 1 + the highest level among the pictures of this
+  // batch it references; stable otherwise): all pictures of a level form one launch group, so the I pictures of a batch -
+  // and every picture whose references were finished by earlier submits - share their launches instead of paying the
+  // latency of the intra wavefront one by one.  Destination surfaces of a batch are distinct and none is recycled inside
+  // it, so the order among independent pictures is free.
+  std::vector<b265_frame_job> ordered(jobs_in, jobs_in + n_jobs);
+  {
+    std::vector<int> level(n_jobs, 0), idx(n_jobs);
+    for (int j = 0; j < n_jobs; j++) {
+      idx[j] = j;
+      const b265_frame_job& J = jobs_in[j];
+      for (int r = 0; r < J.n_refs && r < 16; r++)
+        for (int i = 0; i < j; i++)
+          if (J.ref_surfaces[r] == jobs_in[i].dst_surface) level[j] = std::max(level[j], level[i] + 1);
+    }
+    std::stable_sort(idx.begin(), idx.end(), [&](int a, int c) { return level[a] < level[c]; });
+    for (int j = 0; j < n_jobs; j++) ordered[j] = jobs_in[idx[j]];
+  }
+  const b265_frame_job* jobs = ordered.data();
   b->n_frames = n_jobs;
   b->frames.assign(n_jobs, FrameDev());
   std::vector<uint32_t> res[4], ires[4], mc;

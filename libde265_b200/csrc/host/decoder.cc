@@ -359,9 +359,14 @@ struct Decoder {
         std::unique_lock<std::mutex> l(mu);
         for (;;) {
           if (stop) return;
-          // first picture not yet taken by a recon thread
+          // first picture not yet taken by a recon thread that this context may take: pictures of a GOP pinned to another
+          // context are skipped - no reference crosses a GOP boundary, so the next GOP can be reconstructed on this
+          // context's stream while the other context is still busy with its own (pictures retire in decoding order anyway)
           size_t first = 0;
-          while (first < inflight.size() && inflight[first]->state >= de265_image::TAKEN) first++;
+          while (first < inflight.size() &&
+                 (inflight[first]->state >= de265_image::TAKEN ||
+                  [&] { auto it = gop_ctx.find(inflight[first]->pic.gop); return it != gop_ctx.end() && it->second != ci; }()))
+            first++;
           size_t n = 0;
           // Reference pictures live in the surfaces of ONE context: the pictures between two DPB-emptying pictures
           // (a "GOP") are pinned to the context that takes the first of them.  A batch may hold a picture together with

@@ -7,7 +7,7 @@
 //  * k_intra_blocks: intra_prediction_sample_filtering + planar/DC/angular (intrapred.cc:816-1069)
 //    from explicit border arrays, the same device functions the wavefront uses (intra.cuh).
 //  * k_interp_blocks: put_hevc_qpel_8 / put_hevc_epel_8 slots (fallback-motion.cc:298-407, 482-625).
-#include "intra.cuh"
+#include "intra_seg.cuh"
 #include "kernels.h"
 
 // ---------------------------------------------------------------------------------------------
@@ -39,42 +39,42 @@ void launch_pcm(cudaStream_t st, const FrameDev* frames, int n_frames, int max_p
 }
 
 // ---------------------------------------------------------------------------------------------
-// intra prediction of isolated blocks: a group of N lanes per block, 32/N blocks per warp
+// intra prediction of isolated blocks: one block per warp, the size-independent code of the wavefront (intra_seg.cuh)
 // ---------------------------------------------------------------------------------------------
-template <int LOG2>
-__global__ void __launch_bounds__(128) k_intra_blocks(int cidx, int n_blocks, const uint8_t* __restrict__ modes,
+__global__ void __launch_bounds__(128) k_intra_blocks(int log2, int cidx, int n_blocks, const uint8_t* __restrict__ modes,
                                                       const uint8_t* __restrict__ borders, int strong, int no_edge_filter,
                                                       uint8_t* __restrict__ out) {
-  constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE;
+  const int N = 1 << log2;
   __shared__ __align__(16) uint8_t sm[4][B265_BORDER_BYTES];
   const int warp = threadIdx.x >> 5, lane = lane_id();
-  const int blk = blockIdx.x * 4 + warp;   // one block per warp (lanes 0..N-1), as in the wavefront
+  const int blk = blockIdx.x * 4 + warp;   // one block per warp, as in the wavefront
   if (blk >= n_blocks) return;
   uint8_t* buf0 = sm[warp];
-  uint8_t* buf1 = buf0 + STRIDE;
+  uint8_t* buf1 = buf0 + ibuf_stride(N);
   const int mode = modes[blk];
   {  // p[-2N..2N] -> the two border lines T[k] = p[k], L[k] = p[-k]
     const uint8_t* p = borders + (size_t)blk * (4 * N + 1) + 2 * N;
     for (int k = lane; k <= 2 * N; k += 32) {
-      buf0[IntraBuf<N>::TOP + k] = p[k];
-      buf0[IntraBuf<N>::LEFT + k] = p[-k];
+      buf0[ibuf_top(N) + k] = p[k];
+      buf0[ibuf_left(N) + k] = p[-k];
     }
   }
   __syncwarp();
-  uint8_t* pb = filter_border<LOG2>(buf0, buf1, lane, mode, cidx, strong != 0);
-  uint32_t h[N / 2];
-  const bool by_column = predict_line<LOG2>(pb, lane, mode, cidx, !no_edge_filter, h);
-  if (lane < N) {
-    uint32_t px[N / 4];
-    const uint32_t none[N / 2] = {};
-    finish_line<N>(h, none, false, px);
-    uint8_t* d = out + (size_t)blk * N * N;
-    if (!by_column) {
-#pragma unroll
-      for (int q = 0; q < N / 4; q++) reinterpret_cast<uint32_t*>(d + lane * N)[q] = px[q];
-    } else {
-#pragma unroll
-      for (int j = 0; j < N; j++) d[j * N + lane] = (uint8_t)(px[j >> 2] >> (8 * (j & 3)));
+  uint8_t* pb = filter_border_rt(buf0, buf1, N, lane, mode, cidx, strong != 0);
+  IntraPred P;
+  intra_pred_setup(P, pb, N, log2, lane, mode, cidx, !no_edge_filter);
+  const int lseg = log2 < 3 ? 0 : log2 - 3, items = N << lseg, nvalid = log2 == 2 ? 4 : 8;
+  uint8_t* d = out + (size_t)blk * N * N;
+  for (int item = lane; item < items; item += 32) {
+    const int l = item >> lseg, sg = item & ((1 << lseg) - 1);
+    uint32_t h[4], px[2];
+    const uint32_t none[4] = {0, 0, 0, 0};
+    intra_pred_seg(P, l, sg, h);
+    finish_seg(h, none, false, px);
+    for (int j = 0; j < nvalid; j++) {
+      const uint8_t v = (uint8_t)(px[j >> 2] >> (8 * (j & 3)));
+      if (!P.by_column) d[l * N + 8 * sg + j] = v;
+      else d[(8 * sg + j) * N + l] = v;
     }
   }
 }
@@ -82,13 +82,7 @@ __global__ void __launch_bounds__(128) k_intra_blocks(int cidx, int n_blocks, co
 void launch_intra_blocks(cudaStream_t st, int log2, int cidx, int n_blocks, const uint8_t* modes, const uint8_t* borders,
                          int strong, int no_edge_filter, uint8_t* out) {
   if (n_blocks <= 0) return;
-  const int grid = (n_blocks + 3) / 4;
-  switch (log2) {
-    case 2: k_intra_blocks<2><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;
-    case 3: k_intra_blocks<3><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;
-    case 4: k_intra_blocks<4><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;
-    default: k_intra_blocks<5><<<grid, 128, 0, st>>>(cidx, n_blocks, modes, borders, strong, no_edge_filter, out); break;
-  }
+  k_intra_blocks<<<(n_blocks + 3) / 4, 128, 0, st>>>(log2, cidx, n_blocks, modes, borders, strong, no_edge_filter, out);
 }
 
 // ---------------------------------------------------------------------------------------------

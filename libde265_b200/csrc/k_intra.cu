@@ -38,9 +38,20 @@
 #include <vector>
 #include "transform.cuh"
 #include "intra.cuh"
+#include "intra_seg.cuh"
 #include "kernels.h"
 
 
+// log2 sizes whose TBs take the size-independent segment code (intra_seg.cuh) instead of their own unrolled instantiation.
+// Measured on B200 (4K / 1080p enc265 streams, generator I pictures; batches of 1..128; gpurun_out r2h-r2j): every size on
+// its own instantiation has the shortest chain per TB (a lone 4K picture 1.35 ms; all sizes on the segment code 1.88 ms: the
+// 4-pass loop of a 32x32 TB loses the instruction-level parallelism of the unrolled form, and the run-time size costs address
+// arithmetic on the chain); only the 16x16 block gains from the segment form - one pass with all 32 lanes busy and half the
+// chain per lane (1.28 ms alone, -3..5 % at every batch size).  The smaller code (35 KB instead of 61 KB) only paid off in
+// batches of >= 16 4K pictures, not on the 1080p stream.
+#ifndef INTRA_SEG_SIZES
+#define INTRA_SEG_SIZES 0x10
+#endif
 #define INTRA_WARPS 4   // one warp per SM sub-partition; several CTAs per SM when the batch is large
 #ifndef INTRA_MIN_CTAS
 #define INTRA_MIN_CTAS 4  // resident CTAs per SM the register budget is sized for
@@ -187,6 +198,94 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
   }
 }
 
+
+// Size-independent form (intra_seg.cuh): a lane's unit of work is one 8-sample segment of a line; a 32x32 block is four
+// passes of the warp, a 16x16 block one pass with all lanes busy.  One body for every size.
+template <bool TRACE>
+__device__ __forceinline__ void intra_tb_seg(const CtbEdges& E, const IntraGeom& g, int cidx, int x, int y, int log2, int mode, int flags,
+                                             bool coded, uint64_t M, uint8_t* wborder, long long (&acc)[4]) {
+  long long c0 = 0, c1 = 0, c2 = 0;
+  if (TRACE) c0 = clock64();
+  const int lane = lane_id();
+  const int N = 1 << log2;
+  const int lseg = log2 < 3 ? 0 : log2 - 3;        // segments per line = 1 << lseg (1, 1, 2, 4)
+  const int items = N << lseg;                     // 4, 8, 32, 128
+  const bool small = log2 == 2;                    // half segments: 4 samples per line
+  // the residual of the first pass is independent of the neighbours: issue its load first
+  int item = lane;
+  uint32_t r[4] = {0, 0, 0, 0};
+  auto load_resid = [&](int it, uint32_t (&rr)[4]) {
+    if (!coded || it >= items) return;
+    const int l = it >> lseg, sg = it & ((1 << lseg) - 1);
+    const int16_t* p = g.resid + (size_t)(y + l) * g.pitch + x + 8 * sg;
+    if (small) {
+      const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
+      rr[0] = v.x; rr[1] = v.y;
+    } else {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+      rr[0] = v.x; rr[1] = v.y; rr[2] = v.z; rr[3] = v.w;
+    }
+  };
+  load_resid(item, r);
+  const int xr = x - E.x0, yr = y - E.y0;
+  uint8_t* buf0 = wborder;
+  uint8_t* buf1 = buf0 + ibuf_stride(N);
+  if (log2 == 5) gather_border_rt<true>(E, N, xr, yr, M, lane, buf0);
+  else gather_border_rt<false>(E, N, xr, yr, M, lane, buf0);
+  if (TRACE) c1 = clock64();
+  uint8_t* pb = filter_border_rt(buf0, buf1, N, lane, mode, cidx, g.strong);
+  if (TRACE) c2 = clock64();
+  IntraPred P;
+  intra_pred_setup(P, pb, N, log2, lane, mode, cidx, !(flags & B265_TU_NO_EDGE_FILT));
+  uint8_t* d = g.plane + (size_t)y * g.pitch + x;
+  uint8_t* erow = E.rows + ((yr + N) >> 2) * E.rstride + 16 + xr;   // the TB's bottom row in the edge store
+  uint8_t* ecol = E.cols + ((xr + N) >> 2) * E.S + yr;              // its right column
+  const int last_seg = (1 << lseg) - 1;
+  for (; item < items; item += 32) {   // warp-uniform trip count is not needed: nothing inside synchronises
+    uint32_t r_next[4] = {0, 0, 0, 0};
+    load_resid(item + 32, r_next);
+    const int l = item >> lseg, sg = item & last_seg;
+    uint32_t h[4], px[2];
+    intra_pred_seg(P, l, sg, h);
+    finish_seg(h, r, coded, px);
+    const uint32_t last_word = small ? px[0] : px[1];
+    // The corner sample of a later TB lies on an edge row AND an edge column but only needs to be this TB's
+    // bottom row OR right column: the right column is therefore also entered into the edge rows it crosses.
+    if (!P.by_column) {   // line = row
+      uint8_t* o = d + (size_t)l * g.pitch + 8 * sg;
+      if (small) *reinterpret_cast<uint32_t*>(o) = px[0];
+      else *reinterpret_cast<uint2*>(o) = make_uint2(px[0], px[1]);
+      if (sg == last_seg) {
+        ecol[l] = (uint8_t)(last_word >> 24);
+        if ((l & 3) == 3) E.rows[((yr + l + 1) >> 2) * E.rstride + 16 + xr + N - 1] = (uint8_t)(last_word >> 24);
+      }
+      if (l == N - 1) {
+        reinterpret_cast<uint32_t*>(erow + 8 * sg)[0] = px[0];
+        if (!small) reinterpret_cast<uint32_t*>(erow + 8 * sg)[1] = px[1];
+      }
+    } else {              // line = column, segment = 8 rows
+      uint8_t* o = d + (size_t)(8 * sg) * g.pitch + l;
+#pragma unroll
+      for (int j = 0; j < 8; j++)
+        if (j < 4 || !small) o[(size_t)j * g.pitch] = (uint8_t)(px[j >> 2] >> (8 * (j & 3)));
+      if (sg == last_seg) erow[l] = (uint8_t)(last_word >> 24);
+      if (l == N - 1) {
+        reinterpret_cast<uint32_t*>(ecol + 8 * sg)[0] = px[0];
+        E.rows[((yr + 8 * sg + 4) >> 2) * E.rstride + 16 + xr + N - 1] = (uint8_t)(px[0] >> 24);
+        if (!small) {
+          reinterpret_cast<uint32_t*>(ecol + 8 * sg)[1] = px[1];
+          E.rows[((yr + 8 * sg + 8) >> 2) * E.rstride + 16 + xr + N - 1] = (uint8_t)(px[1] >> 24);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) r[i] = r_next[i];
+  }
+  __syncwarp();  // the next TB of this CTB reads the edge store
+  if (TRACE) {
+    acc[0] += c1 - c0; acc[1] += c2 - c1; acc[3] += clock64() - c2;
+  }
+}
 
 // ---- border exchange between CTB rows: flag-in-data mailboxes --------------------------------------------
 // A CTB's warp posts the CTB's bottom row and right column (the only samples later CTBs can read) as
@@ -419,7 +518,7 @@ __global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __rest
 // TRACE (developer aid, B265_INTRA_TRACE=<file>): per (plane, CTB) slot 12 x uint64 {t_start, t_setup, t_borders, t_tbs, t_end,
 // n_tbs, gather, filter, predict, add+store, globaltimer, (how << 32) | sm id}; how: 0 = first CTB after taking the row from the
 // queue, 1 = next CTB of the row with the edge store reused, 2 = next CTB with a full border fetch
-template <bool TRACE>
+template <bool TRACE, int SEGMAX>
 __global__ void __launch_bounds__(INTRA_WARPS * 32, INTRA_MIN_CTAS)
 k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsigned long long* queue, unsigned qmask, unsigned total_warps,
                   unsigned sleep_ns, unsigned yield_polls, int tile_bytes, unsigned long long* trace) {
@@ -557,11 +656,14 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
             const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
                                ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
             if (TRACE) n_tbs++;
-            switch ((r1 >> 2) & 7) {
-              case 2: intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-              case 3: intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-              case 4: intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
-              default: intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc); break;
+            // two forms of the same arithmetic, bit-identical; which sizes take which: INTRA_SEG_SIZES above
+            {
+              const int lg = (int)((r1 >> 2) & 7);   // SEGMAX is a mask of the log2 sizes that take the segment code
+              if ((SEGMAX >> lg) & 1) intra_tb_seg<TRACE>(E, g, c, x, y, lg, mode, flags, coded, M, s_border[warp], acc);
+              else if (!((SEGMAX >> 5) & 1) && lg == 5) intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
+              else if (!((SEGMAX >> 4) & 1) && lg == 4) intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
+              else if (!((SEGMAX >> 3) & 1) && lg == 3) intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
+              else if (!((SEGMAX >> 2) & 1)) intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
             }
           }
         }
@@ -604,9 +706,9 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb) {
   const size_t dyn = (size_t)INTRA_WARPS * tile_bytes_for(log2_ctb);
   // the opt-in limit is a property of the function, not of a launch: always allow the largest CTB size
   const size_t dyn_max = (size_t)INTRA_WARPS * tile_bytes_for(6);
-  cudaFuncSetAttribute(k_intra_wavefront<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
-  cudaFuncSetAttribute(k_intra_wavefront<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intra_wavefront<false>, INTRA_WARPS * 32, dyn);
+  cudaFuncSetAttribute(k_intra_wavefront<false, INTRA_SEG_SIZES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
+  cudaFuncSetAttribute(k_intra_wavefront<true, INTRA_SEG_SIZES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_intra_wavefront<false, INTRA_SEG_SIZES>, INTRA_WARPS * 32, dyn);
   if (per_sm < 1) per_sm = 1;
   return per_sm * sm_count;
 }
@@ -658,7 +760,7 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     }
     cudaMalloc((void**)&d, n_slots * 96);
     cudaMemsetAsync(d, 0, n_slots * 96, st);
-    k_intra_wavefront<true><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, qmask, total_warps,
+    k_intra_wavefront<true, INTRA_SEG_SIZES><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, qmask, total_warps,
                                                                                      (unsigned)sleep_ns, (unsigned)yield_polls, tb, d);
     cudaStreamSynchronize(st);
     unsigned long long* h = (unsigned long long*)malloc(n_slots * 96);
@@ -668,6 +770,6 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     cudaFree(d);
     return;
   }
-  k_intra_wavefront<false><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(frames, sched, queue, qmask, total_warps,
-                                                                                    (unsigned)sleep_ns, (unsigned)yield_polls, tb, nullptr);
+  k_intra_wavefront<false, INTRA_SEG_SIZES><<<ctas, INTRA_WARPS * 32, (size_t)INTRA_WARPS * tb, st>>>(
+      frames, sched, queue, qmask, total_warps, (unsigned)sleep_ns, (unsigned)yield_polls, tb, nullptr);
 }
