@@ -22,12 +22,13 @@ REF_DIR = os.path.join(ROOT, "oracle", "_ref")
 SWEEP = [("DST4", 1, 2), ("DCT4", 0, 2), ("DCT8", 0, 3), ("DCT16", 0, 4), ("DCT32", 0, 5)]
 STREAM_WL = {
     # name: (golden stream, deblocking patched on, loops of the stream per step, kernel batch, description)
-    "stream_4k": ("c4_2160p_q32", True, 32, 32, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
+    "stream_4k": ("c4_2160p_q32", True, 32, 128, "3840x2160 8-bit 4:2:0 enc265 intra stream (8 unique frames, qp 32), "
                   "deblocking enabled by PPS re-write (SAO cannot be enabled in an enc265 stream)"),
-    "stream_1080p": ("c1_1080p_q32", False, 16, 64, "1920x1080 8-bit 4:2:0 enc265 intra stream (16 unique frames, qp 32)"),
+    "stream_1080p": ("c1_1080p_q32", False, 16, 256, "1920x1080 8-bit 4:2:0 enc265 intra stream (16 unique frames, qp 32)"),
     # P/B streams at the metric's sizes.  The reference's encoder cannot produce inter pictures, so these come from
     # the random-syntax generator (tools/streamgen, golden MD5s from the unmodified reference decoder): merge / AMVP /
-    # temporal MVP, AMP, weighted prediction, SAO and deblocking on; kernel batch = the whole stream in decoding order
+    # temporal MVP, AMP, weighted prediction, SAO and deblocking on; kernel batch = B265_BENCH_STREAMS (8) independent instances of
+    # the whole stream in decoding order
     "stream_inter_1080p": ("gen_pb_1080p_ld32", False, 8, 0, "1920x1080 P/B generator stream, low-delay shape (32 pictures, 3 references, "
                            "weighted prediction, temporal MVP, AMP, SAO, deblocking)"),
     "stream_inter_1080p_ra": ("gen_pb_1080p_ra33", False, 8, 0, "1920x1080 P/B generator stream, random-access shape (33 pictures, output "
@@ -278,33 +279,47 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     threads = int(os.environ.get("B265_BENCH_THREADS", 0)) or max(1, cores // world - 1)   # override: developer sweeps
 
     # ---------------- kernels with work lists resident in HBM ----------------
-    ctx = L.Context(local)
+    # One context holds a batch of `kbatch` pictures (independent pictures of an intra stream, or `kcopies` independent
+    # instances of an inter stream whose dependency levels share launch groups); a step runs it.  B265_BENCH_CONTEXTS > 1
+    # (developer runs) puts one such batch on each of several contexts, the shape the C API's reconstruction threads have;
+    # the contexts then share the SMs (b265_busy_peers).
+    nctx = max(1, int(os.environ.get("B265_BENCH_CONTEXTS", 1)))
+    ctxs = [L.Context(local) for _ in range(nctx)]
+    ctx = ctxs[0]
     uniq = stream_jobs(data, threads=min(threads, 8))       # decoding order
     inter = any(oj.job.n_refs for oj in uniq)
-    if not kbatch:
-        kbatch = len(uniq)
-    jobs, sids = [], []
-    uid2sid = {}
-    for i in range(kbatch):
-        oj = uniq[i % len(uniq)]
-        J = L.FrameJob()
-        C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
-        sid = ctx.surface_alloc(W, H)
-        if inter:   # a parse-only decoder names pictures by unique id: map them to surfaces (the whole stream is one batch)
-            uid2sid[oj.job.dst_surface] = sid
-            for r in range(J.n_refs):
-                J.ref_surfaces[r] = uid2sid[oj.job.ref_surfaces[r]]
-        J.dst_surface = sid
-        sids.append(sid)
-        jobs.append(J)
-    batch = ctx.upload_frames(jobs)
-    ctx.sync()
+    kcopies = 1
+    if not kbatch:   # inter: the whole stream in decoding order, B265_BENCH_STREAMS independent instances of it in one batch
+        kcopies = max(1, int(os.environ.get("B265_BENCH_STREAMS", 8)))
+        kbatch = len(uniq) * kcopies
+
+    def resident_batch(cx):
+        jobs, sids = [], []
+        for copy in range(kcopies):   # inter streams: `kcopies` independent instances of the stream share the launch groups
+            uid2sid = {}
+            for i in range(kbatch // kcopies):
+                oj = uniq[i % len(uniq)]
+                J = L.FrameJob()
+                C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
+                sid = cx.surface_alloc(W, H)
+                if inter:   # a parse-only decoder names pictures by unique id: map them to this instance's surfaces
+                    uid2sid[oj.job.dst_surface] = sid
+                    for r in range(J.n_refs):
+                        J.ref_surfaces[r] = uid2sid[oj.job.ref_surfaces[r]]
+                J.dst_surface = sid
+                sids.append(sid)
+                jobs.append(J)
+        b = cx.upload_frames(jobs)
+        cx.sync()
+        return jobs, sids, b
+    resident = [resident_batch(cx) for cx in ctxs]
+    jobs, sids, batch = resident[0]
     ab = [_job_algorithmic_bytes(J) for J in jobs]
     bytes_res, bytes_intra, bytes_dbk, bytes_mc, bytes_sao = (sum(x[i] for x in ab) for i in range(5))
     for _ in range(a.warmup):
         ctx.run_batch(batch)
     ctx.sync()
-    # per-stage device time (CUDA events between the stages, on the context's stream)
+    # per-stage device time of one batch running alone (CUDA events between the stages, on the context's stream)
     ctx.lib.b265_set_stage_timing(ctx.h, 1)
     st = []
     for _ in range(3):
@@ -313,22 +328,40 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         st.append(ctx.stage_times())
     ctx.lib.b265_set_stage_timing(ctx.h, 0)
     stage = [float(np.mean([s[i] for s in st])) for i in range(6)]
-    launches0 = ctx.launches
+
+    def step():
+        for cx, (_, _, b) in zip(ctxs, resident):
+            cx.run_batch(b)
+    for _ in range(a.warmup):
+        step()
+    for cx in ctxs:
+        cx.sync()
+    launches0 = sum(cx.launches for cx in ctxs)
     clocks = ClockSampler(local)
     clocks.start()
     if world > 1:
         import torch, torch.distributed as dist
         dist.barrier(); torch.cuda.synchronize()
-    ctx.sync()
+    # device time of `steps` steps over all contexts: the start event on context 0's stream, every other stream waits for
+    # it; at the end context 0's stream waits for the others before the stop event
     ctx.timer_start()
+    for cx in ctxs[1:]:
+        cx.wait_for(ctx)
     for _ in range(a.steps):
-        ctx.run_batch(batch)
+        step()
+    for cx in ctxs[1:]:
+        ctx.wait_for(cx)
     ms_total = ctx.timer_stop()
     ms_total = _barrier_max(world, ms_total)
     clk = clocks.stop()
-    launches = ctx.launches - launches0
+    launches = sum(cx.launches for cx in ctxs) - launches0
     ms_step = ms_total / a.steps
-    value = world * kbatch / ms_step * 1e3
+    value = world * nctx * kbatch / ms_step * 1e3
+    for cx, (_, sd, b) in zip(ctxs[1:], resident[1:]):
+        cx.free_batch(b)
+        for s_ in sd:
+            cx.surface_release(s_)
+        cx.close()
     ctx.free_batch(batch)
     # ---- SAO leg: an enc265 stream cannot carry SAO syntax, so the deblocked pictures of
     # this stream are filtered with synthetic per-CTB parameters (seed 5: 20 % off / 40 % band / 40 % edge,
@@ -434,17 +467,22 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         "metric": "decoded frames/s", "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps,
         "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8 pixels / int16 coefficients / int32 accumulators", "data": "synthetic",
-        "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": kbatch,
+        "config": {"workload": "%s: %s" % (wl, desc), "frames_per_step": nctx * kbatch, "contexts": nctx, "frames_per_batch": kbatch,
                    "mpixel_per_s": value * W * H / 1e6,
                    "value_is": "all reconstruction kernels (MC, residual, intra wavefront, deblock V+H, SAO where the stream has it) on a batch "
-                               "of %d pictures whose work lists are resident in HBM; the CPU arm is the whole reference decoder "
-                               "(parsing included) and compares with `e2e`, not with `value`" % kbatch,
+                               "of %d pictures%s whose work lists are resident in HBM%s; the CPU arm is the whole reference decoder "
+                               "(parsing included) and compares with `e2e`, not with `value`"
+                               % (kbatch, " (%d independent instances of the stream: dependent pictures run in launch groups by dependency "
+                                          "level)" % kcopies if kcopies > 1 else "",
+                                  "; %d contexts (one CUDA stream each) hold one such batch each, device time from a start event every "
+                                  "stream waits for to a stop event that waits for every stream" % nctx if nctx > 1 else ""),
                    "l2": "working set per step %d MB of pictures + work lists > 126 MB L2; L2 flushed before the per-stage timings"
-                         % (kbatch * W * H * 3 // 2 >> 20),
+                         % (nctx * kbatch * W * H * 3 // 2 >> 20),
                    "e2e_is": "libde265 C API (de265_push_data/de265_decode/de265_get_next_picture): %d host parse threads, "
                              "%s CUDA contexts, batch %d; %d frames per step" % (threads, os.environ.get("B265_RECON_CONTEXTS", "3"), dbatch, frames_step),
                    "host_cores": cores, "host_cores_per_rank": cores // world,
                    "stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]": [round(x, 3) for x in stage],
+                   "stage_ms_is": "one batch running alone on one context (stages of concurrent batches overlap, so they do not add up to ms_per_step)",
                    "sao_leg_ms": round(sao_ms, 3) if sao_ms else None},
         "e2e": {"value": e2e_fps, "unit": "frames/s",
                 "h2d_bytes_per_step": int((s1["h2d_bytes"] - s0["h2d_bytes"]) / a.steps),
@@ -463,7 +501,7 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
         "roofline": {"bound": "hbm", "kernel": dom[0], "achieved": dom[2] or 0.0, "peak": peak, "unit": "GB/s",
                      "frac": (dom[2] or 0.0) / peak, "traffic": traffic, "peak_source": peak_src,
                      "share_of_step": dom[1] / stage[5] if stage[5] else None,
-                     "note": "largest share of the step; " + dom[3] + "; time = CUDA events around this stage only",
+                     "note": "largest share of a batch; " + dom[3] + "; time = CUDA events around this stage only, the batch running alone",
                      "per_kernel_gbs": {"k_mc": round(mc_gbs, 1) if mc_gbs else None,
                                         "k_residual_sparse x4 + k_intra_prep (4 B/coeff read, 2 B/coded sample written)": round(res_gbs, 1) if res_gbs else None,
                                         "k_intra_wavefront": round(intra_gbs, 1) if intra_gbs else None,
@@ -731,22 +769,37 @@ def run_mc(a, rank, world, local, ClockSampler, measured_peaks):
     launches = ctx.launches - launches0
     ms_step = _barrier_max(world, float(np.mean(ms)))
     ctx.free_batch(batch)
-    # end to end through b265_mc_batch with HOST buffers: reference planes, PU and slice lists up, prediction planes down
-    dst = [np.zeros((H, W), np.uint8), np.zeros((H // 2, W // 2), np.uint8), np.zeros((H // 2, W // 2), np.uint8)]
-    ctx.mc_batch(keep[0], keep[1], refs, dst, W, H)   # untimed: staging buffers
+    # end to end through b265_mc_batch with HOST buffers in pinned memory (b265_host_alloc): reference planes, PU and slice
+    # lists up, prediction planes down, all inside the timed region
+    pins = []
+
+    def pinned(arr):
+        p = C.c_void_p()
+        if ctx.lib.b265_host_alloc(ctx.h, arr.nbytes, C.byref(p)) != 0:
+            return arr.copy()
+        pins.append(p)
+        view = np.frombuffer((C.c_uint8 * arr.nbytes).from_address(p.value), dtype=arr.dtype).reshape(arr.shape)
+        view[...] = arr
+        return view
+    prefs = [[pinned(pl) for pl in r] for r in refs]
+    dst = [pinned(np.zeros((H, W), np.uint8)), pinned(np.zeros((H // 2, W // 2), np.uint8)), pinned(np.zeros((H // 2, W // 2), np.uint8))]
+    ctx.mc_batch(keep[0], keep[1], prefs, dst, W, H)   # untimed: staging buffers
     t0 = time.perf_counter()
     for i in range(layers):
-        ctx.mc_batch(keep[2 * i], keep[2 * i + 1], refs, dst, W, H)
+        ctx.mc_batch(keep[2 * i], keep[2 * i + 1], prefs, dst, W, H)
     e2e_s = _barrier_max(world, time.perf_counter() - t0)
-    e2e = {"value": world * layers * W * H / e2e_s / 1e6, "unit": "Mpixel/s",
+    e2e = {"value": world * layers * W * H / e2e_s / 1e6, "unit": "Mpixel/s", "host_memory": "pinned" if pins else "pageable",
            "h2d_bytes_per_step": int(layers * len(refs) * W * H * 3 // 2 + 24 * n_pus), "d2h_bytes_per_step": int(layers * W * H * 3 // 2)}
+    for p_ in pins:
+        ctx.lib.b265_host_free(ctx.h, p_)
+    cb = cpu_baseline_mc(keep, refs, W, H) if rank == 0 and world == 1 else None
     for s_ in sids + ref_sids:
         ctx.surface_release(s_)
     ctx.close()
     peak, peak_src = measured_peaks()
     gbs = alg / ms_step / 1e6
     px = layers * W * H
-    return {"metric": "motion-compensated Mpixel/s", "value": world * px / ms_step / 1e3, "unit": "Mpixel/s", "n_gpus": world,
+    res = {"metric": "motion-compensated Mpixel/s", "value": world * px / ms_step / 1e3, "unit": "Mpixel/s", "n_gpus": world,
             "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8 pixels / int16 intermediates / int32 accumulators", "data": "synthetic",
             "config": {"workload": "mc_pus: SURVEY 8d config 3, 1920x1080, 3 references, %d PUs in %d pictures" % (n_pus, layers),
@@ -755,6 +808,31 @@ def run_mc(a, rank, world, local, ClockSampler, measured_peaks):
             "roofline": {"bound": "hbm", "kernel": "k_mc", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak,
                          "traffic": None, "peak_source": peak_src,
                          "note": "algorithmic bytes = 3*w*h per uni-predicted PU (1.5 read + 1.5 written), 4.5*w*h per bi-predicted PU"}}
+    if cb is not None:
+        res["cpu_baseline"] = cb
+    return res
+
+
+def cpu_baseline_mc(keep, refs, W, H, budget_s=6.0):
+    """The C oracle's orc_mc_batch (oracle/mc.c: the arithmetic of fallback-motion.cc:33-625 and motion.cc:48-282, pinned
+    against the compiled reference's put_qpel / put_epel / writer slots in tests/test_oracle_mc.py) on the same PU lists,
+    one picture per pass, one thread.  The reference has no entry point that predicts a PU list without a decoder context,
+    hence kind "port"."""
+    from tests import helpers
+    orc = helpers.load_oracle()
+    dst = [np.zeros((H, W), np.uint8), np.zeros((H // 2, W // 2), np.uint8), np.zeros((H // 2, W // 2), np.uint8)]
+    rp = (C.c_void_p * (3 * len(refs)))(*[pl.ctypes.data for r in refs for pl in r])
+    dp = (C.c_void_p * 3)(*[d.ctypes.data for d in dst])
+    n, t0 = 0, time.perf_counter()
+    while True:
+        pus, slices = keep[2 * (n % (len(keep) // 2))], keep[2 * (n % (len(keep) // 2)) + 1]
+        orc.orc_mc_batch(C.byref(pus), len(pus), C.byref(slices), rp, len(refs), dp, W, H, W, W // 2)
+        n += 1
+        if time.perf_counter() - t0 > budget_s or n >= 64:
+            break
+    t = time.perf_counter() - t0
+    return {"value": n * W * H / t / 1e6, "unit": "Mpixel/s", "cores": 1, "kind": "port",
+            "sample": "%d pictures (1920x1080 PU lists of the same workload) through the C oracle's orc_mc_batch, 1 thread" % n}
 
 
 DEFAULT_WORKLOAD = "stream_4k"

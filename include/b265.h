@@ -59,6 +59,11 @@ B265_API const char* b265_last_error(const b265_ctx* ctx);
 B265_API int  b265_create(int device, b265_ctx** out);
 B265_API void b265_destroy(b265_ctx* ctx);
 B265_API int  b265_sync(b265_ctx* ctx);
+/* Work submitted to `ctx` after this call starts only when everything submitted to `other` so far has finished (an event
+ * between the two contexts' CUDA streams, no host wait).  Both contexts on the same device.  No reference counterpart:
+ * the reference's thread pool orders its tasks on the host (threads.cc:150-260).  Contexts of one process that have
+ * batches on the device at the same time share the SMs: the intra wavefront sizes its grid by the number of busy peers. */
+B265_API int  b265_stream_wait(b265_ctx* ctx, b265_ctx* other);
 /* number of kernels launched by this context since creation (bench.py's gpu_launches claim) */
 B265_API uint64_t b265_launch_count(const b265_ctx* ctx);
 
@@ -261,10 +266,11 @@ typedef struct {
 B265_API int  b265_host_alloc(b265_ctx* ctx, size_t bytes, void** out);
 B265_API void b265_host_free(b265_ctx* ctx, void* p);
 
-/* Reconstruct n_jobs pictures. Pictures in one call must not reference each other (all-intra
- * streams batch freely; inter pictures are submitted in decoding order, one call per dependency
- * level). Work is enqueued on the context stream: MC -> inter residual -> intra wavefront (+residual)
- * -> deblock V -> deblock H -> SAO. Returns when everything is enqueued; the job arrays may be
+/* Reconstruct n_jobs (<= 4096) pictures, given in decoding order.  A picture may reference pictures of the same
+ * call: the call is cut into launch groups by dependency level (pictures that reference nothing of this call
+ * share the first group, and so on; at most 255 pictures per group), each group runs MC -> inter residual ->
+ * intra wavefront (+residual) -> deblock V -> deblock H -> SAO on the context stream, groups one after the other.
+ * Destination surfaces of one call are distinct.  Returns when everything is enqueued; the job arrays may be
  * reused after b265_sync() or after a later download with sync. */
 B265_API int b265_submit_frames(b265_ctx* ctx, const b265_frame_job* jobs, int n_jobs);
 

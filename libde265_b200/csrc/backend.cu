@@ -5,6 +5,10 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
+#include <chrono>
+#include <mutex>
+#include <vector>
 #include "kernels.h"
 
 extern "C" {
@@ -47,6 +51,28 @@ int devbuf_reserve(b265_ctx* ctx, DevBuf* b, size_t bytes, bool host) {
   return B265_OK;
 }
 
+// every live context of the process (b265_busy_peers)
+static std::mutex g_ctx_mu;
+static std::vector<b265_ctx*> g_ctxs;
+
+int64_t b265_now_ns() {
+  return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// A peer counts when its last batch is still on the device, or was handed over within the last 20 ms: contexts that take
+// turns (the decoder's reconstruction threads, a server's streams) keep their shares while one of them is between batches.
+int b265_busy_peers(b265_ctx* ctx) {
+  std::lock_guard<std::mutex> lk(g_ctx_mu);
+  const int64_t now = b265_now_ns();
+  int n = 0;
+  for (b265_ctx* c : g_ctxs) {
+    if (c == ctx || c->device != ctx->device || !c->busy_recorded.load(std::memory_order_acquire)) continue;
+    if (now - c->last_batch_ns.load(std::memory_order_relaxed) < 20000000 || cudaEventQuery(c->ev_busy) == cudaErrorNotReady) n++;
+  }
+  cudaGetLastError();   // cudaErrorNotReady is not sticky, but leave no trace for the next CK_LAUNCH
+  return n;
+}
+
 extern "C" {
 
 const char* b265_last_error(const b265_ctx* ctx) { return ctx ? ctx->last_error.c_str() : ""; }
@@ -72,7 +98,13 @@ int b265_create(int device, b265_ctx** out) {
   cudaEventCreate(&ctx->ev0);
   cudaEventCreate(&ctx->ev1);
   cudaEventCreateWithFlags(&ctx->ev_sync, cudaEventBlockingSync | cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&ctx->ev_busy, cudaEventDisableTiming);
+  cudaEventCreateWithFlags(&ctx->ev_wait, cudaEventDisableTiming);
   for (auto& e : ctx->stage_ev) cudaEventCreate(&e);
+  {
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    g_ctxs.push_back(ctx);
+  }
   *out = ctx;
   return B265_OK;
 }
@@ -81,6 +113,10 @@ void b265_free_batch(b265_ctx* ctx, b265_batch* batch);
 
 void b265_destroy(b265_ctx* ctx) {
   if (!ctx) return;
+  {
+    std::lock_guard<std::mutex> lk(g_ctx_mu);
+    g_ctxs.erase(std::remove(g_ctxs.begin(), g_ctxs.end(), ctx), g_ctxs.end());
+  }
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   if (ctx->submit_batch) b265_free_batch(ctx, ctx->submit_batch);
@@ -95,6 +131,8 @@ void b265_destroy(b265_ctx* ctx) {
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   if (ctx->ev_sync) cudaEventDestroy(ctx->ev_sync);
+  if (ctx->ev_busy) cudaEventDestroy(ctx->ev_busy);
+  if (ctx->ev_wait) cudaEventDestroy(ctx->ev_wait);
   for (auto& e : ctx->stage_ev) cudaEventDestroy(e);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -110,6 +148,15 @@ int b265_sync(b265_ctx* ctx) {
   } else {
     CK(cudaStreamSynchronize(ctx->stream));
   }
+  return B265_OK;
+}
+
+int b265_stream_wait(b265_ctx* ctx, b265_ctx* other) {
+  if (!ctx || !other || ctx == other) return B265_ERR_INVALID_ARG;
+  if (ctx->device != other->device) return b265_fail(ctx, B265_ERR_INVALID_ARG, "b265_stream_wait: contexts on different devices", cudaSuccess);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaEventRecord(ctx->ev_wait, other->stream));   // the waiter's event: calls on one context are serialised by its owner anyway
+  CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_wait, 0));
   return B265_OK;
 }
 

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <atomic>
 #include <string>
 #include <vector>
 #include "../../include/b265.h"
@@ -29,6 +30,10 @@ struct b265_ctx {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   cudaEvent_t ev_sync = nullptr;   // blocking-sync event: b265_sync() sleeps instead of spinning on a host core
+  cudaEvent_t ev_busy = nullptr;   // recorded after the last kernel of every batch: not ready = this context has work on the device
+  std::atomic<bool> busy_recorded{false};
+  std::atomic<int64_t> last_batch_ns{0};   // steady-clock time of the last b265_run_batch / b265_submit_frames
+  cudaEvent_t ev_wait = nullptr;   // b265_stream_wait
   cudaEvent_t stage_ev[8] = {};
   bool stage_timing = false;
   float stage_ms[6] = {0, 0, 0, 0, 0, 0};
@@ -57,6 +62,10 @@ int b265_fail(b265_ctx* ctx, int status, const char* what, cudaError_t e);
   } while (0)
 
 int devbuf_reserve(b265_ctx* ctx, DevBuf* b, size_t bytes, bool host);
+// Contexts of this process on ctx's device, other than ctx, whose last batch has not finished (backend.cu).  The intra
+// wavefront sizes its persistent grid by it: concurrent batches share the SMs instead of queueing behind a full grid.
+int b265_busy_peers(b265_ctx* ctx);
+int64_t b265_now_ns();
 
 // Prediction blocks larger than 16x16 are cut into 16x16 pieces when the lists are staged for the device: motion
 // compensation and the motion raster are per-sample functions of (position, motion), so the pieces give the same

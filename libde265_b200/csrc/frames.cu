@@ -80,7 +80,7 @@ static const bool g_build_timing = getenv("B265_BUILD_TIMING") != nullptr;   // 
 
 static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs_in, int n_jobs, b265_batch* b) {
   const double tb0 = t_now();
-  if (n_jobs > 255) return reject(__LINE__, B265_ERR_INVALID_ARG);
+  if (n_jobs > 4096) return reject(__LINE__, B265_ERR_INVALID_ARG);
   // Pictures are reordered by DEPENDENCY LEVEL inside the batch (level = 1 + the highest level among the pictures of this
   // batch it references; stable otherwise): all pictures of a level form one launch group, so the I pictures of a batch -
   // and every picture whose references were finished by earlier submits - share their launches instead of paying the
@@ -126,8 +126,9 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs_in, int n_jobs,
     if (J.bit_depth != 8 || J.chroma_format_idc > 1 || J.n_tus >= (1 << 24) || J.n_pus >= (1 << 24))
       return reject(__LINE__, B265_ERR_UNSUPPORTED);
     if (J.n_refs < 0 || J.n_refs > 16) return reject(__LINE__, B265_ERR_INVALID_ARG);
-    {  // a picture that reads a picture of the current group starts the next group
-      bool dependent = false;
+    {  // a picture that reads a picture of the current group starts the next group; so does the 256th picture of a group
+      // (list items name their picture in 8 bits, relative to the group)
+      bool dependent = !groups.empty() && j - groups.back().first >= 255;
       if (!groups.empty())
         for (int r = 0; r < J.n_refs && !dependent; r++)
           for (int i = groups.back().first; i < j; i++)
@@ -428,6 +429,7 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
   const bool tm = ctx->stage_timing;
   if (tm) for (int i = 0; i < 6; i++) ctx->stage_ms[i] = 0;
   if (b->zero_bytes) CK(cudaMemsetAsync(b->d_zero_begin, 0, b->zero_bytes, st));
+  const int busy_peers = b265_busy_peers(ctx);   // other contexts with a batch on the device right now
   for (size_t gi = 0; gi < b->groups.size(); gi++) {
     const LaunchGroup& g = b->groups[gi];
     const FrameDev* frames = b->d_frames + g.first;
@@ -472,7 +474,7 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
     if (tm) cudaEventRecord(ctx->stage_ev[2], st);   // stage 1 = all residual launches + availability masks
     if (g.n_tickets) {
       launch_intra(st, frames, g.n, g.max_slots, g.max_rows, g.n_runs, b->d_sched, b->d_queue, b->queue_entries,
-                   ctx->sm_count, g.log2_ctb);
+                   ctx->sm_count, g.log2_ctb, busy_peers);
       ctx->launches += 2;
       CK_LAUNCH("k_intra_sched_prep + k_intra_wavefront");
     }
@@ -488,6 +490,9 @@ static int run_batch(b265_ctx* ctx, b265_batch* b) {
       ctx->stage_ms[5] += ms;
     }
   }
+  CK(cudaEventRecord(ctx->ev_busy, st));
+  ctx->last_batch_ns.store(b265_now_ns(), std::memory_order_relaxed);
+  ctx->busy_recorded.store(true, std::memory_order_release);
   return B265_OK;
 }
 

@@ -3,11 +3,15 @@
 #include <stdio.h>
 #include "slice_syntax.h"
 
+#ifdef B265_PROF
+unsigned long long g_prof[16];   // developer aid (-DB265_PROF): TSC ticks per parser section, single-threaded runs only
+extern "C" __attribute__((visibility("default"))) void b265_prof_get(unsigned long long* out) {
+  for (int i = 0; i < 16; i++) out[i] = g_prof[i];
+}
+#endif
+
 namespace b265h {
 
-#ifdef B265_PROF
-unsigned long long g_prof[16];
-#endif
 
 int decode_picture_slices(Picture& pic) {
   PROF(5);

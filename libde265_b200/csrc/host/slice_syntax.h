@@ -30,7 +30,9 @@ struct ProfScope { int i; unsigned long long t; ProfScope(int k) : i(k), t(__rdt
 #define PROF(k) ProfScope prof_scope_##k(k)
 #define PROF_T(v) unsigned long long v = __rdtsc()
 #define PROF_ADD(k, a, b) g_prof[k] += (b) - (a)
+#define PROF_CNT(k, v) g_prof[k] += (v)
 #else
+#define PROF_CNT(k, v)
 #define PROF(k)
 #define PROF_T(v)
 #define PROF_ADD(k, a, b)
@@ -1014,6 +1016,7 @@ int SliceDec<Eng>::transform_unit(int x0, int y0, int xBase, int yBase, int xCU,
 template <class Eng>
 int SliceDec<Eng>::residual_coding(int x0, int y0, int log2_ts, int cidx, int intra_mode, b265_tu& tu) {
   PROF(1);
+  PROF_CNT(9, 1);
   typename Eng::Local cb(cabac);
   Ctx* const cx = ctx;
   const int n = 1 << log2_ts;
@@ -1088,6 +1091,8 @@ int SliceDec<Eng>::residual_coding(int x0, int y0, int log2_ts, int cidx, int in
       else if (cb.bin(cx[tab[0]])) sig[nsig++] = 0;
     }
     if (!nsig) continue;
+    PROF_CNT(10, 1);
+    PROF_CNT(11, nsig);
     PROF_T(p1);
     PROF_ADD(6, p0, p1);
     // greater1 / greater2 flags
@@ -1121,6 +1126,7 @@ int SliceDec<Eng>::residual_coding(int x0, int y0, int log2_ts, int cidx, int in
       const int thr = k < 8 ? (k == first_g1 ? 3 : 2) : 1;
       int a = base;
       if (base == thr) {
+        PROF_CNT(12, 1);
         cb.hint(HINT_COEFF_REMAINING, rice);
         int prefix = 0;
         while (prefix < 32 && cb.bypass()) prefix++;

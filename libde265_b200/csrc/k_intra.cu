@@ -717,7 +717,7 @@ int intra_max_resident_ctas(int sm_count, int log2_ctb) {
 int intra_queue_slack(int sm_count) { return intra_max_resident_ctas(sm_count, 4) * INTRA_WARPS + 64; }
 
 void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_runs, IntraSched* sched,
-                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb) {
+                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb, int busy_peers) {
   if (n_runs <= 0) return;
   static int max_ctas[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (!max_ctas[log2_ctb & 7]) max_ctas[log2_ctb & 7] = intra_max_resident_ctas(sm_count, log2_ctb);
@@ -727,8 +727,11 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
     if (gx > 4 * sm_count) gx = 4 * sm_count;
     k_intra_sched_prep<<<dim3(gx, n_frames), 256, 0, st>>>(frames, sched, queue, qmask, max_rows);
   }
-  // Sleeping warps cost next to nothing, but a grid that fills every CTA slot keeps a second batch (another stream of the
-  // same process) off the SMs until it drains: B265_INTRA_CTAS_PER_SM caps the share of one launch.
+  // Sleeping warps cost next to nothing, but a grid that fills every CTA slot keeps a second batch (another context of the
+  // same process) off the SMs until it drains.  Batches that run side by side fill each other's ramps and tails and let
+  // the residual / deblocking / SAO stages of one use the issue slots the latency-bound wavefront of the other leaves idle
+  // (4K, batches of 32: 3.83 ms per batch alone, 2.78 ms with four contexts at one CTA per SM each), so a launch takes
+  // INTRA_MIN_CTAS / (1 + busy peer contexts) CTAs per SM.  B265_INTRA_CTAS_PER_SM overrides.
   static int cap_per_sm = -1, sleep_ns = -1, yield_polls = -1;
   if (cap_per_sm < 0) {
     const char* e = getenv("B265_INTRA_CTAS_PER_SM");
@@ -745,7 +748,8 @@ void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max
   // one warp per run is all a launch can use
   int ctas = (n_runs + INTRA_WARPS - 1) / INTRA_WARPS;
   if (ctas > max_ctas[log2_ctb & 7]) ctas = max_ctas[log2_ctb & 7];
-  if (cap_per_sm > 0 && ctas > cap_per_sm * sm_count) ctas = cap_per_sm * sm_count;
+  const int share = cap_per_sm > 0 ? cap_per_sm : std::max(1, INTRA_MIN_CTAS / (1 + std::max(0, busy_peers)));
+  if (ctas > share * sm_count) ctas = share * sm_count;
   const unsigned total_warps = (unsigned)ctas * INTRA_WARPS;
   const int tb = tile_bytes_for(log2_ctb);
   static const char* trace_path = getenv("B265_INTRA_TRACE");

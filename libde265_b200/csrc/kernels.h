@@ -30,9 +30,9 @@ void launch_intra_prep(cudaStream_t st, const FrameDev* frames, int n_frames, in
 int intra_max_resident_ctas(int sm_count, int log2_ctb);
 // neighbour masks + run queue (grid over the (plane, CTB) slots of every frame), then the wavefront itself; after
 // launch_intra_prep on the same frames.  `queue` has `queue_entries` (a power of two >= n_runs + intra_queue_slack())
-// 8-byte entries and is zero
+// 8-byte entries and is zero; busy_peers = other contexts with work on the device (the grid takes its share of the SMs)
 void launch_intra(cudaStream_t st, const FrameDev* frames, int n_frames, int max_slots, int max_rows, int n_runs, IntraSched* sched,
-                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb);
+                  unsigned long long* queue, unsigned queue_entries, int sm_count, int log2_ctb, int busy_peers);
 int intra_queue_slack(int sm_count);
 // decoded picture hash of n pictures (k_hash.cu): type 0 MD5, 1 CRC, 2 checksum (sei.h sei_decoded_picture_hash_type);
 // out = n * 3 slots of 16 bytes (MD5 digest / CRC or checksum in the first word); returns the number of launches

@@ -126,6 +126,7 @@ def load():
     lib.b265_destroy.argtypes = [vp]
     lib.b265_destroy.restype = None
     lib.b265_sync.argtypes = [vp]
+    lib.b265_stream_wait.argtypes = [vp, vp]
     lib.b265_launch_count.argtypes = [vp]
     lib.b265_launch_count.restype = C.c_uint64
     lib.b265_host_alloc.argtypes = [vp, C.c_size_t, C.POINTER(vp)]
@@ -203,6 +204,10 @@ class Context:
 
     def sync(self):
         check(self.h, self.lib.b265_sync(self.h), "sync")
+
+    def wait_for(self, other):
+        """work submitted to this context from now on starts after everything submitted to `other` so far (device side)"""
+        check(self.h, self.lib.b265_stream_wait(self.h, other.h), "stream_wait")
 
     @property
     def launches(self):

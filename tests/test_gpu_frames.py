@@ -66,3 +66,49 @@ def test_batch_of_frames(ctx):
             assert np.array_equal(got[c], want[c]), (i, c)
     for s in sids:
         ctx.surface_release(s)
+
+
+@pytest.mark.parametrize("name", ["c1_1080p_q32_lf", "gen_pb_1080p_ld32"])
+def test_concurrent_contexts_share_the_device(name):
+    """Four contexts each run a batch of the same stream at the same time, several rounds without a host sync: the intra
+    wavefront of each takes a share of the SMs by the number of busy peers (frames.cu, b265_busy_peers), every picture of
+    every context still has the reference decoder's MD5.  b265_stream_wait chains the contexts' streams on the device."""
+    import ctypes as C, hashlib
+    from libde265_b200 import lib as L
+    from benchmarks.jobs import stream_jobs
+    from tests.test_parser_streams import load_stream
+    data, gold = load_stream(name)
+    W, H = gold["width"], gold["height"]
+    uniq = stream_jobs(data, threads=4)
+    ctxs = [L.Context(0) for _ in range(4)]
+    held = []
+    for cx in ctxs:
+        jobs, sids, uid2sid = [], [], {}
+        for oj in uniq:
+            J = L.FrameJob()
+            C.memmove(C.byref(J), C.byref(oj.job), C.sizeof(L.FrameJob))
+            sid = cx.surface_alloc(W, H)
+            uid2sid[oj.job.dst_surface] = sid
+            for r in range(J.n_refs):
+                J.ref_surfaces[r] = uid2sid[oj.job.ref_surfaces[r]]
+            J.dst_surface = sid
+            sids.append(sid)
+            jobs.append(J)
+        held.append((jobs, sids, cx.upload_frames(jobs)))
+    for cx in ctxs[1:]:
+        cx.wait_for(ctxs[0])
+    for _ in range(3):
+        for cx, (_, _, b) in zip(ctxs, held):
+            cx.run_batch(b)
+    for cx in ctxs[1:]:
+        ctxs[0].wait_for(cx)
+    ctxs[0].sync()          # the chain: context 0's stream has waited for every other stream
+    assert len(uniq) == gold["frames"]      # both streams are in output order = decoding order
+    for k, (cx, (_, sids, b)) in enumerate(zip(ctxs, held)):
+        for i in range(len(uniq)):
+            planes = cx.surface_download(sids[i], W, H)
+            got = [hashlib.md5(p.tobytes()).hexdigest() for p in planes]
+            assert got == gold["md5"][i], "context %d, picture %d of %s differs from the reference decoder" % (k, i, name)
+        cx.free_batch(b)
+    for cx in ctxs:
+        cx.close()
