@@ -10,7 +10,7 @@ extern "C" int b265_mc_batch(b265_ctx* ctx, int mem, const b265_pu* pus, int n_p
       n_slices < 1 || width <= 0 || height <= 0)
     return B265_ERR_INVALID_ARG;
   if (n_pus == 0) return B265_OK;
-  std::vector<b265_pu> pieces;   // 16x16 pieces (pu_expand)
+  std::vector<b265_pu> pieces;   // <= 16 x 8 pieces (pu_expand)
   pieces.reserve((size_t)n_pus * 2);
   for (int i = 0; i < n_pus; i++) {
     const size_t at = pieces.size();

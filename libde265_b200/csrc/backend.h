@@ -67,17 +67,22 @@ int devbuf_reserve(b265_ctx* ctx, DevBuf* b, size_t bytes, bool host);
 int b265_busy_peers(b265_ctx* ctx);
 int64_t b265_now_ns();
 
-// Prediction blocks larger than 16x16 are cut into 16x16 pieces when the lists are staged for the device: motion
-// compensation and the motion raster are per-sample functions of (position, motion), so the pieces give the same
-// result, and every work item of the MC kernel then costs one tile (balanced scheduling).
-static inline int pu_pieces(const b265_pu& pu) { return ((pu.w + 15) >> 4) * ((pu.h + 15) >> 4); }
+// Prediction blocks larger than 16 x 8 are cut into pieces of at most 16 x 8 when the lists are staged for the device:
+// motion compensation and the motion raster are per-sample functions of (position, motion), so the pieces give the same
+// result, every work item of the MC kernel costs at most one half-warp pass (k_mc.cu), and the scheduling is balanced.
+#define B265_MC_PIECE_W 16
+#define B265_MC_PIECE_H 8
+static inline int pu_pieces(const b265_pu& pu) {
+  return ((pu.w + B265_MC_PIECE_W - 1) / B265_MC_PIECE_W) * ((pu.h + B265_MC_PIECE_H - 1) / B265_MC_PIECE_H);
+}
 static inline int pu_expand(const b265_pu& pu, b265_pu* out) {
   int n = 0;
-  for (int y = 0; y < pu.h; y += 16)
-    for (int x = 0; x < pu.w; x += 16) {
+  for (int y = 0; y < pu.h; y += B265_MC_PIECE_H)
+    for (int x = 0; x < pu.w; x += B265_MC_PIECE_W) {
       b265_pu q = pu;
       q.x = (uint16_t)(pu.x + x); q.y = (uint16_t)(pu.y + y);
-      q.w = (uint8_t)(pu.w - x < 16 ? pu.w - x : 16); q.h = (uint8_t)(pu.h - y < 16 ? pu.h - y : 16);
+      q.w = (uint8_t)(pu.w - x < B265_MC_PIECE_W ? pu.w - x : B265_MC_PIECE_W);
+      q.h = (uint8_t)(pu.h - y < B265_MC_PIECE_H ? pu.h - y : B265_MC_PIECE_H);
       out[n++] = q;
     }
   return n;

@@ -192,7 +192,7 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs_in, int n_jobs,
           if (ctb_area[(size_t)c * nctb + ctb] != full) recs[ctb].mixed |= (uint8_t)(1 << c);
         }
     }
-    {  // one MC item per 16x16 piece of a prediction block (pu_expand)
+    {  // one MC item per <= 16 x 8 piece of a prediction block (pu_expand)
       uint32_t n = 0;
       const int n_sl = std::max(1, J.n_slices);
       for (int i = 0; i < J.n_pus; i++) {

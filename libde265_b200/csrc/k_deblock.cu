@@ -23,8 +23,9 @@ __constant__ uint8_t c_qpc[13] = {29, 30, 31, 32, 33, 33, 34, 34, 35, 35, 36, 36
 
 // ---- PU list -> per-unit motion map (image.h pb_info equivalent, device resident) ----
 // entry: x = predFlags | slot0 << 8 | slot1 << 16, y = mv0 (x | y << 16), z = mv1
+// eight lanes per piece (a piece is at most 16 x 8 samples = 4 x 2 units, backend.h pu_expand)
 __global__ void k_motion_raster(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ items, int n) {
-  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 3;
   if (w >= n) return;
   const uint32_t o = items[w];
   const FrameDev& f = frames[o >> 24];
@@ -36,7 +37,7 @@ __global__ void k_motion_raster(const FrameDev* __restrict__ frames, const uint3
   e.y = (uint16_t)pu.mv[0][0] | ((uint32_t)(uint16_t)pu.mv[0][1] << 16);
   e.z = (uint16_t)pu.mv[1][0] | ((uint32_t)(uint16_t)pu.mv[1][1] << 16);
   e.w = 0;
-  for (int i = lane_id(); i < uw * uh; i += 32)
+  for (int i = threadIdx.x & 7; i < uw * uh; i += 8)
     reinterpret_cast<uint4*>(f.motion)[((pu.y >> 2) + i / uw) * pitch + (pu.x >> 2) + i % uw] = e;
 }
 
@@ -252,7 +253,7 @@ __global__ void k_deblock_chroma(const FrameDev* __restrict__ frames) {
 void launch_deblock(cudaStream_t st, const FrameDev* d_frames, int n_frames, int max_w, int max_h,
                     const uint32_t* mc_items, int n_mc, bool chroma) {
   const int uw = max_w >> 2, uh = max_h >> 2;
-  if (n_mc > 0) k_motion_raster<<<(n_mc * 32 + 255) / 256, 256, 0, st>>>(d_frames, mc_items, n_mc);
+  if (n_mc > 0) k_motion_raster<<<(n_mc * 8 + 255) / 256, 256, 0, st>>>(d_frames, mc_items, n_mc);
   const int per_cta = DBK_WARPS * DBK_ROUNDS * 32;   // candidate segments per block
   dim3 gv((((uw + 1) >> 1) * uh + per_cta - 1) / per_cta, n_frames), gh((uw * ((uh + 1) >> 1) + per_cta - 1) / per_cta, n_frames);
   dim3 cv((((uw + 3) >> 2) * ((uh + 1) >> 1) + 127) / 128, n_frames), chh((((uw + 1) >> 1) * ((uh + 3) >> 2) + 127) / 128, n_frames);
