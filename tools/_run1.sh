@@ -1,18 +1,7 @@
 mkdir -p gpurun_out
-python -c "from libde265_b200 import build as b; b.build()" 2>&1 | tail -2
-for w in mc_pus stream_inter_1080p; do
-  timeout 600 python bench.py --steps 5 --warmup 3 --workload $w 2>/dev/null | grep '^{' > gpurun_out/ci_$w.json
-done
-python tools/benchsum.py ci stream_inter_1080p | head -1
-python -c "
-import json
-d=json.loads(open('gpurun_out/ci_mc_pus.json').read()); print('mc_pus base', d['value'], d['ms_per_step'], d['roofline']['achieved'])"
-B265_NVCC_FLAGS="-DMC_PREFETCH" python -c "from libde265_b200 import build as b; b.build(force=True)" 2>&1 | tail -2
-timeout 300 python -m pytest tests/test_gpu_mc.py -m gpu -x -q 2>&1 | tail -1
-for w in mc_pus stream_inter_1080p; do
-  timeout 600 python bench.py --steps 5 --warmup 3 --workload $w 2>/dev/null | grep '^{' > gpurun_out/cj_$w.json
-done
-python tools/benchsum.py cj stream_inter_1080p | head -1
-python -c "
-import json
-d=json.loads(open('gpurun_out/cj_mc_pus.json').read()); print('mc_pus prefetch', d['value'], d['ms_per_step'], d['roofline']['achieved'])"
+timeout 600 python bench.py --steps 2 --warmup 3 > gpurun_out/d_plain.log 2>&1 || exit 1
+ncu --metrics gpu__time_duration.sum --clock-control none -s 40 -c 200 --csv --log-file gpurun_out/r2b_launches_stream4k.csv python bench.py --steps 2 --warmup 3 > gpurun_out/d_ncu1.log 2>&1
+timeout 300 python benchmarks/stage_probe.py c4_2160p_q32 128 > gpurun_out/sp128_plain.log 2>&1 || exit 1
+ncu --set full --clock-control none --import-source on -k regex:k_intra_wavefront --launch-skip 2 --launch-count 1 -o gpurun_out/r2_intra128 -f python benchmarks/stage_probe.py c4_2160p_q32 128 > gpurun_out/d_ncu2.log 2>&1
+ls -la gpurun_out/r2_intra128.ncu-rep gpurun_out/r2b_launches_stream4k.csv
+tail -1 gpurun_out/sp128_plain.log
