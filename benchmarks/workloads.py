@@ -420,6 +420,9 @@ def run_stream(a, wl, rank, world, local, ClockSampler, measured_peaks):
     step_data = data * loops
     frames_step = nuniq * loops
     dbatch = int(os.environ.get("B265_BENCH_BATCH", 16))   # override: developer sweeps
+    if "B265_RECON_CONTEXTS" not in os.environ:   # the ranks of a node share its cores: cores/N per rank for parse + reconstruction threads
+        per_rank = cores // world
+        os.environ["B265_RECON_CONTEXTS"] = "1" if per_rank <= 4 else ("2" if per_rank <= 8 else "3")
     dec = Decoder(device=local, threads=threads, batch=dbatch)
     count = [0]
     cb = lambda img: count.__setitem__(0, count[0] + 1)

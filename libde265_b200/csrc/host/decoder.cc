@@ -127,6 +127,10 @@ struct Decoder {
     }
     parse_only = g_parse_only;
     int n_ctx = 3;   // measured on 16 cores, 4K: 2 -> 808, 3 -> 859, 4 -> 654 pictures/s (host list building overlaps the GPU)
+    {   // few host cores: the reconstruction threads must not crowd out the parse threads
+      const unsigned hw = std::thread::hardware_concurrency();
+      if (hw && hw <= 4) n_ctx = 1; else if (hw && hw <= 8) n_ctx = 2;
+    }
     if (const char* e = getenv("B265_RECON_CONTEXTS")) n_ctx = std::max(1, std::min(4, atoi(e)));
     if (parse_only) n_ctx = 1;
     for (int i = 0; i < n_ctx; i++) {
