@@ -338,6 +338,44 @@ __device__ __forceinline__ bool fetch_borders(const IntraGeom& g, const CtbEdges
   const int S = E.S, q = S / 4, pitch = g.pitch;
   const int W = (g.width + g.sh) >> g.sh, H = (g.height + g.sh) >> g.sh;
   const uint8_t* org = g.plane + (size_t)E.y0 * pitch + E.x0;
+  (void)recs; (void)plane;
+  if (reuse && !interior) {
+    // The common step inside a row: only the upper-right CTB's bottom row is missing, its words were requested one CTB
+    // ahead by the lanes [q, 2q) that store them (slot == lane).
+    bool wr = false, have = true;
+    uint32_t val = 0;
+    const uint8_t* src = nullptr;
+    if (lane >= q && lane < 2 * q && ((g.nb >> 3) & 1)) {
+      const int w = lane - q;
+      if ((g.nb >> 7) & 1) {
+        wr = true;
+        if ((uint32_t)(pre >> 32) != 0) val = (uint32_t)pre;
+        else { have = false; src = mbox + (size_t)((g.cy - 1) * ctbs_w + g.cx + 1) * (4 * S) + 8 * w; }
+      } else if (E.x0 + S + 4 * w < W) {
+        wr = true;
+        val = ld_cg_u32(org - pitch + S + 4 * w);
+      }
+    }
+    unsigned polls = 0;
+    while (!__all_sync(B265_FULL_MASK, have)) {
+      if (polls) {
+        if (polls >= yield_polls) {   // warp-uniform: is another row waiting for a warp?
+          const unsigned hd = ld_relaxed_u32(&sched->head), tl = ld_relaxed_u32(&sched->tail);
+          if ((int)(tl - hd) > 0) return false;
+          polls = 1;
+        }
+        if (sleep_ns) __nanosleep(sleep_ns);
+      }
+      polls++;
+      if (!have) {
+        const unsigned long long v = ld_relaxed_u64(src);
+        if ((uint32_t)(v >> 32) != 0) { val = (uint32_t)v; have = true; }
+      }
+    }
+    if (wr) *reinterpret_cast<uint32_t*>(E.rows + 16 + 4 * lane) = val;
+    __syncwarp();
+    return true;
+  }
   // slots: [0,q) upper CTB's bottom row, [q,2q) upper-right CTB's bottom row, [2q,3q) left CTB's right column,
   // 3q: corner (last word of the upper-left CTB's bottom row); two slots per lane (3q+1 <= 49)
   const uint8_t* src[2];
@@ -358,9 +396,10 @@ __device__ __forceinline__ bool fetch_borders(const IntraGeom& g, const CtbEdges
     // neighbour CTB of the piece
     const int nx = g.cx + (piece == 1 ? 1 : (piece == 0 ? 0 : -1)), ny = g.cy - (piece == 2 ? 0 : 1);
     // not usable for prediction (outside the picture, other slice/tile): never read, never waited for
-    if (!((g.nb >> (piece == 0 ? 2 : piece == 1 ? 3 : piece == 2 ? 0 : 1)) & 1)) continue;
+    const int nbit = piece == 0 ? 2 : piece == 1 ? 3 : piece == 2 ? 0 : 1;
+    if (!((g.nb >> nbit) & 1)) continue;
     const int nctb = ny * ctbs_w + nx;
-    if ((__ldg(&recs[nctb].has) >> plane) & 1) {   // the neighbour posts its borders in this launch
+    if ((g.nb >> (4 + nbit)) & 1) {   // the neighbour posts its borders in this launch (k_intra_sched_prep)
       kind[k] = 1;
       src[k] = mbox + (size_t)nctb * (4 * S) + (piece == 2 ? 2 * S : 0) + 8 * w;
     } else if (piece == 2) {
@@ -506,7 +545,9 @@ __global__ void __launch_bounds__(256) k_intra_sched_prep(const FrameDev* __rest
           const b265_ctb r = ctbs[ny * f.ctbs_w + nx];
           ok = r.slice == me.slice && r.tile == me.tile && r.addr_ts < me.addr_ts;
         }
-        if (ok) nb |= 1u << k;
+        // bit k: usable for prediction; bit 4 + k: and it posts its borders in this launch (it has intra TBs in this plane),
+        // so the wavefront never reads a neighbour's CTB record on its chain
+        if (ok) nb |= (1u << k) | (((recs[ny * f.ctbs_w + nx].has >> c) & 1u) << (4 + k));
       }
       if (run_start(recs, f.ctbs_w, ctb, c))
         queue_put(queue, qmask, s_base[cy] + atomicAdd(&sched->level_fill[cy], 1u), row_payload(blockIdx.y, c, cy, cx));
