@@ -39,13 +39,28 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, int b, int c) {
   return d;
 }
 
-// NW words of reference row `y` starting at the 4-byte aligned column xa (all clamped to the picture)
-template <int NW>
+// NW words of reference row `y` starting at the 4-byte aligned column xa (all clamped to the picture).  Lanes hold different
+// ROWS, so every load instruction of the warp touches ~30 cache lines: the kernel is bound by L1 tag look-ups, not by bytes.
+// The row piece is therefore fetched as NV 16-byte vectors from the enclosing 16-byte aligned column and the words wanted
+// (offset 0..3 words) are picked with two levels of selects: 3 loads instead of 7 for luma, 2 instead of 4 for chroma.
+template <int NW, int NV>
 __device__ __forceinline__ void load_row(const uint8_t* __restrict__ ref, int pitch, int W, int H, int xa, int y, uint32_t (&w)[NW]) {
+  static_assert(NW + 3 <= 4 * NV, "vectors must cover every word offset");
   const uint8_t* row = ref + (size_t)clip3(0, H - 1, y) * pitch;
-  if (xa >= 0 && xa + 4 * NW <= W && (reinterpret_cast<uintptr_t>(row) & 3) == 0) {
+  const int xv = xa & ~15;
+  if (xa >= 0 && xa + 4 * NW <= W && xv + 16 * NV <= pitch && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    uint32_t u[4 * NV];
 #pragma unroll
-    for (int i = 0; i < NW; i++) w[i] = __ldg(reinterpret_cast<const uint32_t*>(row + xa) + i);
+    for (int i = 0; i < NV; i++) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(row + xv) + i);
+      u[4 * i] = v.x; u[4 * i + 1] = v.y; u[4 * i + 2] = v.z; u[4 * i + 3] = v.w;
+    }
+    const bool o1 = (xa >> 2) & 1, o2 = (xa >> 3) & 1;
+    uint32_t t[NW + 2];
+#pragma unroll
+    for (int i = 0; i < NW + 2; i++) t[i] = o1 ? u[i + 1] : u[i];
+#pragma unroll
+    for (int i = 0; i < NW; i++) w[i] = o2 ? t[i + 2] : t[i];
   } else {   // the row crosses the left or right picture edge: per-sample coordinate clamp (mc_luma, motion.cc:146-149)
 #pragma unroll
     for (int i = 0; i < NW; i++) {
@@ -61,7 +76,7 @@ __device__ __forceinline__ void load_row(const uint8_t* __restrict__ ref, int pi
 __device__ __forceinline__ void luma_fetch(bool on, int l, const uint8_t* __restrict__ ref, int pitch, int W, int H, int x0, int y0,
                                            int th, uint32_t (&w)[7]) {
   const int xs = x0 - 3;
-  if (on && l < th + 7) load_row<7>(ref, pitch, W, H, xs - (xs & 3), y0 - 3 + l, w);
+  if (on && l < th + 7) load_row<7, 3>(ref, pitch, W, H, xs - (xs & 3), y0 - 3 + l, w);
 }
 
 // two products of int16 halves of a with the two low signed bytes of b
@@ -147,7 +162,7 @@ __device__ __forceinline__ void luma_filter(int16_t* tmp, bool on, int l, const 
 __device__ __forceinline__ void chroma_fetch(bool on, int l8, const uint8_t* __restrict__ ref, int pitch, int W, int H, int x0, int y0,
                                              int chh, uint32_t (&w)[4]) {
   const int xs = x0 - 1;
-  if (on && l8 < chh + 3) load_row<4>(ref, pitch, W, H, xs - (xs & 3), y0 - 1 + l8, w);
+  if (on && l8 < chh + 3) load_row<4, 2>(ref, pitch, W, H, xs - (xs & 3), y0 - 1 + l8, w);
 }
 
 // step 2. Result: row = l8>>1, x = 4*(l8&1)..+3 of the group's tile
@@ -211,28 +226,32 @@ __device__ __forceinline__ int write_sample(const WParams& p, int a, int b) {
 // Piece records are fetched MC_CHUNK at a time, one per lane (items are consecutive, so are the records), and handed to
 // the halves pass by pass: the dependent item -> record -> slice round trips are paid once per chunk, not per piece.
 #define MC_CHUNK 16
+#ifndef MC_WARPS
+#define MC_WARPS 8
+#endif
 #ifndef MC_MIN_CTAS
 #define MC_MIN_CTAS 2
 #endif
 
-__global__ void __launch_bounds__(B265_WARPS_PER_CTA * 32, MC_MIN_CTAS)
+__global__ void __launch_bounds__(MC_WARPS * 32, MC_MIN_CTAS)
 k_mc(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ items, int n_items) {
-  __shared__ McSmem smem[B265_WARPS_PER_CTA];
+  __shared__ McSmem smem[MC_WARPS];
   McSmem& s = smem[threadIdx.x >> 5];
   const int lane = lane_id();
   const int half = lane >> 4, l = lane & 15;          // luma: half-warp per piece, lane l of the half
   const int plane = (lane >> 3) & 1, l8 = lane & 7;   // chroma: 8 lanes per (piece, plane)
   int16_t* const ltmp = s.tmp[half];
   int16_t (*const ctmp)[8] = reinterpret_cast<int16_t (*)[8]>(&s.tmp[0][0]) + (lane >> 3) * 7;
-  const int warps_total = gridDim.x * B265_WARPS_PER_CTA;
-  for (int base = (blockIdx.x * B265_WARPS_PER_CTA + (threadIdx.x >> 5)) * MC_CHUNK; base < n_items; base += warps_total * MC_CHUNK) {
+  const int warps_total = gridDim.x * MC_WARPS;
+  for (int base = (blockIdx.x * MC_WARPS + (threadIdx.x >> 5)) * MC_CHUNK; base < n_items; base += warps_total * MC_CHUNK) {
     const int cnt = min(MC_CHUNK, n_items - base);
     uint32_t my_o = 0;
     uint2 rec[3] = {make_uint2(0, 0), make_uint2(0, 0), make_uint2(0, 0)};
     if (lane < cnt) {
       my_o = __ldg(items + base + lane);
       const uint2* r = reinterpret_cast<const uint2*>(frames[my_o >> 24].pus + (my_o & 0xffffff));   // 24-byte records, 8-byte aligned
-      rec[0] = __ldg(r); rec[1] = __ldg(r + 1); rec[2] = __ldg(r + 2);
+      rec[0] = __ldg(r); rec[1] = __ldg(r + 1);
+      rec[2].x = __ldg(reinterpret_cast<const uint32_t*>(r + 2));   // the last word is padding: no dead destination register
     }
     for (int j0 = 0; j0 < cnt; j0 += 2) {
       const bool have = j0 + half < cnt;
@@ -333,7 +352,7 @@ k_mc(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ items, in
 void launch_mc(cudaStream_t st, const FrameDev* frames, const uint32_t* items, int n, int sm_count) {
   if (n <= 0) return;
   const int chunks = (n + MC_CHUNK - 1) / MC_CHUNK;
-  int ctas = (chunks + B265_WARPS_PER_CTA - 1) / B265_WARPS_PER_CTA;
-  int grid = min(ctas, sm_count * MC_MIN_CTAS * 2);
-  k_mc<<<grid, B265_WARPS_PER_CTA * 32, 0, st>>>(frames, items, n);
+  int ctas = (chunks + MC_WARPS - 1) / MC_WARPS;
+  int grid = min(ctas, sm_count * MC_MIN_CTAS * 2);   // two waves of resident CTAs, grid-stride over the chunks
+  k_mc<<<grid, MC_WARPS * 32, 0, st>>>(frames, items, n);
 }
