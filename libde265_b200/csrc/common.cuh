@@ -105,6 +105,22 @@ struct FrameDev {
 #define B265_SAOREC_FOREIGN 0x80
 
 // one picture to hash (k_hash.cu): planes of an 8-bit surface; plane[c] == NULL: no such plane (4:0:0)
+// Interleave the low 4 bits of x (even positions) and y (odd positions).
+__host__ __device__ __forceinline__ unsigned morton4(unsigned x, unsigned y) {
+  x = (x | (x << 2)) & 0x33; x = (x | (x << 1)) & 0x55;
+  y = (y | (y << 2)) & 0x33; y = (y | (y << 1)) & 0x55;
+  return x | (y << 1);
+}
+// int16 residual scratch of the coded intra TBs (FrameDev::resid): BLOCK-LINEAR.  A TB's N x N residual is one contiguous
+// run of N*N values, line l at +l*N (lines = rows, or columns for the column-wise predicted modes 2..17), at the z-order
+// position of the TB inside its CTB (TBs are aligned quadtree blocks, so such runs never overlap): the row-per-lane stores of
+// the residual pre-pass and loads of the wavefront then touch 1/4 .. 1/16 of the cache lines a pitched plane costs.
+// (x, y) in samples of the component, lg_s = log2 of the CTB size in that component.
+__host__ __device__ __forceinline__ size_t resid_block(int x, int y, int lg_s, int ctbs_w) {
+  const int m = (1 << lg_s) - 1;
+  return ((size_t)((y >> lg_s) * ctbs_w + (x >> lg_s)) << (2 * lg_s)) + ((size_t)morton4((x & m) >> 2, (y & m) >> 2) << 4);
+}
+
 struct HashJob {
   const uint8_t* plane[3];
   int w[3], h[3], pitch[3];

@@ -307,10 +307,13 @@ static int build_batch(b265_ctx* ctx, const b265_frame_job* jobs_in, int n_jobs,
       if (J.dst_surface < 0 || J.dst_surface >= (int)ctx->surfaces.size() || !ctx->surfaces[J.dst_surface].used)
         return reject(__LINE__, B265_ERR_INVALID_ARG);
       const Surface& S = ctx->surfaces[J.dst_surface];
-      so[j].resid[0] = P.take((size_t)2 * S.pitch[0] * J.height);
+      // block-linear (common.cuh resid_block): whole CTBs, S*S values each
+      const size_t nctb = (size_t)((J.width + (1 << J.log2_ctb) - 1) >> J.log2_ctb) * ((J.height + (1 << J.log2_ctb) - 1) >> J.log2_ctb);
+      (void)S;
+      so[j].resid[0] = P.take((size_t)2 * (nctb << (2 * J.log2_ctb)));
       if (J.chroma_format_idc) {
-        so[j].resid[1] = P.take((size_t)2 * S.pitch[1] * ((J.height + 1) >> 1));
-        so[j].resid[2] = P.take((size_t)2 * S.pitch[2] * ((J.height + 1) >> 1));
+        so[j].resid[1] = P.take((size_t)2 * (nctb << (2 * J.log2_ctb - 2)));
+        so[j].resid[2] = P.take((size_t)2 * (nctb << (2 * J.log2_ctb - 2)));
       }
     }
   }

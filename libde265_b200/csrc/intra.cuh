@@ -30,13 +30,6 @@ template <int N> struct IntraBuf {
   static constexpr int STRIDE = 6 * N + 8;
 };
 
-__device__ __forceinline__ unsigned morton4(unsigned x, unsigned y) {
-  // interleave the low 4 bits of x (even positions) and y (odd positions)
-  x = (x | (x << 2)) & 0x33; x = (x | (x << 1)) & 0x55;
-  y = (y | (y << 2)) & 0x33; y = (y | (y << 1)) & 0x55;
-  return x | (y << 1);
-}
-
 // Picture / CTB constants of a ticket, held in registers (the FrameDev record lives in global memory;
 // re-reading its fields per TB would cost an L2 round trip each).
 struct IntraGeom {
@@ -44,6 +37,7 @@ struct IntraGeom {
   int width, height;         // luma picture size
   int log2_ctb, log2_min_tb;
   int cx, cy;                // CTB position in CTB units
+  int ctbs_w;                // CTBs per row (resid_block)
   unsigned nb;               // neighbouring CTBs usable for prediction (same slice, same tile, earlier in decoding
                              // order; intrapred.cc:486-508): bit0 left, bit1 upper-left, bit2 upper, bit3 upper-right
   const uint8_t* unit_info;  // non-NULL only with constrained_intra_pred

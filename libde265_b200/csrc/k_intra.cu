@@ -100,7 +100,10 @@ __global__ void __launch_bounds__(256) k_intra_prep(const FrameDev* __restrict__
       }
       if (ok) g.nb |= 1u << k;
     }
-    f.tb_mask[i] = intra_avail_mask(g, tu.x, tu.y, lg);
+    // bits 0..32: availability of the neighbour units; bits 40..63: where the TB's residual lies in the block-linear scratch
+    // (resid_block, in units of 16 values), so that the wavefront has no address arithmetic on its chain
+    f.tb_mask[i] = intra_avail_mask(g, tu.x, tu.y, lg) |
+                   ((uint64_t)(resid_block(tu.x, tu.y, f.log2_ctb - g.sh, f.ctbs_w) >> 4) << 40);
   }
 }
 
@@ -148,7 +151,7 @@ __device__ __forceinline__ void store_words_smem(uint8_t* p, const uint32_t (&px
 
 template <int LOG2, bool TRACE>
 __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, int cidx, int x, int y, int mode, int flags,
-                                         bool coded, uint64_t M, uint8_t* wborder, long long (&acc)[4]) {
+                                         bool coded, uint64_t M, const int16_t* rblk, uint8_t* wborder, long long (&acc)[4]) {
   constexpr int N = 1 << LOG2, STRIDE = IntraBuf<N>::STRIDE;
   long long c0 = 0, c1 = 0, c2 = 0, c3 = 0;
   if (TRACE) c0 = clock64();
@@ -157,7 +160,7 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
   const int l = active ? lane : 0;
   // the residual line is independent of the neighbours: issue its load first
   uint32_t r[N / 2];
-  if (coded && active) load_resid_line<N>(g.resid + (size_t)(y + l) * g.pitch + x, r);
+  if (coded && active) load_resid_line<N>(rblk + l * N, r);
   const int xr = x - E.x0, yr = y - E.y0;
   uint8_t* buf0 = wborder;
   uint8_t* buf1 = buf0 + STRIDE;
@@ -203,7 +206,7 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
 // passes of the warp, a 16x16 block one pass with all lanes busy.  One body for every size.
 template <bool TRACE>
 __device__ __forceinline__ void intra_tb_seg(const CtbEdges& E, const IntraGeom& g, int cidx, int x, int y, int log2, int mode, int flags,
-                                             bool coded, uint64_t M, uint8_t* wborder, long long (&acc)[4]) {
+                                             bool coded, uint64_t M, const int16_t* rblk, uint8_t* wborder, long long (&acc)[4]) {
   long long c0 = 0, c1 = 0, c2 = 0;
   if (TRACE) c0 = clock64();
   const int lane = lane_id();
@@ -214,10 +217,11 @@ __device__ __forceinline__ void intra_tb_seg(const CtbEdges& E, const IntraGeom&
   // the residual of the first pass is independent of the neighbours: issue its load first
   int item = lane;
   uint32_t r[4] = {0, 0, 0, 0};
+  const int16_t* rbase = rblk;
   auto load_resid = [&](int it, uint32_t (&rr)[4]) {
     if (!coded || it >= items) return;
     const int l = it >> lseg, sg = it & ((1 << lseg) - 1);
-    const int16_t* p = g.resid + (size_t)(y + l) * g.pitch + x + 8 * sg;
+    const int16_t* p = rbase + l * N + 8 * sg;
     if (small) {
       const uint2 v = __ldg(reinterpret_cast<const uint2*>(p));
       rr[0] = v.x; rr[1] = v.y;
@@ -597,7 +601,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
     masks = reinterpret_cast<const uint2*>(f->tb_mask);
     g.sh = (c && f->cw) ? 1 : 0;
     g.width = f->width; g.height = f->height;
-    g.log2_ctb = f->log2_ctb; g.log2_min_tb = f->log2_min_tb;
+    g.log2_ctb = f->log2_ctb; g.log2_min_tb = f->log2_min_tb; g.ctbs_w = ctbs_w;
     g.plane = f->plane[c]; g.resid = f->resid[c]; g.pitch = f->pitch[c];
     g.unit_info = (fflags & B265_FRAME_CONSTRAINED_INTRA) ? f->unit_info : nullptr;
     g.unit_pitch = g.width >> 2;
@@ -703,17 +707,18 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
             const int x = (int)(r0 & 0xffff), y = (int)(r0 >> 16);
             const int flags = (int)((r1 >> 8) & 0xff), mode = (int)(r1 >> 24);
             const bool coded = (r3 & 0xffff) != 0;
-            const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) |
-                               ((uint64_t)__shfl_sync(B265_FULL_MASK, mymask.y, src) << 32);
+            const uint32_t mhi = __shfl_sync(B265_FULL_MASK, mymask.y, src);
+            const uint64_t M = (uint64_t)__shfl_sync(B265_FULL_MASK, mymask.x, src) | ((uint64_t)(mhi & 0xffu) << 32);
+            const int16_t* rblk = g.resid + ((size_t)(mhi >> 8) << 4);   // the TB's residual block (k_intra_prep)
             if (TRACE) n_tbs++;
             // two forms of the same arithmetic, bit-identical; which sizes take which: INTRA_SEG_SIZES above
             {
               const int lg = (int)((r1 >> 2) & 7);   // SEGMAX is a mask of the log2 sizes that take the segment code
-              if ((SEGMAX >> lg) & 1) intra_tb_seg<TRACE>(E, g, c, x, y, lg, mode, flags, coded, M, s_border[warp], acc);
-              else if (!((SEGMAX >> 5) & 1) && lg == 5) intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
-              else if (!((SEGMAX >> 4) & 1) && lg == 4) intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
-              else if (!((SEGMAX >> 3) & 1) && lg == 3) intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
-              else if (!((SEGMAX >> 2) & 1)) intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, s_border[warp], acc);
+              if ((SEGMAX >> lg) & 1) intra_tb_seg<TRACE>(E, g, c, x, y, lg, mode, flags, coded, M, rblk, s_border[warp], acc);
+              else if (!((SEGMAX >> 5) & 1) && lg == 5) intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
+              else if (!((SEGMAX >> 4) & 1) && lg == 4) intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
+              else if (!((SEGMAX >> 3) & 1) && lg == 3) intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
+              else if (!((SEGMAX >> 2) & 1)) intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
             }
           }
         }

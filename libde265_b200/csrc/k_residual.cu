@@ -102,9 +102,9 @@ k_residual_sparse(const FrameDev* __restrict__ frames, const uint32_t* __restric
     if (SCRATCH) {
       int16_t* d = nullptr;
       int pitch = 0;
-      if (active) {
-        pitch = f->pitch[cidx];
-        d = f->resid[cidx] + (size_t)tu.y * pitch + tu.x;
+      if (active) {   // block-linear scratch (common.cuh resid_block): the TB's lines are N apart
+        pitch = N;
+        d = f->resid[cidx] + resid_block(tu.x, tu.y, f->log2_ctb - ((cidx && f->cw) ? 1 : 0), f->ctbs_w);
       }
       residual_store_scratch<LOG2>(blk, sub, tu.flags, bounds, active, d, pitch, tu.intra_mode >= 2 && tu.intra_mode < 18);
     } else {

@@ -361,22 +361,45 @@ k_residual_sparse_fast(const FrameDev* __restrict__ frames, const uint32_t* __re
   const int grp = lane / N, sub = lane % N;
   uint32_t* blk = smem[warp] + grp * Cfg::BLKW;
   const int slot = pair_slot(N, sub);
-  const int warps_total = gridDim.x * DENSE_WARPS;
-  for (int base = (blockIdx.x * DENSE_WARPS + warp) * G; base < n; base += warps_total * G) {
-    const int i = base + grp;
-    const bool active = i < n;
-    b265_tu tu = {};
-    const FrameDev* f = frames;
-    if (active) {
-      const uint32_t o = order[i];
-      f = frames + (o >> 24);
-      tu = f->tus[o & 0xffffff];
-    }
+  const int stride = gridDim.x * DENSE_WARPS * G;
+  // The chain list item -> frame -> TU record -> levels is three dependent memory round trips per TU.  It is walked two
+  // iterations ahead: the item of iteration k+2 and the TU record of iteration k+1 are requested while TU k is computed
+  // (SPARSE_PREFETCH: also the cache lines of its levels).
+  int base = (blockIdx.x * DENSE_WARPS + warp) * G;
+  auto item_at = [&](int b, bool& ok) -> uint32_t {
+    ok = b < n && b + grp < n;
+    return ok ? __ldg(order + b + grp) : 0u;
+  };
+  auto tu_at = [&](uint32_t o, bool ok, const FrameDev*& f) -> uint4 {
+    f = frames + (o >> 24);
+    return ok ? __ldg(reinterpret_cast<const uint4*>(f->tus + (o & 0xffffff))) : make_uint4(0, 0, 0, 0);
+  };
+  bool ok_next, ok_nn;
+  uint32_t o_next = item_at(base, ok_next);
+  const FrameDev* f_next;
+  uint4 tu_next = tu_at(o_next, ok_next, f_next);
+  uint32_t o_nn = item_at(base + stride, ok_nn);
+  uint32_t kc_pref = 0;
+  if (ok_next && sub < (int)(tu_next.w & 0xffff)) kc_pref = __ldg(reinterpret_cast<const uint32_t*>(f_next->coeffs + tu_next.z) + sub);
+  for (; base < n; base += stride) {
+    const bool active = ok_next;
+    const FrameDev* f = f_next;
+    b265_tu tu;
+    tu.x = (uint16_t)(tu_next.x & 0xffff); tu.y = (uint16_t)(tu_next.x >> 16);
+    tu.cidx_log2 = (uint8_t)tu_next.y; tu.flags = (uint8_t)(tu_next.y >> 8); tu.qp = (uint8_t)(tu_next.y >> 16);
+    tu.intra_mode = (uint8_t)(tu_next.y >> 24);
+    tu.coeff_off = tu_next.z;
+    tu.ncoeff = (uint16_t)(tu_next.w & 0xffff);
+    tu.reserved = 0;
+    ok_next = ok_nn;
+    o_next = o_nn;
+    o_nn = item_at(base + 2 * stride, ok_nn);
     const int cidx = tu.cidx_log2 & 3;
     __syncwarp();   // the previous iteration's row pass has read the result plane
 #pragma unroll
     for (int q = 0; q < N / 8; q++) reinterpret_cast<uint4*>(blk)[sub * (N / 8) + q] = make_uint4(0, 0, 0, 0);
     __syncwarp();
+    tu_next = tu_at(o_next, ok_next, f_next);
     // ---- scatter + dequantise ----
     int mx = -1, my = -1;
     {
@@ -387,7 +410,9 @@ k_residual_sparse_fast(const FrameDev* __restrict__ frames, const uint32_t* __re
       const int mid = cidx + ((tu.flags & B265_TU_INTRA_CU) ? 0 : (N < 32 ? 3 : 1));
       int16_t* plane = reinterpret_cast<int16_t*>(blk);
       for (int e = sub; e < ncoeff; e += N) {
-        const b265_coeff kc = c[e];
+        b265_coeff kc;
+        if (e == sub) { kc.level = (int16_t)(kc_pref & 0xffff); kc.pos = (uint16_t)(kc_pref >> 16); }   // requested an iteration ago
+        else kc = c[e];
         const int x = kc.pos & (N - 1), y = kc.pos >> LOG2;
         int v;
         if (sl) v = dequant_list(kc.level, tu.qp, LOG2, (LOG2 == 4) ? sl->s16[mid][kc.pos] : sl->s32[mid][kc.pos]);
@@ -407,6 +432,10 @@ k_residual_sparse_fast(const FrameDev* __restrict__ frames, const uint32_t* __re
     else if (nrows > 4) dense_cols<LOG2, 8>(blk, sub, slot);
     else dense_cols<LOG2, 4>(blk, sub, slot);
     __syncwarp();
+    // the next TU's first levels (one per lane; most TUs have no more) travel during the row pass and the stores
+    kc_pref = 0;
+    if (ok_next && sub < (int)(tu_next.w & 0xffff))
+      kc_pref = __ldg(reinterpret_cast<const uint32_t*>(f_next->coeffs + tu_next.z) + sub);
     // ---- second pass along the rows ----
     int out[N];
     if (N >= 32 && ncols > 16) sparse_rows<LOG2, (N >= 32 ? 32 : N)>(blk, sub, out);
@@ -416,22 +445,27 @@ k_residual_sparse_fast(const FrameDev* __restrict__ frames, const uint32_t* __re
     if (!active) continue;
     const int pitch = f->pitch[cidx];
     if (SCRATCH) {
-      int16_t* d = f->resid[cidx] + (size_t)tu.y * pitch + tu.x;
+      // block-linear scratch (common.cuh resid_block): line l of the TB at +l*N, the whole TB contiguous
+      int16_t* d = f->resid[cidx] + resid_block(tu.x, tu.y, f->log2_ctb - ((cidx && f->cw) ? 1 : 0), f->ctbs_w);
       const bool transposed = tu.intra_mode >= 2 && tu.intra_mode < 18;
       if (transposed) {
 #pragma unroll
-        for (int x = 0; x < N; x++) d[(size_t)x * pitch + sub] = (int16_t)min(max(out[x] >> 12, -1024), 1023);
+        for (int x = 0; x < N; x++) d[x * N + sub] = (int16_t)min(max(out[x] >> 12, -1024), 1023);
       } else {
-        uint4* dr = reinterpret_cast<uint4*>(d + (size_t)sub * pitch);
+        // Every lane stores another row, so a store instruction costs one L1 wavefront per lane whatever its width (the
+        // pre-pass is bound by exactly those, ncu l1tex data-pipe 64-74 %): 32 bytes per instruction (sm_100 STG.256)
+        int16_t* dr = d + sub * N;   // 32-byte aligned: a TB starts at a multiple of 256 values, a line is 32 or 64 bytes
 #pragma unroll
-        for (int q = 0; q < N / 8; q++) {
-          uint32_t w[4];
+        for (int q = 0; q < N / 16; q++) {
+          uint32_t w[8];
 #pragma unroll
-          for (int j = 0; j < 4; j++) {
-            const uint32_t p2 = pack_sat16(out[8 * q + 2 * j] >> 12, out[8 * q + 2 * j + 1] >> 12);
+          for (int j = 0; j < 8; j++) {
+            const uint32_t p2 = pack_sat16(out[16 * q + 2 * j] >> 12, out[16 * q + 2 * j + 1] >> 12);
             w[j] = __vmaxs2(__vmins2(p2, 0x03ff03ffu), 0xfc00fc00u);
           }
-          dr[q] = make_uint4(w[0], w[1], w[2], w[3]);
+          asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dr + 16 * q), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                       "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+                       : "memory");
         }
       }
     } else {
