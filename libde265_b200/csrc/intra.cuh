@@ -101,6 +101,21 @@ struct CtbEdges {
 };
 __host__ __device__ constexpr int ctb_edges_bytes(int S) { return (S / 4 + 1) * (2 * S + 16) + (S / 4 + 1) * S; }
 
+// General reference-sample substitution for one scan unit (any availability pattern; constrained_intra_pred can punch holes
+// into the run): kept out of line, the wavefront's hot path is the single-run form in gather_border.
+static __device__ __noinline__ uint32_t gather_fetch_general(uint64_t M, int s, int H, const uint8_t* colp, const uint8_t* rowp) {
+  const bool av = (M >> s) & 1;
+  const uint64_t lower = M & (((uint64_t)1 << s) - 1);
+  int t = av ? s : (lower ? 63 - __clzll((long long)lower) : __ffsll((long long)M) - 1);
+  const int pick = av ? 0 : (lower ? 1 : 2);   // 0 = the unit itself, 1 = its last sample in scan order, 2 = its first sample
+  if (M == 0) t = H;
+  const uint8_t* a = t < H ? colp + 4 * (H - 1 - t) : rowp + 4 * (t - H - 1);
+  const uint32_t w = *reinterpret_cast<const uint32_t*>(a);
+  const bool byte0 = (t < H) ? (pick == 1) : (pick == 2 && t != H);
+  const uint32_t sel = (pick == 0 && t != H) ? 0x3210u : (byte0 ? 0x0000u : 0x3333u);
+  return M ? __byte_perm(w, 0, sel) : 0x80808080u;
+}
+
 // Border of the TB at (xr,yr) relative to the CTB origin -> buf (IntraBuf layout), with the reference
 // sample substitution of intrapred.cc:395-431: a missing unit copies the nearest available sample before it
 // in scan order, leading missing units copy the first available sample, nothing available -> 128.
@@ -114,30 +129,32 @@ __device__ __forceinline__ void gather_border(const CtbEdges& E, int xr, int yr,
   const mask_t M = (mask_t)M64;
   const uint8_t* colp = E.cols + (xr >> 2) * E.S + yr;                   // column xr-1, from the TB's first row down
   const uint8_t* rowp = E.rows + (yr >> 2) * E.rstride + 16 + xr;        // row yr-1, from the TB's first column on
-  auto fetch = [&](int s) -> uint32_t {
-    const bool av = (M >> s) & 1;
-    const mask_t lower = M & (((mask_t)1 << s) - 1);
-    int t, pick;  // pick: 0 = the unit itself, 1 = its last sample in scan order, 2 = its first sample
-    if (N == 32) {
-      t = av ? s : (lower ? 63 - __clzll((long long)lower) : __ffsll((long long)M) - 1);
-    } else {
-      t = av ? s : (lower ? 31 - __clz((int)lower) : __ffs((int)M) - 1);
-    }
-    pick = av ? 0 : (lower ? 1 : 2);
-    if (M == 0) t = H;
-    // unit t as a word: left units run down the column, the corner is the last byte of the word before the row
-    const uint8_t* a = t < H ? colp + 4 * (H - 1 - t) : rowp + 4 * (t - H - 1);
-    const uint32_t w = *reinterpret_cast<const uint32_t*>(a);
-    // scan order runs UP the left column (last sample = byte 0) and RIGHT along the top row (last = byte 3)
-    const bool byte0 = (t < H) ? (pick == 1) : (pick == 2 && t != H);
-    const uint32_t sel = (pick == 0 && t != H) ? 0x3210u : (byte0 ? 0x0000u : 0x3333u);
-    return M ? __byte_perm(w, 0, sel) : 0x80808080u;
-  };
   const bool left = lane < H;
   const int wi = left ? lane : lane - H;                           // word of the line: samples 1+4w .. 4+4w
   const int s = lane < N ? (left ? H - 1 - lane : lane + 1) : H;   // scan unit of this lane
-  const uint32_t v = fetch(s);
-  const uint32_t c = fetch(H);
+  // Nearly always the available units are ONE run [ra, rb] of the scan (missing: a piece of the lower-left end and / or of
+  // the upper-right end): the source unit is then the scan unit clamped to the run - two warp-uniform bit scans instead of a
+  // masked scan per lane on the chain.
+  const int ra = (N == 32) ? __ffsll((long long)M) - 1 : __ffs((int)M) - 1;
+  const int rb = (N == 32) ? 63 - __clzll((long long)M) : 31 - __clz((int)M);
+  uint32_t v, c;
+  if (M != 0 && M == (mask_t)((((mask_t)2 << rb) - 1) & ~(((mask_t)1 << ra) - 1))) {
+    auto fetch_run = [&](int u) -> uint32_t {
+      const int t = min(max(u, ra), rb);
+      const uint8_t* a = t < H ? colp + 4 * (H - 1 - t) : rowp + 4 * (t - H - 1);
+      const uint32_t w = *reinterpret_cast<const uint32_t*>(a);
+      // below the run: first sample of unit ra; above it: last sample of unit rb; scan order runs UP the left column (last
+      // sample = byte 0) and RIGHT along the top row (last = byte 3); the corner unit is the last byte of its word
+      const bool byte0 = (t < H) ? (u > rb) : (u < ra && t != H);
+      const uint32_t sel = (u == t && t != H) ? 0x3210u : (byte0 ? 0x0000u : 0x3333u);
+      return __byte_perm(w, 0, sel);
+    };
+    v = fetch_run(s);
+    c = fetch_run(H);
+  } else {
+    v = gather_fetch_general((uint64_t)M, s, H, colp, rowp);
+    c = gather_fetch_general((uint64_t)M, H, H, colp, rowp);
+  }
   if (lane < N) *reinterpret_cast<uint32_t*>(buf + (left ? IntraBuf<N>::LEFT : IntraBuf<N>::TOP) + 1 + 4 * wi) = v;
   if (lane == 0) {
     buf[IntraBuf<N>::TOP] = (uint8_t)c;
