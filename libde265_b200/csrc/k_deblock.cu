@@ -168,8 +168,11 @@ __device__ __forceinline__ void deblock_luma_segment(const FrameDev& f, int ux, 
 #ifndef DBK_ROUNDS
 #define DBK_ROUNDS 4
 #endif
+#ifndef DBK_MIN_CTAS
+#define DBK_MIN_CTAS 10   // 48 registers: 40 warps per SM (ncu: long-scoreboard bound at 28); measured 8 / 9 / 10: deblock stage of 128 4K pictures 1.42 / 1.37 / 1.35 ms, 1.48 at 72 registers
+#endif
 template <bool VERT>
-__global__ void __launch_bounds__(DBK_WARPS * 32) k_deblock_luma(const FrameDev* __restrict__ frames) {
+__global__ void __launch_bounds__(DBK_WARPS * 32, DBK_MIN_CTAS) k_deblock_luma(const FrameDev* __restrict__ frames) {
   const FrameDev& f = frames[blockIdx.y];
   if (!(f.flags & B265_FRAME_DEBLOCK) || !f.unit_info) return;
   __shared__ uint32_t queue[DBK_WARPS][DBK_ROUNDS * 32];
