@@ -239,16 +239,34 @@ __global__ void k_deblock_chroma(const FrameDev* __restrict__ frames) {
     const int tc = c_tc[clip3(0, 53, qpc + 2 * (bs - 1) + tc_offset)];
     const int pitch = f.pitch[c];
     uint8_t* ptr = f.plane[c] + (size_t)yc * pitch + xc;
+    // word accesses (xc is a multiple of 8 for vertical, of 4 for horizontal edges): the kernel waits on its loads
+    if (VERT) {
+      uint32_t wp[4], wq[4];
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      uint8_t* p0p = VERT ? ptr + k * pitch - 1 : ptr + k - pitch;
-      uint8_t* p1p = VERT ? ptr + k * pitch - 2 : ptr + k - 2 * pitch;
-      uint8_t* q0p = VERT ? ptr + k * pitch : ptr + k;
-      uint8_t* q1p = VERT ? ptr + k * pitch + 1 : ptr + k + pitch;
-      const int p0 = *p0p, p1 = *p1p, q0 = *q0p, q1 = *q1p;
-      const int delta = clip3(-tc, tc, ((((q0 - p0) << 2) + p1 - q1 + 4) >> 3));
-      if (filterP) *p0p = (uint8_t)clip8(p0 + delta);
-      if (filterQ) *q0p = (uint8_t)clip8(q0 - delta);
+      for (int k = 0; k < 4; k++) {
+        wp[k] = *reinterpret_cast<const uint32_t*>(ptr + k * pitch - 4);
+        wq[k] = *reinterpret_cast<const uint32_t*>(ptr + k * pitch);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int p1 = (wp[k] >> 16) & 0xff, p0 = wp[k] >> 24, q0 = wq[k] & 0xff, q1 = (wq[k] >> 8) & 0xff;
+        const int delta = clip3(-tc, tc, ((((q0 - p0) << 2) + p1 - q1 + 4) >> 3));
+        if (filterP) ptr[k * pitch - 1] = (uint8_t)clip8(p0 + delta);
+        if (filterQ) ptr[k * pitch] = (uint8_t)clip8(q0 - delta);
+      }
+    } else {
+      const uint32_t P1 = *reinterpret_cast<const uint32_t*>(ptr - 2 * pitch), P0 = *reinterpret_cast<const uint32_t*>(ptr - pitch);
+      const uint32_t Q0 = *reinterpret_cast<const uint32_t*>(ptr), Q1 = *reinterpret_cast<const uint32_t*>(ptr + pitch);
+      int np[4], nq[4];
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const int p1 = (P1 >> (8 * k)) & 0xff, p0 = (P0 >> (8 * k)) & 0xff, q0 = (Q0 >> (8 * k)) & 0xff, q1 = (Q1 >> (8 * k)) & 0xff;
+        const int delta = clip3(-tc, tc, ((((q0 - p0) << 2) + p1 - q1 + 4) >> 3));
+        np[k] = clip8(p0 + delta);
+        nq[k] = clip8(q0 - delta);
+      }
+      if (filterP) *reinterpret_cast<uint32_t*>(ptr - pitch) = pack4(np[0], np[1], np[2], np[3]);
+      if (filterQ) *reinterpret_cast<uint32_t*>(ptr) = pack4(nq[0], nq[1], nq[2], nq[3]);
     }
   }
 }
