@@ -1,4 +1,5 @@
-timeout 900 python -m pytest tests/test_gpu_frames.py tests/test_gpu_streams.py tests/test_gpu_kernel_api.py -m gpu -x -q 2>&1 | tail -2
-timeout 300 python bench.py --steps 5 --warmup 3 2>/dev/null | grep '^{' | python -c "
-import json,sys
-d=json.loads(sys.stdin.read()); print('  4k', d['value'], d['config']['stage_ms[pcm+mc,residual+avail,intra_wavefront,deblock,sao,total]'])"
+mkdir -p gpurun_out
+timeout 1500 compute-sanitizer --tool memcheck --error-exitcode 7 python -m pytest tests/test_gpu_mc.py "tests/test_gpu_streams.py::test_stream_md5" tests/test_gpu_frames.py -m gpu -x -q -k "not 2160p and not 1080p and not concurrent" > gpurun_out/sanitizer.log 2>&1
+echo "exit $?"
+grep -c "Invalid\|out of bounds" gpurun_out/sanitizer.log
+tail -5 gpurun_out/sanitizer.log
