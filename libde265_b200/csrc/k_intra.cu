@@ -202,6 +202,123 @@ __device__ __forceinline__ void intra_tb(const CtbEdges& E, const IntraGeom& g, 
 }
 
 
+// 4x4 blocks without the border buffer: a third of the TBs of a textured picture are 4x4 and sit in long serial chains (one
+// CTB can hold 64 of them), where the cost of a TB is the LATENCY of its instruction chain, not its 16 samples.  Every lane
+// reads the five neighbour units (lower-left, left, corner, top, upper-right) straight from the edge store (same addresses
+// in all lanes: broadcasts), substitutes the missing ones in registers and predicts from registers; one barrier per TB (the
+// edge store update) instead of three, no shared-memory round trip between gather and prediction.  Same arithmetic as
+// gather_border / predict_line (intra.cuh), bit-identical.
+//   selectors that build ref[-4..-1] of the main line from the other line's samples 1..4 (inverse-angle projection,
+//   intrapred.cc:937-951), per mode 11..25
+__constant__ uint16_t c_neg_sel4[15] = {0x0, 0x0, 0x3000, 0x1000, 0x1300, 0x1200, 0x130, 0x120, 0x130, 0x1200, 0x1300, 0x1000, 0x3000, 0x0, 0x0};
+
+template <bool TRACE>
+__device__ __forceinline__ void intra_tb4(const CtbEdges& E, const IntraGeom& g, int cidx, int x, int y, int mode, int flags,
+                                          bool coded, uint32_t M, const int16_t* rblk, long long (&acc)[4]) {
+  long long c0 = 0;
+  if (TRACE) c0 = clock64();
+  const int lane = lane_id();
+  const bool active = lane < 4;
+  const int l = lane & 3;
+  uint2 res = make_uint2(0, 0);
+  if (coded && active) res = __ldg(reinterpret_cast<const uint2*>(rblk + 4 * l));
+  const int xr = x - E.x0, yr = y - E.y0;
+  const uint8_t* colp = E.cols + (xr >> 2) * E.S + yr;              // column xr-1, rows yr ..
+  const uint8_t* rowp = E.rows + (yr >> 2) * E.rstride + 16 + xr;   // row yr-1, columns xr ..
+  // units in scan order: 0 lower-left (rows yr+4..7), 1 left, 2 corner, 3 top, 4 upper-right
+  uint32_t U[5];
+  U[0] = *reinterpret_cast<const uint32_t*>(colp + 4);
+  U[1] = *reinterpret_cast<const uint32_t*>(colp);
+  U[2] = __byte_perm(*reinterpret_cast<const uint32_t*>(rowp - 4), 0, 0x3333);
+  U[3] = *reinterpret_cast<const uint32_t*>(rowp);
+  U[4] = *reinterpret_cast<const uint32_t*>(rowp + 4);
+  // reference sample substitution (intrapred.cc:395-431): the scan runs UP the left column (first sample of a left unit =
+  // byte 3, last = byte 0) and RIGHT along the top row (first = byte 0, last = byte 3)
+  if (M == 0) {
+#pragma unroll
+    for (int i = 0; i < 5; i++) U[i] = 0x80808080u;
+  } else {
+    const int first = __ffs((int)M) - 1;
+    uint32_t lead = 0;
+#pragma unroll
+    for (int i = 0; i < 5; i++)
+      if (i == first) lead = __byte_perm(U[i], 0, i < 2 ? 0x3333 : 0x0000);
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+      if (i < first) U[i] = lead;
+      else if (i > 0 && !((M >> i) & 1)) U[i] = __byte_perm(U[i - 1], 0, (i - 1) < 2 ? 0x0000 : 0x3333);
+    }
+  }
+  const uint32_t L0 = U[1], L1 = U[0], T0 = U[3], T1 = U[4], corner = U[2] & 0xff;   // L[1..4], L[5..8], T[1..4], T[5..8]
+  uint32_t h0, h1;
+  bool by_column = false;
+  if (mode >= 2) {   // angular (intrapred.cc:903-1005)
+    const bool horiz = mode < 18;
+    const uint32_t m0 = horiz ? L0 : T0, m1 = horiz ? L1 : T1, o0 = horiz ? T0 : L0;
+    const int ang = c_intra_angle[mode];
+    // ref[-4..11] as four words; ref[0] = corner, ref[k] = main line sample k
+    const uint32_t R0 = (ang < 0) ? __byte_perm(o0, 0, c_neg_sel4[mode - 11]) : 0u;
+    const uint32_t R1 = corner | (m0 << 8), R2 = __funnelshift_r(m0, m1, 24), R3 = m1 >> 24;
+    const int t = (l + 1) * ang, idx = t >> 5, f = t & 31;
+    const int p = idx + 5, w = p >> 2, b = 8 * (p & 3);   // ref[idx+1] is byte p of the sixteen
+    const uint32_t A = w == 0 ? R0 : (w == 1 ? R1 : R2), B = w == 0 ? R1 : (w == 1 ? R2 : R3), Cw = w == 0 ? R2 : (w == 1 ? R3 : 0u);
+    const uint32_t lo0 = __funnelshift_r(A, B, b), lo1 = __funnelshift_r(B, Cw, b);
+    const uint32_t W0 = (uint32_t)(32 - f) | ((uint32_t)f << 8);
+    const uint32_t b34 = __funnelshift_r(lo0, lo1, 24);
+    const uint32_t v0 = __dp4a(lo0, W0, 16u), v1 = __dp4a(lo0, W0 << 8, 16u), v2 = __dp4a(lo0, W0 << 16, 16u), v3 = __dp4a(b34, W0, 16u);
+    h0 = (__byte_perm(v0, v1, 0x5410) >> 5) & 0x00ff00ffu;
+    h1 = (__byte_perm(v2, v3, 0x5410) >> 5) & 0x00ff00ffu;
+    if ((mode == 26 || mode == 10) && cidx == 0 && !(flags & B265_TU_NO_EDGE_FILT))
+      h0 = (h0 & 0xffff0000u) | (uint32_t)clip8((int)(m0 & 0xff) + (((int)((o0 >> (8 * l)) & 0xff) - (int)corner) >> 1));
+    by_column = horiz;
+  } else if (mode == 0) {   // planar (intrapred.cc:1009-1032), lane = row
+    const uint32_t abd = ((L0 >> (8 * l)) & 0xff) | ((T1 & 0xff) << 8) | ((L1 & 0xff) << 24);
+    const uint32_t Wy = ((uint32_t)(3 - l) << 16) | ((uint32_t)(l + 1) << 24);
+    uint32_t v[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      const uint32_t op = __byte_perm(abd, T0, 0x3010u | ((4u + i) << 8));   // [L[1+y], T[5], T[1+x], L[5]]
+      v[i] = __dp4a(op, Wy | (uint32_t)(3 - i) | ((uint32_t)(i + 1) << 8), 4u) >> 3;
+    }
+    h0 = v[0] | (v[1] << 16);
+    h1 = v[2] | (v[3] << 16);
+  } else {   // DC (intrapred.cc:1036-1069), lane = row
+    const int dc = (int)(__dp4a(T0, 0x01010101u, 0u) + __dp4a(L0, 0x01010101u, 4u)) >> 3;
+    h0 = h1 = (uint32_t)dc * 0x00010001u;
+    if (cidx == 0) {
+      if (l == 0) {
+        h0 = (uint32_t)(((int)(T0 & 0xff) + 3 * dc + 2) >> 2) | ((uint32_t)(((int)((T0 >> 8) & 0xff) + 3 * dc + 2) >> 2) << 16);
+        h1 = (uint32_t)(((int)((T0 >> 16) & 0xff) + 3 * dc + 2) >> 2) | ((uint32_t)(((int)(T0 >> 24) + 3 * dc + 2) >> 2) << 16);
+        h0 = (h0 & 0xffff0000u) | (uint32_t)(((int)(L0 & 0xff) + 2 * dc + (int)(T0 & 0xff) + 2) >> 2);
+      } else {
+        h0 = (h0 & 0xffff0000u) | (uint32_t)(((int)((L0 >> (8 * l)) & 0xff) + 3 * dc + 2) >> 2);
+      }
+    }
+  }
+  if (coded) {
+    h0 = __viaddmin_s16x2_relu(h0, res.x, 0x00ff00ffu);
+    h1 = __viaddmin_s16x2_relu(h1, res.y, 0x00ff00ffu);
+  }
+  const uint32_t px = __byte_perm(h0, h1, 0x6420);
+  if (active) {
+    uint8_t* d = g.plane + (size_t)y * g.pitch + x;
+    uint8_t* erow = E.rows + ((yr + 4) >> 2) * E.rstride + 16 + xr;   // the TB's bottom row
+    uint8_t* ecol = E.cols + ((xr + 4) >> 2) * E.S + yr;              // its right column
+    if (!by_column) {   // lane = row
+      *reinterpret_cast<uint32_t*>(d + (size_t)l * g.pitch) = px;
+      ecol[l] = (uint8_t)(px >> 24);
+      if (l == 3) *reinterpret_cast<uint32_t*>(erow) = px;
+    } else {            // lane = column
+#pragma unroll
+      for (int j = 0; j < 4; j++) d[(size_t)j * g.pitch + l] = (uint8_t)(px >> (8 * j));
+      erow[l] = (uint8_t)(px >> 24);
+      if (l == 3) *reinterpret_cast<uint32_t*>(ecol) = px;
+    }
+  }
+  __syncwarp();  // the next TB of this CTB reads the edge store
+  if (TRACE) acc[0] += clock64() - c0;
+}
+
 // Size-independent form (intra_seg.cuh): a lane's unit of work is one 8-sample segment of a line; a 32x32 block is four
 // passes of the warp, a 16x16 block one pass with all lanes busy.  One body for every size.
 template <bool TRACE>
@@ -718,7 +835,7 @@ k_intra_wavefront(const FrameDev* __restrict__ frames, IntraSched* sched, unsign
               else if (!((SEGMAX >> 5) & 1) && lg == 5) intra_tb<5, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
               else if (!((SEGMAX >> 4) & 1) && lg == 4) intra_tb<4, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
               else if (!((SEGMAX >> 3) & 1) && lg == 3) intra_tb<3, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
-              else if (!((SEGMAX >> 2) & 1)) intra_tb<2, TRACE>(E, g, c, x, y, mode, flags, coded, M, rblk, s_border[warp], acc);
+              else if (!((SEGMAX >> 2) & 1)) intra_tb4<TRACE>(E, g, c, x, y, mode, flags, coded, (uint32_t)M, rblk, acc);
             }
           }
         }
