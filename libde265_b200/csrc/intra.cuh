@@ -81,6 +81,29 @@ __device__ __forceinline__ bool unit_available(const IntraGeom& g, unsigned cur_
 __device__ __forceinline__ uint64_t intra_avail_mask(const IntraGeom& g, int xB, int yB, int log2) {
   const int N = 1 << log2, H = N >> 1, sh = g.sh;
   const unsigned cur_zs = zs_in_ctb(g, xB << sh, yB << sh);
+  if (!g.unit_info) {
+    // Without constrained_intra_pred five tests decide everything: the units next to the left column, next to the top row,
+    // below-left and above-right each lie in ONE aligned N x N block (all in one CTB, all before or all after the current
+    // block in z-scan), so each group shares its answer; only the picture's bottom / right edge can cut the two outer groups.
+    const int Q = N >> 2;   // units per group
+    uint64_t M = 0;
+    if (unit_available(g, cur_zs, (xB - 1) << sh, (yB + N) << sh)) {            // below-left: units s = Q-1 (nearest) .. 0
+      // the reference tests a left unit at its LAST row: units that lie completely above the picture's bottom edge
+      const int rows_left = (((g.height + (1 << sh) - 1) >> sh) - (yB + N)) >> 2;
+      const int n = min(Q, max(rows_left, 0));
+      M |= (((uint64_t)1 << n) - 1) << (Q - n);
+    }
+    if (unit_available(g, cur_zs, (xB - 1) << sh, yB << sh)) M |= (((uint64_t)1 << Q) - 1) << Q;          // left: s = Q .. H-1
+    if (unit_available(g, cur_zs, (xB - 1) << sh, (yB - 1) << sh)) M |= (uint64_t)1 << H;                  // corner
+    if (unit_available(g, cur_zs, xB << sh, (yB - 1) << sh)) M |= (((uint64_t)1 << Q) - 1) << (H + 1);    // top
+    if (unit_available(g, cur_zs, (xB + N) << sh, (yB - 1) << sh)) {                                       // above-right
+      // ... and a top unit at its FIRST column
+      const int cols_left = (g.width - ((xB + N) << sh) + (4 << sh) - 1) >> (2 + sh);
+      const int n = min(Q, max(cols_left, 0));
+      M |= (((uint64_t)1 << n) - 1) << (H + 1 + Q);
+    }
+    return M;
+  }
   uint64_t M = 0;
   for (int s = 0; s < H; s++)
     if (unit_available(g, cur_zs, (xB - 1) << sh, (yB + 2 * N - 1 - 4 * s) << sh)) M |= 1ull << s;
