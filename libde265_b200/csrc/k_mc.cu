@@ -73,10 +73,15 @@ __device__ __forceinline__ void load_row(const uint8_t* __restrict__ ref, int pi
 }
 
 // luma, step 1: lane l < th+7 of the half fetches reference row l of the piece at (x0,y0) (7 words from the aligned column)
+// Without a vertical phase only the th rows of the piece itself are read (rows 3 .. th+2 of the window): the vertical tap
+// vector is then {0,0,0,64,..}, whatever is left in the other rows of the shared buffer is multiplied by zero.
+__device__ __forceinline__ bool row_wanted(int l, int n, int halo_before, int halo, int frac) {
+  return frac ? l < n + halo : (l >= halo_before && l < n + halo_before);
+}
 __device__ __forceinline__ void luma_fetch(bool on, int l, const uint8_t* __restrict__ ref, int pitch, int W, int H, int x0, int y0,
-                                           int th, uint32_t (&w)[7]) {
+                                           int th, int fy, uint32_t (&w)[7]) {
   const int xs = x0 - 3;
-  if (on && l < th + 7) load_row<7, 3>(ref, pitch, W, H, xs - (xs & 3), y0 - 3 + l, w);
+  if (on && row_wanted(l, th, 3, 7, fy)) load_row<7, 3>(ref, pitch, W, H, xs - (xs & 3), y0 - 3 + l, w);
 }
 
 // two products of int16 halves of a with the two low signed bytes of b
@@ -100,7 +105,7 @@ __device__ __forceinline__ int tmp_row(int r) { return (r + (r >> 2)) * 16; }
 __device__ __forceinline__ void luma_filter(int16_t* tmp, bool on, int l, const uint32_t (&w)[7], int x0, int fx, int fy, int tw,
                                             int th, int (&out)[8]) {
   const int off = (x0 - 3) & 3;
-  if (on && l < th + 7) {
+  if (on && row_wanted(l, th, 3, 7, fy)) {
     uint32_t a[6];
 #pragma unroll
     for (int i = 0; i < 6; i++) a[i] = __funnelshift_r(w[i], w[i + 1], 8 * off);
@@ -160,16 +165,16 @@ __device__ __forceinline__ void luma_filter(int16_t* tmp, bool on, int l, const 
 
 // chroma: a group of 8 lanes per (piece, plane), tile cw x chh <= 8x4.  Step 1: lane l8 < chh+3 fetches row l8.
 __device__ __forceinline__ void chroma_fetch(bool on, int l8, const uint8_t* __restrict__ ref, int pitch, int W, int H, int x0, int y0,
-                                             int chh, uint32_t (&w)[4]) {
+                                             int chh, int fy, uint32_t (&w)[4]) {
   const int xs = x0 - 1;
-  if (on && l8 < chh + 3) load_row<4, 2>(ref, pitch, W, H, xs - (xs & 3), y0 - 1 + l8, w);
+  if (on && row_wanted(l8, chh, 1, 3, fy)) load_row<4, 2>(ref, pitch, W, H, xs - (xs & 3), y0 - 1 + l8, w);
 }
 
 // step 2. Result: row = l8>>1, x = 4*(l8&1)..+3 of the group's tile
 __device__ __forceinline__ void chroma_filter(int16_t (*tmp)[8], bool on, int l8, const uint32_t (&w)[4], int x0, int fx, int fy, int cw,
                                               int chh, int (&out)[4]) {
   const int off = (x0 - 1) & 3;
-  if (on && l8 < chh + 3) {
+  if (on && row_wanted(l8, chh, 1, 3, fy)) {
     uint32_t a[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) a[i] = __funnelshift_r(w[i], w[i + 1], 8 * off);
@@ -296,10 +301,10 @@ k_mc(const FrameDev* __restrict__ frames, const uint32_t* __restrict__ items, in
       const int cpx = px >> 1, cpy = py >> 1;
       const int cax = cpx + (mvax >> 3), cay = cpy + (mvay >> 3), cbx = cpx + (mv1x >> 3), cby = cpy + (mv1y >> 3);
       uint32_t wa[7], wb[7], wca[4], wcb[4];
-      luma_fetch(on, l, f.ref_plane[slota][0], pitch0, W, H, lax, lay, th, wa);
-      luma_fetch(bi, l, f.ref_plane[slot1][0], pitch0, W, H, lbx, lby, th, wb);
-      chroma_fetch(con, l8, f.ref_plane[slota][1 + plane], pitch1, fcw, fch, cax, cay, th >> 1, wca);
-      chroma_fetch(cbi, l8, f.ref_plane[slot1][1 + plane], pitch1, fcw, fch, cbx, cby, th >> 1, wcb);
+      luma_fetch(on, l, f.ref_plane[slota][0], pitch0, W, H, lax, lay, th, mvay & 3, wa);
+      luma_fetch(bi, l, f.ref_plane[slot1][0], pitch0, W, H, lbx, lby, th, mv1y & 3, wb);
+      chroma_fetch(con, l8, f.ref_plane[slota][1 + plane], pitch1, fcw, fch, cax, cay, th >> 1, mvay & 7, wca);
+      chroma_fetch(cbi, l8, f.ref_plane[slot1][1 + plane], pitch1, fcw, fch, cbx, cby, th >> 1, mv1y & 7, wcb);
       const bool any_bi = __any_sync(B265_FULL_MASK, bi), any_c = __any_sync(B265_FULL_MASK, con);
       // ---- luma ----
       int a[8], b[8];
