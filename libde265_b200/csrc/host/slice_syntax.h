@@ -14,8 +14,8 @@
 //   S4 read_pcm_samples       (slice.cc:4356)   -> b265_pcm + sample bytes
 //   deblocking edge flags (deblock.cc:130-225), QP_Y / pred-mode / pcm / bypass maps -> unit_info, qp_y
 //   sao_info (slice.h:265-273)                  -> b265_sao per CTB
-// Inter prediction syntax (prediction_unit, merge/AMVP) is not implemented yet: P/B slices are
-// rejected with DE265_ERROR_NOT_IMPLEMENTED_YET (502).
+//   S3 generate_inter_prediction_samples (slice.cc:4110-4140 -> motion.cc:279) -> b265_pu (motion vectors derived here:
+//      merge candidates, AMVP, temporal MVP = the reference's motion.cc:1020-2160)
 #pragma once
 #include <string.h>
 #include <algorithm>
