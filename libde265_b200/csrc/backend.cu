@@ -59,15 +59,16 @@ int64_t b265_now_ns() {
   return std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
-// A peer counts when its last batch is still on the device, or was handed over within the last 20 ms: contexts that take
-// turns (the decoder's reconstruction threads, a server's streams) keep their shares while one of them is between batches.
+// A peer counts when its last batch is still on the device, or was handed over within the last 200 ms: contexts that take
+// turns (the decoder's reconstruction threads, a server's streams) keep their shares while one of them is between batches
+// (one full-size grid among shared ones stalls every peer for the length of its wavefront).
 int b265_busy_peers(b265_ctx* ctx) {
   std::lock_guard<std::mutex> lk(g_ctx_mu);
   const int64_t now = b265_now_ns();
   int n = 0;
   for (b265_ctx* c : g_ctxs) {
     if (c == ctx || c->device != ctx->device || !c->busy_recorded.load(std::memory_order_acquire)) continue;
-    if (now - c->last_batch_ns.load(std::memory_order_relaxed) < 20000000 || cudaEventQuery(c->ev_busy) == cudaErrorNotReady) n++;
+    if (now - c->last_batch_ns.load(std::memory_order_relaxed) < 200000000 || cudaEventQuery(c->ev_busy) == cudaErrorNotReady) n++;
   }
   cudaGetLastError();   // cudaErrorNotReady is not sticky, but leave no trace for the next CK_LAUNCH
   return n;
