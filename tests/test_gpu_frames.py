@@ -68,6 +68,32 @@ def test_batch_of_frames(ctx):
         ctx.surface_release(s)
 
 
+def test_batch_larger_than_a_launch_group(ctx):
+    """300 independent pictures in ONE submit: frames.cu cuts launch groups at 255 pictures (work-list items name their picture
+    in 8 bits relative to the group); every picture still equals the C oracle.  Four distinct synthetic pictures, repeated."""
+    rng = np.random.default_rng(10)
+    w, h = 128, 64
+    base = [SynthJob(rng, w, h, log2_ctb=4 + (i % 2), deblock=(i != 1), sao=(i >= 2)) for i in range(4)]
+    want = []
+    for i, sj in enumerate(base):
+        recon, dbk, outs = oracle_frame(sj.job, w, h)
+        want.append(outs if i >= 2 else (dbk if i != 1 else recon))
+    jobs, sids = [], []
+    for k in range(300):
+        J = L.FrameJob()
+        C.memmove(C.byref(J), C.byref(base[k % 4].job), C.sizeof(L.FrameJob))
+        J.dst_surface = ctx.surface_alloc(w, h)
+        sids.append(J.dst_surface)
+        jobs.append(J)
+    ctx.submit_frames(jobs)
+    for k in (0, 1, 2, 3, 127, 254, 255, 256, 257, 299):
+        got = ctx.surface_download(sids[k], w, h)
+        for c in range(3):
+            assert np.array_equal(got[c], want[k % 4][c]), (k, c)
+    for s_ in sids:
+        ctx.surface_release(s_)
+
+
 @pytest.mark.parametrize("name", ["c1_1080p_q32_lf", "gen_pb_1080p_ld32"])
 def test_concurrent_contexts_share_the_device(name):
     """Four contexts each run a batch of the same stream at the same time, several rounds without a host sync: the intra
