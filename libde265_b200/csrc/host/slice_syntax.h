@@ -336,8 +336,10 @@ void SliceDec<Eng>::decode_qp(int xCU, int yCU, int log2_cb) {
   qp_cr_prime = qc_cr + sps.qp_bd_offset_c;
   const int n_cb = 1 << (std::max(log2_cb, 3) - sps.log2_min_cb);
   const int ci = cb_idx(xCU, yCU);
-  for (int j = 0; j < n_cb && (yCU >> sps.log2_min_cb) + j < pic.cb_h; j++)
-    for (int i = 0; i < n_cb && (xCU >> sps.log2_min_cb) + i < pic.cb_w; i++) pic.qp_y[ci + j * pic.cb_w + i] = (int8_t)qpy;
+  {
+    const int nx = std::min(n_cb, pic.cb_w - (xCU >> sps.log2_min_cb)), ny = std::min(n_cb, pic.cb_h - (yCU >> sps.log2_min_cb));
+    for (int j = 0; j < ny; j++) memset(&pic.qp_y[ci + j * pic.cb_w], qpy, (size_t)std::max(nx, 0));
+  }
   cur_qpy = qpy;
 }
 
@@ -350,9 +352,18 @@ void SliceDec<Eng>::mark_tu_edges(int x0, int y0, int log2_ts, int xCU, int yCU,
   const int n_u = 1 << (log2_ts - 2);
   const int ux = x0 >> 2, uy = y0 >> 2;
   uint8_t* ui = pic.unit_info.data();
-  if (cbf_luma)
-    for (int j = 0; j < n_u; j++)
-      for (int i = 0; i < n_u; i++) ui[(uy + j) * pic.u_w + ux + i] |= B265_UNIT_CBF;
+  if (cbf_luma) {   // whole words where the TB is wide enough (x86: unaligned word access is fine; memcpy keeps it legal C++)
+    for (int j = 0; j < n_u; j++) {
+      uint8_t* row = ui + (uy + j) * pic.u_w + ux;
+      if (n_u == 8) {
+        uint64_t v; memcpy(&v, row, 8); v |= 0x0101010101010101ull * B265_UNIT_CBF; memcpy(row, &v, 8);
+      } else if (n_u == 4) {
+        uint32_t v; memcpy(&v, row, 4); v |= 0x01010101u * B265_UNIT_CBF; memcpy(row, &v, 4);
+      } else {
+        for (int i = 0; i < n_u; i++) row[i] |= B265_UNIT_CBF;
+      }
+    }
+  }
   if (sh.deblocking_disabled) return;
   pic.any_deblock = true;
   bool filter_left = true, filter_top = true;
